@@ -1,0 +1,199 @@
+"""Generate tests/golden/*.npz by running the UNMODIFIED reference in the build container.
+
+TEST INFRASTRUCTURE.  Run as `python oracle/make_golden.py [fk] [geometry] [warp] [model]`
+(no argument = all).  /root/reference is read-only and absent on the GPU box, so the
+outputs are committed; this script is the provenance record for every fixture.
+
+Fixtures
+  fk_user05.npz   poses + hand model of sample_data/user05/recording_{00,02,11}.json and the
+                  reference's own golden `gt_keypoints` from the sibling .npy pickles
+                  (written by run_eval_known_skeleton.py:96-104) -> FK known-answer test.
+  geometry.npz    real calibration / per-frame camera poses / GT hand poses from
+                  sample_data/recording_00.json (every 3rd frame) + the crop cameras the
+                  reference HandTracker.gen_crop_cameras (tracker.py:222-260) produced.
+  warp.npz        reference tracker._warp_image (tracker.py:61-89, numpy fp64 + cv2.remap)
+                  outputs for crops of that geometry on seeded synthetic images.
+  model.npz       reference UmeTrackModel outputs (umetrack_model.py:188-242) for the seeded
+                  state dict of absolutetrack_b200 `make_random_state_dict(0)`.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+GOLD = os.path.join(ROOT, "tests", "golden")
+sys.path.insert(0, HERE)
+
+import ref_import  # noqa: E402
+
+ref_import.import_reference()
+REF = ref_import.REFERENCE_ROOT
+
+from lib.tracker import tracker as RT  # noqa: E402
+from lib.tracker.perspective_crop import landmarks_from_hand_pose  # noqa: E402
+from lib.tracker.tracking_result import SingleHandPose  # noqa: E402
+from lib.tracker.video_pose_data import _load_hand_pose_labels  # noqa: E402
+
+HM_KEYS = [
+    "joint_rotation_axes",
+    "joint_rest_positions",
+    "landmark_rest_positions",
+    "landmark_rest_bone_weights",
+    "landmark_rest_bone_indices",
+    "joint_limits",
+]
+
+
+def hand_model_arrays(hm, prefix=""):
+    out = {}
+    for k in HM_KEYS:
+        v = getattr(hm, k)
+        if v is not None:
+            out[prefix + k] = v.numpy()
+    return out
+
+
+def synth_image(kind, seed, H=480, W=636):
+    """Synthetic source view: 'noise' = iid uniform u8, 'smooth' = band-limited."""
+    if kind == "noise":
+        return np.random.default_rng(seed).integers(0, 256, (H, W), dtype=np.uint8)
+    y, x = np.mgrid[0:H, 0:W].astype(np.float64)
+    v = 127 + 100 * np.sin((x + 7 * seed) / 15.0) * np.cos((y + 3 * seed) / 11.0)
+    return np.clip(np.rint(v), 0, 255).astype(np.uint8)
+
+
+class _SizeOnlyModel:
+    def getInputImageSizes(self):
+        return (96, 96)
+
+    def to(self, d):
+        return self
+
+
+def make_fk():
+    out = {}
+    for rec in ["00", "02", "11"]:
+        L = _load_hand_pose_labels(f"{REF}/sample_data/user05/recording_{rec}.json")
+        g = np.load(f"{REF}/sample_data/user05/recording_{rec}.npy", allow_pickle=True)
+        g = g if isinstance(g, dict) else g.item()
+        valid = g["valid_tracking"]  # [2,T]
+        # sanity: the reference FK run now reproduces its own stored golden
+        for h in range(2):
+            for t in np.nonzero(valid[h])[0][::50]:
+                lm = landmarks_from_hand_pose(
+                    L.hand_model, SingleHandPose(L.joint_angles[t, h], L.wrist_transforms[t, h], 1.0), h
+                )
+                assert np.abs(lm - g["gt_keypoints"][h, t]).max() < 1e-3
+        p = f"r{rec}_"
+        out[p + "joint_angles"] = L.joint_angles.astype(np.float32)  # [T,2,22]
+        out[p + "wrist_transforms"] = L.wrist_transforms.astype(np.float64)  # [T,2,4,4]
+        out[p + "valid"] = valid
+        out[p + "gt_keypoints"] = g["gt_keypoints"].astype(np.float32)  # [2,T,21,3]
+        out.update(hand_model_arrays(L.hand_model, p))
+    np.savez_compressed(os.path.join(GOLD, "fk_user05.npz"), **out)
+    print("fk_user05.npz", sum(int(out[k].sum()) for k in out if k.endswith("valid")), "poses")
+
+
+def _frames():
+    L = _load_hand_pose_labels(f"{REF}/sample_data/recording_00.json")
+    idx = np.arange(0, len(L), 3)
+    return L, idx
+
+
+def make_geometry():
+    L, idx = _frames()
+    ht = RT.HandTracker(_SizeOnlyModel(), RT.HandTrackerOpts())
+    out = {
+        "frame_index": idx,
+        "cam_f": np.array([c.f for c in L.cameras], np.float64),
+        "cam_c": np.array([c.c for c in L.cameras], np.float64),
+        "cam_coeffs": np.array([tuple(c.distort) for c in L.cameras], np.float64),
+        "cam_wh": np.array([(c.width, c.height) for c in L.cameras], np.int64),
+        "camera_angles": np.array(L.camera_angles, np.float64),
+        "camera_to_world": L.camera_to_world_transforms[idx].astype(np.float64),
+        "joint_angles": L.joint_angles[idx].astype(np.float64),
+        "wrist_transforms": L.wrist_transforms[idx].astype(np.float64),
+        "hand_confidences": L.hand_confidences[idx].astype(np.float64),
+    }
+    out.update(hand_model_arrays(L.hand_model, "hm_"))
+    gen = _load_generic()
+    out.update(hand_model_arrays(gen, "generic_"))
+    # crop cameras from the reference: [F,2 hands,2 slots]: cam index (-1 = none), f, c, c2w
+    F = len(idx)
+    cc_cam = -np.ones((F, 2, 2), np.int64)
+    cc_f = np.zeros((F, 2, 2, 2))
+    cc_c = np.zeros((F, 2, 2, 2))
+    cc_c2w = np.zeros((F, 2, 2, 4, 4))
+    for k, fi in enumerate(idx):
+        cams = [c.copy(camera_to_world_xf=L.camera_to_world_transforms[fi, i]) for i, c in enumerate(L.cameras)]
+        gt = {
+            h: SingleHandPose(L.joint_angles[fi, h], L.wrist_transforms[fi, h], L.hand_confidences[fi, h])
+            for h in range(2)
+            if L.hand_confidences[fi, h] > 0
+        }
+        cc = ht.gen_crop_cameras(cams, L.camera_angles, L.hand_model, gt, 1)
+        for h, d in cc.items():
+            for s, (ci, cam) in enumerate(d.items()):
+                cc_cam[k, h, s] = ci
+                cc_f[k, h, s] = cam.f
+                cc_c[k, h, s] = cam.c
+                cc_c2w[k, h, s] = cam.camera_to_world_xf
+    out.update(crop_cam=cc_cam, crop_f=cc_f, crop_c=cc_c, crop_c2w=cc_c2w)
+    np.savez_compressed(os.path.join(GOLD, "geometry.npz"), **out)
+    print("geometry.npz", F, "frames", int((cc_cam >= 0).sum()), "crops")
+
+
+def _load_generic():
+    import json
+
+    from lib.common.hand import HandModel
+
+    with open(f"{REF}/dataset/generic_hand_model.json") as f:
+        js = json.load(f)
+    keep = {k: (torch.tensor(v) if isinstance(v, list) else v) for k, v in js.items()}
+    for k in ("mesh_vertices", "mesh_triangles", "dense_bone_weights"):
+        keep[k] = None
+    return HandModel(**keep)
+
+
+def make_warp():
+    from lib.common import camera as RC
+
+    G = np.load(os.path.join(GOLD, "geometry.npz"))
+    crops, meta = [], []
+    n = 0
+    for k in range(0, G["crop_cam"].shape[0], 10):
+        for h in range(2):
+            for s in range(2):
+                ci = int(G["crop_cam"][k, h, s])
+                if ci < 0:
+                    continue
+                src = RC.Fisheye62CameraModel(
+                    636, 480, G["cam_f"][ci], G["cam_c"][ci], G["cam_coeffs"][ci], G["camera_to_world"][k, ci]
+                )
+                dst = RC.PinholePlaneCameraModel(96, 96, G["crop_f"][k, h, s], G["crop_c"][k, h, s], [], G["crop_c2w"][k, h, s])
+                kind = "noise" if n % 2 == 0 else "smooth"
+                img = synth_image(kind, n)
+                crops.append(RT._warp_image(src, dst, img))
+                meta.append((k, h, s, n % 2, n))
+                n += 1
+    np.savez_compressed(os.path.join(GOLD, "warp.npz"), crops=np.stack(crops), meta=np.array(meta, np.int64))
+    print("warp.npz", len(crops), "crops")
+
+
+if __name__ == "__main__":
+    os.makedirs(GOLD, exist_ok=True)
+    what = sys.argv[1:] or ["fk", "geometry", "warp", "model"]
+    if "fk" in what:
+        make_fk()
+    if "geometry" in what:
+        make_geometry()
+    if "warp" in what:
+        make_warp()
+    if "model" in what:
+        from make_golden_model import make_model
+
+        make_model()

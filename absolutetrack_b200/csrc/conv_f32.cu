@@ -1,0 +1,292 @@
+// float32 NHWC implicit-GEMM convolution on CUDA cores (the reference-exact encoder/tail path,
+// AT_PREC_FP32) + the fused stem (conv3x3(1->32)+BN+ReLU+maxpool2).
+//
+// Replaces the cuDNN/oneDNN calls behind backbone_resnet.py:56-72 (BasicBlock),
+// model_utils.py:119-135 (stem, proj), :141-163 (fusion), :195-208 (head), temporal.py:31-37.
+// GEMM view: M = N*Ho*Wo output pixels, N = Cout, K = kh*kw*Cin.  BatchNorm is folded into the
+// weights on the host; the epilogue fuses bias + residual + ReLU and can write into a channel
+// slice of a wider NHWC buffer (concat for free).
+#include "conv.cuh"
+
+namespace at {
+
+namespace {
+
+constexpr int BK = 16;
+constexpr int kConvThreads = 256;
+
+struct ConvArgs {
+  const float* in;
+  const float* w;     // [taps][Cin][CoutP]
+  const float* bias;  // [CoutP]
+  const float* res;   // optional residual, NHWC with res_ld channels per pixel
+  float* out;
+  int N, H, W, Cin, Ho, Wo, Cout, CoutP;
+  int ksize, stride, pad;
+  int in_ld, in_coff, out_ld, out_coff, res_ld;
+  int relu;
+  int M;  // N*Ho*Wo
+};
+
+template <int BM, int BN>
+__global__ void __launch_bounds__(kConvThreads) conv_nhwc_f32_kernel(ConvArgs a) {
+  constexpr int TN_THREADS = BN / 4;
+  constexpr int A_F4 = BM * BK / 4 / kConvThreads;  // float4 loads of A per thread (1 or 2)
+  constexpr int LDA = BM + 4;
+  static_assert(BM * BN / 16 == kConvThreads, "tile/threads mismatch");
+  __shared__ __align__(16) float As[2][BK][LDA];
+  __shared__ __align__(16) float Bs[2][BK][BN];
+
+  const int tid = threadIdx.x;
+  const int m0 = blockIdx.x * BM;
+  const int n0 = blockIdx.y * BN;
+  const int tx = tid % TN_THREADS, ty = tid / TN_THREADS;
+
+  // A-load bookkeeping: this thread always loads the same pixel row(s), 4 consecutive k
+  int a_row[A_F4], a_kq[A_F4], a_img[A_F4], a_oy[A_F4], a_ox[A_F4];
+  bool a_ok[A_F4];
+#pragma unroll
+  for (int i = 0; i < A_F4; ++i) {
+    const int l = tid + i * kConvThreads;
+    a_row[i] = l / 4;
+    a_kq[i] = l % 4;
+    const int m = m0 + a_row[i];
+    a_ok[i] = m < a.M;
+    const int mm = a_ok[i] ? m : 0;
+    a_img[i] = mm / (a.Ho * a.Wo);
+    const int rem = mm - a_img[i] * (a.Ho * a.Wo);
+    a_oy[i] = rem / a.Wo;
+    a_ox[i] = rem - a_oy[i] * a.Wo;
+  }
+  const int b_row = tid / TN_THREADS, b_c4 = tid % TN_THREADS;
+  const bool b_thread = b_row < BK;
+  const bool vec_in = ((a.Cin | a.in_ld | a.in_coff) & 3) == 0;
+
+  const int kchunks = (a.Cin + BK - 1) / BK;
+  const int taps = a.ksize * a.ksize;
+  const int steps = taps * kchunks;
+
+  float4 ra[A_F4];
+  float4 rb;
+
+  auto load_step = [&](int step) {
+    const int tap = step / kchunks;
+    const int k0 = (step - tap * kchunks) * BK;
+    const int r = tap / a.ksize, s = tap - r * a.ksize;
+#pragma unroll
+    for (int i = 0; i < A_F4; ++i) {
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      const int iy = a_oy[i] * a.stride + r - a.pad;
+      const int ix = a_ox[i] * a.stride + s - a.pad;
+      const int k = k0 + a_kq[i] * 4;
+      if (a_ok[i] && (unsigned)iy < (unsigned)a.H && (unsigned)ix < (unsigned)a.W && k < a.Cin) {
+        const float* p = a.in + ((int64_t)(a_img[i] * a.H + iy) * a.W + ix) * a.in_ld + a.in_coff + k;
+        if (vec_in) {
+          v = __ldg(reinterpret_cast<const float4*>(p));
+        } else {
+          v.x = __ldg(p);
+          if (k + 1 < a.Cin) v.y = __ldg(p + 1);
+          if (k + 2 < a.Cin) v.z = __ldg(p + 2);
+          if (k + 3 < a.Cin) v.w = __ldg(p + 3);
+        }
+      }
+      ra[i] = v;
+    }
+    rb = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (b_thread) {
+      const int k = k0 + b_row;
+      const int n = n0 + b_c4 * 4;
+      if (k < a.Cin && n < a.CoutP)
+        rb = __ldg(reinterpret_cast<const float4*>(a.w + ((int64_t)tap * a.Cin + k) * a.CoutP + n));
+    }
+  };
+  auto store_step = [&](int buf) {
+#pragma unroll
+    for (int i = 0; i < A_F4; ++i) {
+      As[buf][a_kq[i] * 4 + 0][a_row[i]] = ra[i].x;
+      As[buf][a_kq[i] * 4 + 1][a_row[i]] = ra[i].y;
+      As[buf][a_kq[i] * 4 + 2][a_row[i]] = ra[i].z;
+      As[buf][a_kq[i] * 4 + 3][a_row[i]] = ra[i].w;
+    }
+    if (b_thread) *reinterpret_cast<float4*>(&Bs[buf][b_row][b_c4 * 4]) = rb;
+  };
+
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  load_step(0);
+  store_step(0);
+  __syncthreads();
+  for (int step = 0; step < steps; ++step) {
+    const int buf = step & 1;
+    if (step + 1 < steps) load_step(step + 1);
+#pragma unroll
+    for (int kk = 0; kk < BK; ++kk) {
+      const float4 av = *reinterpret_cast<const float4*>(&As[buf][kk][ty * 4]);
+      const float4 bv = *reinterpret_cast<const float4*>(&Bs[buf][kk][tx * 4]);
+      const float am[4] = {av.x, av.y, av.z, av.w};
+      const float bn[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(am[i], bn[j], acc[i][j]);
+    }
+    if (step + 1 < steps) store_step(buf ^ 1);
+    __syncthreads();
+  }
+
+  // epilogue: bias + residual + relu
+  const int n = n0 + tx * 4;
+  if (n >= a.Cout) return;
+  float bias[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) bias[j] = (n + j < a.CoutP) ? __ldg(a.bias + n + j) : 0.f;
+  const bool vec_out = ((a.out_ld | a.out_coff) & 3) == 0 && (n + 3 < a.Cout);
+  const bool vec_res = a.res != nullptr && (a.res_ld & 3) == 0 && (n + 3 < a.Cout);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int m = m0 + ty * 4 + i;
+    if (m >= a.M) continue;
+    float v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = acc[i][j] + bias[j];
+    if (a.res != nullptr) {
+      const float* rp = a.res + (int64_t)m * a.res_ld + n;
+      if (vec_res) {
+        const float4 rv = __ldg(reinterpret_cast<const float4*>(rp));
+        v[0] += rv.x; v[1] += rv.y; v[2] += rv.z; v[3] += rv.w;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (n + j < a.Cout) v[j] += __ldg(rp + j);
+      }
+    }
+    if (a.relu) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] = fmaxf(v[j], 0.f);
+    }
+    float* op = a.out + (int64_t)m * a.out_ld + a.out_coff + n;
+    if (vec_out) {
+      *reinterpret_cast<float4*>(op) = make_float4(v[0], v[1], v[2], v[3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (n + j < a.Cout) op[j] = v[j];
+    }
+  }
+}
+
+// Stem: conv3x3(1->32, pad 1, bias) + BN (folded) + ReLU + maxpool 2x2   (model_utils.py:119-124)
+// in: crops [c,96,96] (u8 grey levels -> /255, or f32); out NHWC [c,48,48,32] f32.
+// One thread = one pooled pixel x 8 output channels (4 lanes cover the 32 channels).
+template <typename TIn>
+__global__ void __launch_bounds__(256) stem_kernel(const TIn* __restrict__ crops, const float* __restrict__ w,
+                                                   const float* __restrict__ bias, float* __restrict__ out, int c,
+                                                   int H, int W) {
+  __shared__ float sw[9 * 32];
+  __shared__ float sb[32];
+  for (int i = threadIdx.x; i < 9 * 32; i += blockDim.x) sw[i] = w[i];
+  if (threadIdx.x < 32) sb[threadIdx.x] = bias[threadIdx.x];
+  __syncthreads();
+  const int Hp = H / 2, Wp = W / 2;
+  const int64_t total = (int64_t)c * Hp * Wp * 4;
+  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= total) return;
+  const int cg = (int)(gid & 3);  // channel group of 8
+  const int64_t pix = gid >> 2;
+  const int px = (int)(pix % Wp);
+  const int py = (int)((pix / Wp) % Hp);
+  const int64_t img = pix / ((int64_t)Wp * Hp);
+  const TIn* ip = crops + img * H * W;
+  float patch[4][4];
+#pragma unroll
+  for (int dy = 0; dy < 4; ++dy)
+#pragma unroll
+    for (int dx = 0; dx < 4; ++dx) {
+      const int y = 2 * py - 1 + dy, x = 2 * px - 1 + dx;
+      float v = 0.f;
+      if ((unsigned)y < (unsigned)H && (unsigned)x < (unsigned)W) {
+        if (sizeof(TIn) == 1)
+          v = __fdiv_rn((float)ip[y * W + x], 255.0f);
+        else
+          v = (float)ip[y * W + x];
+      }
+      patch[dy][dx] = v;
+    }
+  float res[8];
+#pragma unroll
+  for (int ch = 0; ch < 8; ++ch) {
+    const int co = cg * 8 + ch;
+    float best = 0.f;  // ReLU then max == max(0, max of the four)
+#pragma unroll
+    for (int oy = 0; oy < 2; ++oy)
+#pragma unroll
+      for (int ox = 0; ox < 2; ++ox) {
+        float s = sb[co];
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+          for (int q = 0; q < 3; ++q) s = fmaf(patch[oy + r][ox + q], sw[(r * 3 + q) * 32 + co], s);
+        best = fmaxf(best, s);
+      }
+    res[ch] = best;
+  }
+  float4* op = reinterpret_cast<float4*>(out + pix * 32 + cg * 8);
+  op[0] = make_float4(res[0], res[1], res[2], res[3]);
+  op[1] = make_float4(res[4], res[5], res[6], res[7]);
+}
+
+}  // namespace
+
+int conv_nhwc_f32(const ConvLayer& L, const float* blob, const float* in, int in_ld, int in_coff, const float* res,
+                  int res_ld, float* out, int out_ld, int out_coff, int N, int H, int W, bool relu,
+                  cudaStream_t stream) {
+  ConvArgs a;
+  a.in = in;
+  a.w = blob + L.weight_offset;
+  a.bias = blob + L.bias_offset;
+  a.res = res;
+  a.out = out;
+  a.N = N; a.H = H; a.W = W; a.Cin = L.cin;
+  a.ksize = L.ksize; a.stride = L.stride; a.pad = L.ksize / 2;
+  a.Ho = (H + 2 * a.pad - L.ksize) / L.stride + 1;
+  a.Wo = (W + 2 * a.pad - L.ksize) / L.stride + 1;
+  a.Cout = L.cout;
+  a.CoutP = (int)round_up(L.cout, 4);
+  a.in_ld = in_ld; a.in_coff = in_coff; a.out_ld = out_ld; a.out_coff = out_coff; a.res_ld = res_ld;
+  a.relu = relu ? 1 : 0;
+  const int64_t M = (int64_t)N * a.Ho * a.Wo;
+  if (M == 0) return AT_OK;
+  if (M > 0x7fffffffLL) {
+    set_error("conv_nhwc_f32: M too large");
+    return AT_ERR_INVALID_ARGUMENT;
+  }
+  a.M = (int)M;
+  if (L.cout <= 32) {
+    dim3 grid((unsigned)((M + 127) / 128), (unsigned)((L.cout + 31) / 32));
+    conv_nhwc_f32_kernel<128, 32><<<grid, kConvThreads, 0, stream>>>(a);
+  } else {
+    dim3 grid((unsigned)((M + 63) / 64), (unsigned)((L.cout + 63) / 64));
+    conv_nhwc_f32_kernel<64, 64><<<grid, kConvThreads, 0, stream>>>(a);
+  }
+  return check_launch("conv_nhwc_f32_kernel");
+}
+
+int stem_f32(const ConvLayer& L, const float* blob, const void* crops, int crop_dtype, float* out, int c,
+             cudaStream_t stream) {
+  const int H = 96, W = 96;
+  const int64_t total = (int64_t)c * (H / 2) * (W / 2) * 4;
+  const unsigned blocks = (unsigned)((total + 255) / 256);
+  if (crop_dtype == AT_U8)
+    stem_kernel<uint8_t><<<blocks, 256, 0, stream>>>((const uint8_t*)crops, blob + L.weight_offset,
+                                                      blob + L.bias_offset, out, c, H, W);
+  else
+    stem_kernel<float><<<blocks, 256, 0, stream>>>((const float*)crops, blob + L.weight_offset, blob + L.bias_offset,
+                                                    out, c, H, W);
+  return check_launch("stem_kernel");
+}
+
+}  // namespace at

@@ -1,0 +1,198 @@
+// Perspective-crop resampler: fused  dst-pixel -> fisheye source map  +  OpenCV fixed-point
+// bilinear gather  +  /255 and dtype convert.   Replaces tracker._warp_image
+// (lib/tracker/tracker.py:61-89) and the /255 of tracker.py:332; and, second kernel, the
+// torch_data homography resampler (lib/batched_dataset/data_transform.py:78-144).
+//
+// Roofline: HBM-bound by design (source bounding box bytes + 96*96*sizeof(out) per crop).
+// One CTA handles a quarter of one crop (24 rows), threads walk dst pixels in raster order so
+// output stores are fully coalesced and the gathered source taps of a warp are neighbours
+// (they hit the same few 128B lines through L1).
+#include "at_common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kSplit = 4;  // CTAs per crop
+
+template <typename T>
+struct MapParams {
+  T M[9], d[3], fdx, fdy, cdx, cdy, fsx, fsy, csx, csy, k1, k2, k3, k4, p1, p2, k5, k6;
+};
+
+template <typename T>
+__device__ __forceinline__ T t_sqrt(T x);
+template <>
+__device__ __forceinline__ float t_sqrt<float>(float x) { return sqrtf(x); }
+template <>
+__device__ __forceinline__ double t_sqrt<double>(double x) { return sqrt(x); }
+template <typename T>
+__device__ __forceinline__ T t_atan2(T y, T x);
+template <>
+__device__ __forceinline__ float t_atan2<float>(float y, float x) { return atan2f(y, x); }
+template <>
+__device__ __forceinline__ double t_atan2<double>(double y, double x) { return atan2(y, x); }
+
+// Map one dst pixel to float32 source window coordinates, in the reference's operation order:
+// camera.py:320-329,69-75 (pinhole unproject + normalise, eps 5.43e-20), :296-306 (rotate),
+// :80-85 (arctan projection, eps 2^-128), :122-143 (Fisheye62), :308-312, tracker.py:78-82.
+template <typename T>
+__device__ __forceinline__ void map_pixel(const MapParams<T>& P, int x, int y, float& wx, float& wy) {
+  const T qx = (T(x) - P.cdx) / P.fdx;
+  const T qy = (T(y) - P.cdy) / P.fdy;
+  T nrm = t_sqrt(qx * qx + qy * qy + T(1));
+  nrm = nrm > T(5.43e-20) ? nrm : T(5.43e-20);
+  const T vx = qx / nrm, vy = qy / nrm, vz = T(1) / nrm;
+  const T ex = P.M[0] * vx + P.M[1] * vy + P.M[2] * vz + P.d[0];
+  const T ey = P.M[3] * vx + P.M[4] * vy + P.M[5] * vz + P.d[1];
+  const T ez = P.M[6] * vx + P.M[7] * vy + P.M[8] * vz + P.d[2];
+  if (ez < T(0)) {
+    wx = -1.0f;
+    wy = -1.0f;
+    return;
+  }
+  const T r = t_sqrt(ex * ex + ey * ey);
+  const T eps = T(2.938735877055719e-39);  // 2^-128
+  const T s = t_atan2(r, ez) / (r > eps ? r : eps);
+  const T px = ex * s, py = ey * s;
+  const T pi2 = T(9.869604401089358);
+  T r2 = px * px + py * py;
+  r2 = r2 > pi2 ? pi2 : r2;
+  const T r4 = r2 * r2, r6 = r2 * r4, r8 = r4 * r4, r10 = r4 * r6, r12 = r6 * r6;
+  const T radial = T(1) + P.k1 * r2 + P.k2 * r4 + P.k3 * r6 + P.k4 * r8 + P.k5 * r10 + P.k6 * r12;
+  const T ux = px * radial, uy = py * radial;
+  const T x2 = ux * ux, y2 = uy * uy, xy = ux * uy, rr = x2 + y2;
+  const T dx = ux + (T(2) * P.p2 * xy + P.p1 * (rr + T(2) * x2));
+  const T dy = uy + (T(2) * P.p1 * xy + P.p2 * (rr + T(2) * y2));
+  wx = (float)(dx * P.fsx + P.csx);
+  wy = (float)(dy * P.fsy + P.csy);
+}
+
+// cv2.remap(INTER_LINEAR, BORDER_CONSTANT=0) on uint8: 1/32-px coordinates, 15-bit weights.
+__device__ __forceinline__ int remap_fixed_u8(const uint8_t* __restrict__ img, int64_t row_stride, int W, int H,
+                                              float wx, float wy) {
+  const int sx = __float2int_rn(wx * 32.0f);
+  const int sy = __float2int_rn(wy * 32.0f);
+  const int ix = min(max(sx >> 5, -32768), 32767);
+  const int iy = min(max(sy >> 5, -32768), 32767);
+  const int fx = sx & 31, fy = sy & 31;
+  const bool x0 = (unsigned)ix < (unsigned)W, x1 = (unsigned)(ix + 1) < (unsigned)W;
+  const bool y0 = (unsigned)iy < (unsigned)H, y1 = (unsigned)(iy + 1) < (unsigned)H;
+  const uint8_t* r0 = img + (int64_t)iy * row_stride + ix;
+  const uint8_t* r1 = r0 + row_stride;
+  const int t00 = (y0 && x0) ? __ldg(r0) : 0;
+  const int t01 = (y0 && x1) ? __ldg(r0 + 1) : 0;
+  const int t10 = (y1 && x0) ? __ldg(r1) : 0;
+  const int t11 = (y1 && x1) ? __ldg(r1 + 1) : 0;
+  const int acc = ((32 - fy) * (32 - fx) * t00 + (32 - fy) * fx * t01 + fy * (32 - fx) * t10 + fy * fx * t11) * 32;
+  return (acc + 16384) >> 15;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+crop_resample_kernel(const uint8_t* __restrict__ src, int64_t frame_stride, int64_t view_stride, int64_t row_stride,
+                     const AtCropParams* __restrict__ params, int dst_w, int dst_h, void* __restrict__ out,
+                     int out_dtype) {
+  __shared__ MapParams<T> P;
+  __shared__ int s_meta[4];
+  const int crop = blockIdx.x;
+  const AtCropParams& g = params[crop];
+  if (threadIdx.x < 9) P.M[threadIdx.x] = (T)g.M[threadIdx.x];
+  if (threadIdx.x < 3) P.d[threadIdx.x] = (T)g.d[threadIdx.x];
+  if (threadIdx.x == 32) {
+    P.fdx = (T)g.f_dst[0]; P.fdy = (T)g.f_dst[1]; P.cdx = (T)g.c_dst[0]; P.cdy = (T)g.c_dst[1];
+    P.fsx = (T)g.f_src[0]; P.fsy = (T)g.f_src[1]; P.csx = (T)g.c_src[0]; P.csy = (T)g.c_src[1];
+    P.k1 = (T)g.k[0]; P.k2 = (T)g.k[1]; P.k3 = (T)g.k[2]; P.k4 = (T)g.k[3];
+    P.p1 = (T)g.k[4]; P.p2 = (T)g.k[5]; P.k5 = (T)g.k[6]; P.k6 = (T)g.k[7];
+    s_meta[0] = g.frame; s_meta[1] = g.view; s_meta[2] = g.src_w; s_meta[3] = g.src_h;
+  }
+  __syncthreads();
+  const int W = s_meta[2], H = s_meta[3];
+  const uint8_t* img = src + (int64_t)s_meta[0] * frame_stride + (int64_t)s_meta[1] * view_stride;
+  const int npix = dst_w * dst_h;
+  const int per = (npix + kSplit - 1) / kSplit;
+  const int p_begin = blockIdx.y * per;
+  const int p_end = min(npix, p_begin + per);
+  const int64_t obase = (int64_t)crop * npix;
+  for (int p = p_begin + threadIdx.x; p < p_end; p += kThreads) {
+    const int y = p / dst_w, x = p - y * dst_w;
+    float wx, wy;
+    map_pixel<T>(P, x, y, wx, wy);
+    const int v = remap_fixed_u8(img, row_stride, W, H, wx, wy);
+    if (out_dtype == AT_U8) {
+      ((uint8_t*)out)[obase + p] = (uint8_t)v;
+    } else if (out_dtype == AT_F32) {
+      ((float*)out)[obase + p] = __fdiv_rn((float)v, 255.0f);
+    } else {
+      ((__nv_bfloat16*)out)[obase + p] = __float2bfloat16_rn(__fdiv_rn((float)v, 255.0f));
+    }
+  }
+}
+
+// data_transform.py:78-144, float64 map (numpy promotes float32 x int32 -> float64 at :99).
+__global__ void __launch_bounds__(kThreads)
+resample_homography_kernel(const float* __restrict__ images, int H, int W, const float* __restrict__ xfs, int oh,
+                           int ow, float* __restrict__ out, float out_divisor) {
+  const int n = blockIdx.x;
+  __shared__ double m[12];
+  if (threadIdx.x < 12) m[threadIdx.x] = (double)xfs[(int64_t)n * 16 + threadIdx.x];
+  __syncthreads();
+  const float* img = images + (int64_t)n * H * W;
+  const int npix = oh * ow;
+  const int per = (npix + kSplit - 1) / kSplit;
+  const int p_begin = blockIdx.y * per, p_end = min(npix, p_begin + per);
+  for (int p = p_begin + threadIdx.x; p < p_end; p += kThreads) {
+    const int v = p / ow, u = p - v * ow;
+    const double du = u, dv = v;
+    // tensordot order (:99): sum over (u, v, 1) then + t (:101)
+    const double gx = (m[0] * du + m[1] * dv + m[2]) + m[3];
+    const double gy = (m[4] * du + m[5] * dv + m[6]) + m[7];
+    const double gz = (m[8] * du + m[9] * dv + m[10]) + m[11];
+    const double x = gx / gz, y = gy / gz;
+    float res = 0.0f;
+    if (x >= 0.0 && x < (double)(W - 1) && y >= 0.0 && y < (double)(H - 1)) {
+      const int x0 = (int)x, y0 = (int)y, x1 = x0 + 1, y1 = y0 + 1;
+      const double f00 = img[(int64_t)y0 * W + x0], f01 = img[(int64_t)y1 * W + x0];
+      const double f10 = img[(int64_t)y0 * W + x1], f11 = img[(int64_t)y1 * W + x1];
+      const double val = (((f00 * (x1 - x)) * (y1 - y) + (f10 * (x - x0)) * (y1 - y)) + (f01 * (x1 - x)) * (y - y0)) +
+                         (f11 * (x - x0)) * (y - y0);
+      res = (float)(val / (double)((x1 - x0) * (y1 - y0)));
+    }
+    out[(int64_t)n * npix + p] = __fdiv_rn(res, out_divisor);
+  }
+}
+
+}  // namespace
+
+extern "C" int at_crop_resample_fisheye62_u8(const uint8_t* src, int64_t frame_stride, int64_t view_stride,
+                                             int64_t row_stride, const AtCropParams* params, int n_crops,
+                                             int dst_w, int dst_h, void* out, int out_dtype, int map_mode,
+                                             void* stream) {
+  AT_REQUIRE(n_crops >= 0, "at_crop_resample_fisheye62_u8: n_crops < 0");
+  if (n_crops == 0) return AT_OK;
+  AT_REQUIRE(src && params && out, "at_crop_resample_fisheye62_u8: NULL pointer");
+  AT_REQUIRE(dst_w > 0 && dst_h > 0 && dst_w <= 4096 && dst_h <= 4096, "at_crop_resample_fisheye62_u8: bad crop size");
+  AT_REQUIRE(out_dtype == AT_U8 || out_dtype == AT_F32 || out_dtype == AT_BF16,
+             "at_crop_resample_fisheye62_u8: bad out_dtype %d", out_dtype);
+  AT_REQUIRE(map_mode == AT_MAP_FP32 || map_mode == AT_MAP_FP64, "at_crop_resample_fisheye62_u8: bad map_mode %d",
+             map_mode);
+  dim3 grid((unsigned)n_crops, kSplit);
+  if (map_mode == AT_MAP_FP64)
+    crop_resample_kernel<double><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+        src, frame_stride, view_stride, row_stride, params, dst_w, dst_h, out, out_dtype);
+  else
+    crop_resample_kernel<float><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+        src, frame_stride, view_stride, row_stride, params, dst_w, dst_h, out, out_dtype);
+  return at::check_launch("crop_resample_kernel");
+}
+
+extern "C" int at_resample_homography_f32(const float* images, int n, int H, int W, const float* xfs, int oh, int ow,
+                                          float* out, float out_divisor, void* stream) {
+  AT_REQUIRE(n >= 0, "at_resample_homography_f32: n < 0");
+  if (n == 0) return AT_OK;
+  AT_REQUIRE(images && xfs && out, "at_resample_homography_f32: NULL pointer");
+  AT_REQUIRE(H > 1 && W > 1 && oh > 0 && ow > 0, "at_resample_homography_f32: bad image size");
+  AT_REQUIRE(out_divisor != 0.0f, "at_resample_homography_f32: out_divisor is 0");
+  dim3 grid((unsigned)n, kSplit);
+  resample_homography_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(images, H, W, xfs, oh, ow, out, out_divisor);
+  return at::check_launch("resample_homography_kernel");
+}

@@ -1,0 +1,191 @@
+/*
+ * absolutetrack_b200 - C-ABI of the B200 (sm_100a) implementation of UmeTrack's per-frame
+ * multi-view inference hot path (crop resample -> per-view encoder -> FTL/fusion/temporal ->
+ * pose head -> FK/skinning).
+ *
+ * The reference (2InfinityN6eyond/AbsoluteTrack) is 100% Python and has no FFI layer: its
+ * boundary for this path is the Python surface lib.tracker.tracker.HandTracker /
+ * lib.models.umetrack_model.UmeTrackModel / lib.common.hand_skinning.skin_landmarks.  The
+ * host mirror of that surface lives in absolutetrack_b200/lib/ and binds the entry points
+ * below with ctypes (absolutetrack_b200/_cabi.py); INTEGRATION.md shows the stub a reference
+ * maintainer would add.  Each entry point cites the reference code it replaces
+ * (file:line relative to the reference root).
+ *
+ * Conventions: plain pointers and sizes only; every data pointer is a DEVICE pointer owned by
+ * the caller unless marked HOST; every launch goes onto `stream` (a cudaStream_t passed as
+ * void*); functions return 0 or a negative AtStatus, never throw, never allocate device
+ * memory, never synchronise.  at_last_error_string() describes the last failure on the
+ * calling thread.
+ */
+#ifndef ABSOLUTETRACK_B200_H_
+#define ABSOLUTETRACK_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AT_VERSION 100 /* major*10000 + minor*100 + patch */
+
+typedef enum AtStatus {
+  AT_OK = 0,
+  AT_ERR_INVALID_ARGUMENT = -1,
+  AT_ERR_CUDA = -2,
+  AT_ERR_WORKSPACE_TOO_SMALL = -3,
+  AT_ERR_UNSUPPORTED = -4
+} AtStatus;
+
+typedef enum AtDType { AT_U8 = 0, AT_F32 = 1, AT_BF16 = 2 } AtDType;
+typedef enum AtMapMode { AT_MAP_FP32 = 0, AT_MAP_FP64 = 1 } AtMapMode;
+typedef enum AtPrecision { AT_PREC_FP32 = 0, AT_PREC_BF16 = 1 } AtPrecision;
+typedef enum AtHeadMode { AT_HEAD_KNOWN_SKELETON = 0, AT_HEAD_PREDICT_SCALE = 1 } AtHeadMode;
+
+int at_version(void);
+const char* at_last_error_string(void);
+/* 1 when the library was compiled with the tcgen05 encoder (always, for sm_100a builds). */
+int at_has_tcgen05(void);
+
+/* ------------------------------------------------------------------------------------------
+ * (1) Perspective-crop resampler.  Replaces tracker._warp_image (lib/tracker/tracker.py:61-89):
+ * per dst pixel: pinhole unproject (camera.py:320-329,69-75), rotate into the source camera
+ * (camera.py:296-306), arctan projection (camera.py:80-85), Fisheye62 distortion
+ * (camera.py:122-143), window coords (camera.py:308-312), z<0 -> (-1,-1) (tracker.py:78-80),
+ * cast float32, then cv2.remap INTER_LINEAR / BORDER_CONSTANT 0 in OpenCV's fixed point
+ * (tracker.py:87) and optionally the /255 -> float of tracker.py:332.
+ * The host precomposes M = R_src^T R_dst and d = R_src^T (t_dst - t_src) in fp64.
+ * ---------------------------------------------------------------------------------------- */
+typedef struct AtCropParams {
+  int32_t frame;   /* source frame index in the batch */
+  int32_t view;    /* source view (camera) index inside the frame */
+  int32_t src_w;   /* source image width  (636) */
+  int32_t src_h;   /* source image height (480) */
+  double M[9];     /* row-major 3x3: src_eye = M * dst_eye + d */
+  double d[3];
+  double f_dst[2]; /* crop (pinhole) focal lengths */
+  double c_dst[2]; /* crop principal point */
+  double f_src[2]; /* fisheye focal lengths */
+  double c_src[2]; /* fisheye principal point */
+  double k[8];     /* k1 k2 k3 k4 p1 p2 k5 k6 (camera.py:111-118 field order) */
+  double reserved[2];
+} AtCropParams;    /* 256 bytes */
+
+/* src pixel (frame,view,y,x) = src[frame*frame_stride + view*view_stride + y*row_stride + x].
+ * For the recording layout uint8[480,4,636] (video_pose_data.py:123-125): frame_stride =
+ * 480*2544, view_stride = 636, row_stride = 2544.  out: [n_crops, dst_h, dst_w] of out_dtype
+ * (AT_U8: grey levels; AT_F32 / AT_BF16: level/255). */
+int at_crop_resample_fisheye62_u8(const uint8_t* src, int64_t frame_stride, int64_t view_stride,
+                                  int64_t row_stride, const AtCropParams* params, int n_crops,
+                                  int dst_w, int dst_h, void* out, int out_dtype, int map_mode,
+                                  void* stream);
+
+/* The torch_data pinhole->pinhole resampler.  Replaces data_transform._resample_images_batched
+ * (lib/batched_dataset/data_transform.py:78-144): (u,v,1) -> xf[0:3,0:3]*(u,v,1)+xf[0:3,3],
+ * /z, mask 0<=x<W-1 & 0<=y<H-1, float bilinear, 0 outside.  images [n,H,W] f32, xfs [n,4,4] f32
+ * row-major, out [n,oh,ow] f32, divided (IEEE float32 division) by out_divisor: 255 reproduces the
+ * normalisation of data_transform.py:275, 1 leaves grey levels.  The reference's numpy promotes
+ * the map to float64 (float32 matrix x int32 grid, :99); so does the kernel. */
+int at_resample_homography_f32(const float* images, int n, int H, int W, const float* xfs, int oh,
+                               int ow, float* out, float out_divisor, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (4) Hand forward kinematics + landmark skinning.  Replaces hand_skinning.skin_landmarks
+ * (lib/common/hand_skinning.py:189-209: _joint_local_transform :35-53 with pytorch3d
+ * so3_exp_map, _finger_fk :17-32, _hand_skinning_transform :100-127, _get_skinning_weights
+ * :70-97, _lbs :56-67) and the right-hand mirror of perspective_crop.landmarks_from_hand_pose
+ * (lib/tracker/perspective_crop.py:40-51).  float32 throughout, like the reference.
+ * ---------------------------------------------------------------------------------------- */
+typedef struct AtHandModel {
+  const float* joint_rotation_axes;          /* [22,3] or [n,22,3] */
+  const float* joint_rest_positions;         /* [22,3] or [n,22,3] */
+  const float* landmark_rest_positions;      /* [21,3] or [n,21,3] */
+  const float* landmark_rest_bone_weights;   /* [21,K] or [n,21,K] */
+  const int32_t* landmark_rest_bone_indices; /* [21,K] or [n,21,K] */
+  int32_t n_weights;                         /* K (3 in every reference hand model) */
+  int32_t per_sample;                        /* 0: one model shared by all n; 1: one per sample */
+} AtHandModel;
+
+/* joint_angles [n,22], wrist_xforms [n,4,4] row-major, hand_idx [n] or NULL (1 = right hand:
+ * column 0 of the wrist transform is negated first), landmarks out [n,21,3]. */
+int at_fk_skin_f32(const float* joint_angles, const float* wrist_xforms, const int64_t* hand_idx,
+                   const AtHandModel* model, int64_t n, float* landmarks, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (2)+(3) Network.  Replaces UmeTrackModel.regress_pose_use_skeleton / regress_pose_pred_skel_scale
+ * (lib/models/umetrack_model.py:188-242) and everything below them: backbone
+ * (model_utils.py:107-138, backbone_resnet.py:14-158), FTL (model_utils.py:57-104,166-192),
+ * 2-view fusion (feature_extractor.py:61-141), SimpleConvRNN (temporal.py:51-139),
+ * SkeletonEncoder (skeleton_encoder.py:43-53), PoseRegressor + decoders + Procrustes
+ * (regressor.py:76-186, model_utils.py:17-54), wrist->world (umetrack_model.py:77-97).
+ *
+ * Weights: ONE float32 device blob holding every layer with BatchNorm (eval, eps 1e-5) already
+ * folded into the preceding conv/linear.  Layer order and per-layer layout are fixed by
+ * at_model_layer_table(); conv weights are stored [kh][kw][Cin][CoutP] with CoutP = Cout
+ * rounded up to 4 (zero padded), followed by bias [CoutP].  The host packer is
+ * absolutetrack_b200/lib/models/model_loader.py (it consumes the reference's 252-key
+ * state dict unchanged, model_loader.py:84-87).
+ * ---------------------------------------------------------------------------------------- */
+typedef struct AtLayerInfo {
+  char name[48];       /* e.g. "backbone.layer2.0.conv1" */
+  int32_t cin, cout, ksize, stride;
+  int64_t weight_offset; /* float index into the blob */
+  int64_t bias_offset;
+} AtLayerInfo;
+
+/* Fills up to `capacity` entries; returns the number of layers (or a negative AtStatus). */
+int at_model_layer_table(AtLayerInfo* table, int capacity);
+/* Total float count of the blob. */
+int64_t at_model_blob_floats(void);
+/* Prepack the bf16 operand blob used by the tcgen05 encoder from the fp32 blob.
+ * bf16_blob must hold at_model_bf16_blob_bytes() bytes. */
+int64_t at_model_bf16_blob_bytes(void);
+int at_model_prepack_bf16(const float* blob, void* bf16_blob, void* stream);
+
+/* Per-view encoder: crops [c,96,96] (AT_U8 grey levels, or AT_F32 already /255) ->
+ * features [c,6,6,72] float32 (NHWC; the reference's [c,72,6,6] transposed).
+ * workspace must hold at_encoder_workspace_bytes(c, precision) bytes. */
+int64_t at_encoder_workspace_bytes(int c, int precision);
+int at_encoder_forward(const float* blob, const void* bf16_blob, const void* crops, int crop_dtype,
+                       int c, float* features, void* workspace, int64_t workspace_bytes,
+                       int precision, void* stream);
+
+/* Recurrent state of SimpleConvRNN (temporal.py:41-42,105-125), owned by the caller. */
+typedef struct AtTemporalState {
+  float* mem_features;    /* [capacity,6,6,18] NHWC */
+  float* prev_extrinsics; /* [capacity,4,4] */
+  int64_t capacity;
+} AtTemporalState;
+
+typedef struct AtTailInputs {
+  const float* features;       /* [c,6,6,72] from at_encoder_forward */
+  const float* intrinsics;     /* [c,3,3] */
+  const float* extrinsics;     /* [c,4,4] world->crop-eye, metres */
+  const int64_t* sample_range; /* [n,2] (start,end) into the c crops; end-start in {1,2} */
+  const int64_t* memory_idx;   /* [n] */
+  const uint8_t* use_memory;   /* [n] bool */
+  const int64_t* hand_idx;     /* [n] */
+  const float* skel_axes;      /* [1 or n,22,3]  (NULL for AT_HEAD_PREDICT_SCALE) */
+  const float* skel_rest;      /* [1 or n,22,3]  metres */
+  int32_t n;                   /* hand samples */
+  int32_t c;                   /* crops */
+  int32_t n_skel;              /* 1 or n */
+  int32_t head_mode;           /* AtHeadMode */
+} AtTailInputs;
+
+typedef struct AtTailOutputs {
+  float* joint_angles; /* [n,22] */
+  float* wrist_xfs;    /* [n,4,4] wrist->world (metres), right hands mirrored */
+  float* skel_scales;  /* [n] (AT_HEAD_PREDICT_SCALE only, else may be NULL) */
+  float* sigmas;       /* [n,21] */
+  int32_t* status;     /* [1] device flag: set non-zero on a bad sample_range / memory_idx */
+} AtTailOutputs;
+
+int64_t at_tail_workspace_bytes(int n);
+int at_tail_forward(const float* blob, const AtTailInputs* in, AtTemporalState* state,
+                    const AtTailOutputs* out, void* workspace, int64_t workspace_bytes,
+                    void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ABSOLUTETRACK_B200_H_ */

@@ -77,7 +77,10 @@ def state_dict_spec() -> List[Tuple[str, Tuple[int, ...]]]:
 def make_random_state_dict(seed: int = 0) -> Dict[str, torch.Tensor]:
     """Seeded random checkpoint with the reference's key set (the real weights are not
     distributed with the reference: .MISSING_LARGE_BLOBS).  Conv weights use the reference's
-    init N(0, sqrt(2/(k*k*cout))) (backbone_resnet.py:119-122); BN statistics are non-trivial."""
+    init N(0, sqrt(2/(k*k*cout))) (backbone_resnet.py:119-122); BN statistics are non-trivial.
+    The residual-branch BN gains and the output layers are scaled so that activations stay O(1)
+    and the decoded pose is plausible (joint angles ~0.3 rad, wrist ~0.35 m in front of cam0):
+    errors measured on it are then meaningful in mm / degrees."""
     g = torch.Generator().manual_seed(seed)
     sd = {}
     for key, shape in state_dict_spec():
@@ -86,11 +89,29 @@ def make_random_state_dict(seed: int = 0) -> Dict[str, torch.Tensor]:
             sd[key] = torch.tensor(100, dtype=torch.long)
         elif leaf in ("running_var",) or (leaf == "weight" and len(shape) == 1):
             sd[key] = torch.rand(shape, generator=g) + 0.5
+            if leaf == "weight" and (".bn2." in key or ".downsample.1." in key):
+                sd[key] *= 0.5  # keep the residual sums from growing through 12 blocks
         elif leaf in ("running_mean", "bias"):
             sd[key] = torch.randn(shape, generator=g) * 0.1
         else:
             fan = shape[0] * (shape[2] * shape[3] if len(shape) == 4 else 1)
             sd[key] = torch.randn(shape, generator=g) * math.sqrt(2.0 / fan)
+    sd[_BB + ".1.weight"] *= 0.25
+    # rigid 7-point template (regressor.py:19-47) under a fixed plausible wrist pose
+    q = 0.1 / math.sqrt(2.0)
+    tmpl = torch.tensor([[0, 0, 0], [0.1, 0, 0], [0, 0.1, 0], [0, 0, 0.1], [-q, -q, 0], [-q, 0, -q], [0, -q, -q]])
+    ax = torch.tensor([1.0, 2.0, 3.0]) / math.sqrt(14.0) * 0.5
+    K = torch.tensor([[0, -ax[2], ax[1]], [ax[2], 0, -ax[0]], [-ax[1], ax[0], 0]])
+    R0 = torch.matrix_exp(K)
+    pts = (tmpl @ R0.T + torch.tensor([0.05, -0.03, 0.35])).reshape(-1)
+    for h, n_out in (("k", 62), ("u", 63)):
+        base = f"_regressor_{h}._pose_regression_layers.2"
+        sd[base + ".weight"] *= 0.3
+        b = torch.randn(n_out, generator=g) * 0.3
+        b[20:41] = pts + torch.randn(21, generator=g) * 0.005
+        if h == "u":
+            b[41] = 0.05
+        sd[base + ".bias"] = b
     return sd
 
 

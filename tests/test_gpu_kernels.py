@@ -1,0 +1,208 @@
+"""GPU parity tests of the individual kernels, through the C-ABI, against the CPU oracle and the
+committed reference goldens.  Run with `pytest -m gpu` on a B200."""
+import numpy as np
+import pytest
+import torch
+
+import np_oracle as O
+import scenario
+
+pytestmark = pytest.mark.gpu
+
+
+def _hand_model_tuple(d, prefix=""):
+    from absolutetrack_b200.lib.common.hand import HandModel
+
+    g = lambda k: torch.from_numpy(np.asarray(d[prefix + k]))  # noqa: E731
+    z = torch.zeros(1)
+    return HandModel(
+        joint_rotation_axes=g("joint_rotation_axes").float(), joint_rest_positions=g("joint_rest_positions").float(),
+        joint_frame_index=z, joint_parent=z, joint_first_child=z, joint_next_sibling=z,
+        landmark_rest_positions=g("landmark_rest_positions").float(),
+        landmark_rest_bone_weights=g("landmark_rest_bone_weights").float(),
+        landmark_rest_bone_indices=g("landmark_rest_bone_indices"), hand_scale=None,
+        joint_limits=g("joint_limits").float() if prefix + "joint_limits" in d else None,
+    )
+
+
+# ------------------------------------------------------------------ FK + skinning (a11)
+@pytest.mark.parametrize("rec", ["00", "02", "11"])
+def test_fk_matches_reference_golden_keypoints(cuda_lib, gold, rec):
+    """Known-answer test: the reference's own gt_keypoints pickles, tolerance 1e-3 mm."""
+    from absolutetrack_b200.lib.common.hand_skinning import skin_landmarks_cuda
+
+    G = gold["fk_user05"]
+    p = f"r{rec}_"
+    hm = _hand_model_tuple(G, p)
+    ja = torch.from_numpy(G[p + "joint_angles"])            # [T,2,22]
+    wx = torch.from_numpy(G[p + "wrist_transforms"])        # [T,2,4,4] f64
+    T = ja.shape[0]
+    hidx = torch.tensor([0, 1]).expand(T, 2)
+    out = skin_landmarks_cuda(hm, ja, wx, hand_idx=hidx).cpu().numpy()  # [T,2,21,3]
+    valid = G[p + "valid"]                                   # [2,T]
+    gt = G[p + "gt_keypoints"]                               # [2,T,21,3]
+    n = 0
+    for h in range(2):
+        d = np.abs(out[:, h][valid[h]] - gt[h][valid[h]])
+        n += int(valid[h].sum())
+        assert d.max() < 1e-3, f"hand {h}: max |dlandmark| = {d.max()} mm"
+    assert n > 800
+
+
+def test_fk_matches_oracle_random_poses_and_per_sample_models(cuda_lib, gold):
+    from absolutetrack_b200.lib.common.hand_skinning import skin_landmarks, skin_landmarks_cuda
+
+    G = gold["geometry"]
+    hm = _hand_model_tuple(G, "hm_")
+    rng = np.random.default_rng(0)
+    for n in (1, 63, 64, 65, 1000):
+        ja = rng.uniform(-1.5, 1.5, (n, 22)).astype(np.float32)
+        wx = np.tile(np.eye(4, dtype=np.float32), (n, 1, 1))
+        wx[:, :3, :3] = O.so3_exp_map_f32(rng.normal(0, 1, (n, 3)).astype(np.float32))
+        wx[:, :3, 3] = rng.normal(0, 300, (n, 3))
+        hidx = rng.integers(0, 2, n)
+        ref = O.landmarks_from_hand_pose(scenario.hand_model(), ja, wx, hidx)
+        out = skin_landmarks_cuda(hm, torch.from_numpy(ja), torch.from_numpy(wx), hand_idx=torch.from_numpy(hidx))
+        assert np.abs(out.cpu().numpy() - ref).max() < 1e-3
+    # per-sample (batched) hand models with leading dims [bs, seq] (run_inference_torch_data.py:123-130)
+    bs, seq = 3, 5
+    scale = torch.linspace(0.8, 1.2, bs * seq).reshape(bs, seq, 1, 1)
+    from absolutetrack_b200.lib.common.hand import HandModel
+
+    hmb = hm._replace(
+        joint_rotation_axes=hm.joint_rotation_axes.expand(bs, seq, 22, 3).contiguous(),
+        joint_rest_positions=hm.joint_rest_positions * scale,
+        landmark_rest_positions=hm.landmark_rest_positions * scale,
+        landmark_rest_bone_weights=hm.landmark_rest_bone_weights.expand(bs, seq, 21, 3).contiguous(),
+        landmark_rest_bone_indices=hm.landmark_rest_bone_indices.expand(bs, seq, 21, 3).contiguous(),
+    )
+    ja = torch.from_numpy(rng.uniform(-1, 1, (bs, seq, 22)).astype(np.float32))
+    wx = torch.eye(4).expand(bs, seq, 4, 4).contiguous()
+    out = skin_landmarks(hmb, ja, wx)
+    assert out.shape == (bs, seq, 21, 3) and out.device.type == "cpu"
+    md = {k: getattr(hmb, k).reshape((bs * seq,) + tuple(getattr(hmb, k).shape[2:])).numpy() for k in
+          ("joint_rotation_axes", "joint_rest_positions", "landmark_rest_positions", "landmark_rest_bone_weights",
+           "landmark_rest_bone_indices")}
+    ref = O.skin_landmarks(md, ja.reshape(-1, 22).numpy(), wx.reshape(-1, 4, 4).numpy())
+    assert np.abs(out.reshape(-1, 21, 3).numpy() - ref).max() < 1e-3
+    # scalar leading dims () as in perspective_crop.py:27-37
+    one = skin_landmarks(hm, ja[0, 0], wx[0, 0])
+    assert one.shape == (21, 3)
+
+
+def test_fk_empty_batch(cuda_lib, gold):
+    from absolutetrack_b200.lib.common.hand_skinning import skin_landmarks_cuda
+
+    hm = _hand_model_tuple(gold["geometry"], "hm_")
+    out = skin_landmarks_cuda(hm, torch.zeros(0, 22), torch.zeros(0, 4, 4))
+    assert out.shape == (0, 21, 3)
+
+
+# ------------------------------------------------------------------ crop resampler (a1)
+def _crop_records(meta):
+    from absolutetrack_b200.lib.common import camera as C
+
+    G = scenario.geometry()
+    recs = []
+    for (k, h, s, kind, seed) in meta:
+        cam = int(G["crop_cam"][k, h, s])
+        src = C.Fisheye62CameraModel(636, 480, G["cam_f"][cam], G["cam_c"][cam], G["cam_coeffs"][cam], G["camera_to_world"][k, cam])
+        dst = C.PinholePlaneCameraModel(96, 96, G["crop_f"][k, h, s], G["crop_c"][k, h, s], [], G["crop_c2w"][k, h, s])
+        recs.append(C.crop_kernel_params(src, dst))
+    return recs
+
+
+def _run_crops(meta, map_mode, out_dtype=torch.uint8):
+    from absolutetrack_b200.lib.tracker.tracker import crop_resample_cuda, pack_crop_params
+
+    imgs = np.stack([scenario.synth_image("noise" if kind == 0 else "smooth", seed) for (_, _, _, kind, seed) in meta])
+    recs = [(i, 0, r) for i, r in enumerate(_crop_records(meta))]
+    params = torch.from_numpy(pack_crop_params(recs)).cuda()
+    src = torch.from_numpy(imgs).cuda()
+    out = crop_resample_cuda(src, 480 * 636, 0, 636, params, (96, 96), out_dtype, map_mode)
+    return (out.float() if out_dtype == torch.bfloat16 else out).cpu().numpy()
+
+
+def test_crop_fp64_map_is_bit_exact_vs_reference_golden(cuda_lib, gold):
+    """tests/golden/warp.npz holds the reference tracker._warp_image (numpy fp64 + cv2.remap)
+    outputs; the fp64-map mode must reproduce every pixel."""
+    W = gold["warp"]
+    out = _run_crops(W["meta"], "fp64")
+    mism = int((out != W["crops"]).sum())
+    assert mism == 0, f"{mism} of {out.size} pixels differ"
+
+
+def test_crop_fp32_map_within_one_grey_level_on_smooth_images(cuda_lib, gold):
+    W = gold["warp"]
+    out = _run_crops(W["meta"], "fp32").astype(np.int32)
+    ref = W["crops"].astype(np.int32)
+    smooth = W["meta"][:, 3] == 1
+    d = np.abs(out - ref)
+    assert d[smooth].max() <= 1                      # north_star: crops within 1/255 per pixel
+    assert (d[~smooth] > 1).mean() < 2e-3             # noise images: rare 1/32-px bin flips only
+
+
+def test_crop_float_output_is_level_over_255(cuda_lib, gold):
+    W = gold["warp"]
+    meta = W["meta"][:6]
+    f = _run_crops(meta, "fp64", torch.float32)
+    assert np.array_equal(f, W["crops"][:6].astype(np.float32) / 255.0)
+    b = _run_crops(meta, "fp64", torch.bfloat16)
+    assert np.array_equal(b, torch.from_numpy(f).bfloat16().float().numpy())
+
+
+def test_crop_edge_cases(cuda_lib):
+    """Source behind the camera (z<0 -> (-1,-1) -> 0), fully outside, strided multi-view source."""
+    from absolutetrack_b200.lib.common import camera as C
+    from absolutetrack_b200.lib.tracker.tracker import _warp_image, crop_resample_cuda, pack_crop_params
+
+    G = scenario.geometry()
+    k, h, s = 5, 0, 0
+    cam = int(G["crop_cam"][k, h, s])
+    src = C.Fisheye62CameraModel(636, 480, G["cam_f"][cam], G["cam_c"][cam], G["cam_coeffs"][cam], G["camera_to_world"][k, cam])
+    c2w = G["crop_c2w"][k, h, s].copy()
+    back = c2w.copy()
+    back[:3, :3] = c2w[:3, :3] @ np.diag([1.0, -1.0, -1.0])  # look the other way
+    dst_back = C.PinholePlaneCameraModel(96, 96, G["crop_f"][k, h, s], G["crop_c"][k, h, s], [], back)
+    img = scenario.synth_image("noise", 3)
+    sd = lambda cam_: dict(f=cam_.f, c=cam_.c, c2w=cam_.camera_to_world_xf, coeffs=tuple(src.distort), width=cam_.width, height=cam_.height)  # noqa: E731
+    out = _warp_image(src, dst_back, img)
+    assert np.array_equal(out, O.warp_image(sd(src), sd(dst_back), img))
+    # wide crop (small focal) reaching beyond the source image borders
+    dst_wide = C.PinholePlaneCameraModel(96, 96, (20.0, 20.0), G["crop_c"][k, h, s], [], c2w)
+    out = _warp_image(src, dst_wide, img)
+    assert np.array_equal(out, O.warp_image(sd(src), sd(dst_wide), img))
+    # the recording layout [480, 4, 636] addressed with strides, 2 frames x 4 views
+    frames = np.stack([scenario.synth_frame("noise", 11), scenario.synth_frame("smooth", 12)])
+    dst = C.PinholePlaneCameraModel(96, 96, G["crop_f"][k, h, s], G["crop_c"][k, h, s], [], c2w)
+    recs = [(f, v, C.crop_kernel_params(src, dst)) for f in range(2) for v in range(4)]
+    out = crop_resample_cuda(torch.from_numpy(frames).cuda(), 480 * 2544, 636, 2544,
+                             torch.from_numpy(pack_crop_params(recs)).cuda(), (96, 96), torch.uint8, "fp64").cpu().numpy()
+    for i, (f, v, _) in enumerate(recs):
+        assert np.array_equal(out[i], O.warp_image(sd(src), sd(dst), np.ascontiguousarray(frames[f, :, v, :])))
+    # empty batch
+    e = crop_resample_cuda(torch.from_numpy(frames).cuda(), 0, 0, 636, torch.zeros((0, 256), dtype=torch.uint8).cuda())
+    assert e.shape == (0, 96, 96)
+
+
+# ------------------------------------------------------------------ homography resampler (a12)
+def test_homography_resampler_matches_oracle(cuda_lib):
+    from absolutetrack_b200 import _cabi
+
+    rng = np.random.default_rng(1)
+    n, H, W = 5, 120, 160
+    imgs = (rng.random((n, H, W), dtype=np.float32) * 255).astype(np.float32)
+    xf = np.tile(np.eye(4, dtype=np.float32), (n, 1, 1))
+    xf[:, 0, 0] = rng.uniform(0.8, 1.6, n); xf[:, 1, 1] = rng.uniform(0.8, 1.6, n)
+    xf[:, 0, 1] = rng.normal(0, 0.05, n); xf[:, 1, 0] = rng.normal(0, 0.05, n)
+    xf[:, 0, 2] = rng.normal(0, 20, n); xf[:, 1, 2] = rng.normal(0, 20, n)
+    xf[:, 2, 0] = rng.normal(0, 1e-4, n); xf[:, 0, 3] = rng.normal(0, 2, n)
+    xf[0] = np.eye(4)  # identity: integer grid, exercises the x == W-1 exclusion
+    ref = O.resample_homography(imgs, xf, (96, 96)) / np.float32(255)
+    d_img, d_xf = torch.from_numpy(imgs).cuda(), torch.from_numpy(xf).cuda()
+    out = torch.empty(n, 96, 96, device="cuda")
+    rc = cuda_lib.at_resample_homography_f32(d_img.data_ptr(), n, H, W, d_xf.data_ptr(), 96, 96, out.data_ptr(), 255.0,
+                                             _cabi.stream_ptr())
+    _cabi.check(rc)
+    assert np.abs(out.cpu().numpy() - ref).max() <= 1e-6
+    assert (ref != 0).mean() > 0.5

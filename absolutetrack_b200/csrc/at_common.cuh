@@ -10,8 +10,10 @@
 namespace at {
 
 void set_error(const char* fmt, ...);
+void count_launch();  // every kernel launch of this library is counted (at_launch_count)
 
 inline int check_launch(const char* what) {
+  count_launch();
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("%s: %s", what, cudaGetErrorString(e));

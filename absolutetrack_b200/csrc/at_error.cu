@@ -4,8 +4,11 @@
 
 #include "at_common.cuh"
 
+#include <atomic>
+
 namespace {
 thread_local char g_err[512] = "";
+std::atomic<long long> g_launches{0};
 }
 
 namespace at {
@@ -15,8 +18,10 @@ void set_error(const char* fmt, ...) {
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
 }
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 }  // namespace at
 
+extern "C" int64_t at_launch_count(void) { return (int64_t)g_launches.load(); }
 extern "C" int at_version(void) { return AT_VERSION; }
 extern "C" const char* at_last_error_string(void) { return g_err; }
 extern "C" int at_has_tcgen05(void) {

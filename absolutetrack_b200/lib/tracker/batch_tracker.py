@@ -1,0 +1,120 @@
+"""Batched frame-stream tracking: the throughput-shaped entry of the hot path.
+
+The reference tracks one frame per call (HandTracker.track_frame, lib/tracker/tracker.py:262-289,
+called from the per-frame loop of run_eval_known_skeleton.py:68-90).  Independent sequences
+(recordings) have no data dependence on each other, so this class advances S independent
+sequences by one frame per call: S multi-view frames -> 4S crops -> 2S poses -> 2S x 21
+landmarks, with the SimpleConvRNN memory slot of (sequence s, hand h) at s*2+h.  It is the same
+arithmetic as S HandTracker instances stepping in lock-step (tracker._make_inputs :315-368,
+UmeTrackModel.regress_pose_use_skeleton umetrack_model.py:188-219, _gen_tracking_result
+:370-412 and perspective_crop.landmarks_from_hand_pose :40-51), launched once per stage.
+
+Everything runs in libabsolutetrack_b200.so; there is no CPU path.
+"""
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+import torch
+
+from .. import _cabi
+from ..common.hand import HandModel
+from ..common.hand_skinning import skin_landmarks_cuda
+from ..models.umetrack_model import InputFrameData, InputFrameDesc, InputSkeletonData
+from .tracker import crop_resample_cuda
+
+M_TO_MM = 1000.0
+
+
+@dataclass
+class FrameBatch:
+    """One time step of S sequences.  Tensors may live on the host (pinned for async copies)
+    or on the device; `to(device)` moves all of them.
+
+    frames       uint8 [S, H, V, W]  multi-view frames in the recording layout
+                 (video_pose_data.py:123-125: a [H, V*W] video frame viewed as [H, V, W])
+    crop_params  uint8 [c, 256]      packed AtCropParams (frame = sequence slot, view = camera)
+    intrinsics   f32 [c,3,3], extrinsics f32 [c,4,4] (world->crop eye, metres)
+    sample_range i64 [n,2], hand_idx i64 [n], memory_idx i64 [n], use_memory bool [n]
+    """
+
+    frames: torch.Tensor
+    crop_params: torch.Tensor
+    intrinsics: torch.Tensor
+    extrinsics: torch.Tensor
+    sample_range: torch.Tensor
+    hand_idx: torch.Tensor
+    memory_idx: torch.Tensor
+    use_memory: torch.Tensor
+
+    def to(self, device, non_blocking=True) -> "FrameBatch":
+        return FrameBatch(*[getattr(self, f).to(device, non_blocking=non_blocking) for f in self.__dataclass_fields__])
+
+    def pin(self) -> "FrameBatch":
+        return FrameBatch(*[getattr(self, f).pin_memory() for f in self.__dataclass_fields__])
+
+    def nbytes(self) -> int:
+        return sum(getattr(self, f).numel() * getattr(self, f).element_size() for f in self.__dataclass_fields__)
+
+
+@dataclass
+class BatchResult:
+    joint_angles: torch.Tensor   # [n,22]
+    wrist_xforms: torch.Tensor   # [n,4,4] wrist->world, millimetres, right hands mirrored
+    landmarks: torch.Tensor      # [n,21,3] world, millimetres
+
+
+class BatchedHandTracker:
+    def __init__(self, model, hand_model_mm: HandModel, max_slots: int, map_mode: str = "fp32",
+                 crop_dtype: torch.dtype = torch.uint8) -> None:
+        if not torch.cuda.is_available():
+            raise _cabi.AbsoluteTrackError("BatchedHandTracker needs a CUDA device (no CPU fallback)")
+        self._device = torch.device("cuda", torch.cuda.current_device())
+        self._model = model.to(self._device)
+        self._model.memory_capacity_hint = int(max_slots)
+        self._model.strict = False  # status flag is read by check() instead of once per call
+        self._map_mode = map_mode
+        self._crop_dtype = crop_dtype
+        f32 = dict(device=self._device, dtype=torch.float32)
+        self._hm = hand_model_mm
+        self._skel = InputSkeletonData(
+            joint_rotation_axes=hand_model_mm.joint_rotation_axes.to(**f32).contiguous(),
+            joint_rest_positions=(hand_model_mm.joint_rest_positions.to(**f32) * 0.001).contiguous(),
+        )
+        self._hm_dev = HandModel(*[
+            (v.to(self._device) if isinstance(v, torch.Tensor) else v) for v in hand_model_mm
+        ])
+
+    @property
+    def device(self):
+        return self._device
+
+    def step_device(self, b: FrameBatch) -> BatchResult:
+        """All inputs already on the device."""
+        S, H, V, W = b.frames.shape
+        crops = crop_resample_cuda(
+            b.frames, H * V * W, W, V * W, b.crop_params, (96, 96), self._crop_dtype, self._map_mode
+        )
+        out = self._model.regress_pose_use_skeleton(
+            InputFrameData(crops, b.intrinsics, b.extrinsics),
+            InputFrameDesc(b.sample_range, b.memory_idx, b.use_memory, b.hand_idx),
+            self._skel,
+        )
+        wrist_mm = out.wrist_xfs.clone()
+        wrist_mm[:, :3, 3] *= M_TO_MM
+        # the model already mirrored right hands (umetrack_model.py:88-89); landmarks_from_hand_pose
+        # mirrors them back before FK (perspective_crop.py:46-48) -> hand_idx does that in-kernel
+        lm = skin_landmarks_cuda(self._hm_dev, out.joint_angles, wrist_mm, hand_idx=b.hand_idx)
+        return BatchResult(out.joint_angles, wrist_mm, lm)
+
+    def step(self, host_batch: FrameBatch, out_host: Optional[dict] = None) -> dict:
+        """Host buffers in, host buffers out (H2D + kernels + D2H on the current stream)."""
+        r = self.step_device(host_batch.to(self._device))
+        if out_host is None:
+            out_host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True) for k, v in vars(r).items()}
+        for k, v in vars(r).items():
+            out_host[k].copy_(v, non_blocking=True)
+        return out_host
+
+    def check(self) -> None:
+        self._model.check_status()

@@ -1,0 +1,374 @@
+#!/usr/bin/env python
+"""bench.py - hand-frames/s of the UmeTrack multi-view inference hot path on B200.
+
+Contract: `python bench.py --gpus N --steps K --warmup W` (for N>1 launched under torchrun, one
+rank per GPU).  One "step" advances S independent synthetic 4-view sequences by one frame:
+crop resample (4S crops) -> encoder -> FTL/fusion/temporal/head (2S hand samples) -> FK/skinning
+(2S x 21 landmarks).  Prints ONE JSON line on rank 0.
+
+  value     : hand-frames/s, inputs resident in HBM, CUDA-event timed, max over ranks
+  e2e       : same metric through BatchedHandTracker.step with pinned HOST buffers (H2D of the
+              frames + parameters and D2H of poses + landmarks inside the timed region)
+  roofline  : the per-view encoder (the dominant stage), FLOPs / CUDA-event time vs the measured
+              bf16 tensor peak of MEASURED_PEAKS.json
+  cpu_baseline : the oracle port of the reference's CPU path (numpy fp64 warp + fixed-point
+              remap, torch-CPU fp32 network, numpy FK) on a bounded sample, rank 0, N=1 only
+  --impl reference : that CPU arm alone, as its own JSON line.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "hand_frames_per_sec"
+UNIT = "hand-frames/s"
+ENCODER_FLOP_PER_CROP = 969_228_288           # SURVEY.md 8(d), counted on the reference modules
+TAIL_FLOP_PER_HAND = 19_150_000
+FK_BYTES_PER_HAND = 404                        # shared hand model
+CROP_SRC_BYTES = 32_160                        # mean source bounding box per crop
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sust=d["bf16_tflops_sustained"], src="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, src="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.index)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def mark(self):
+        return time.time()
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                pass
+
+    def summary(self, windows):
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ts, line in self.rows:
+            if not any(a - 0.05 <= ts <= b + 0.15 for a, b in windows):
+                continue
+            p = [x.strip() for x in line.split(",")]
+            try:
+                sm.append(float(p[0])); mx = max(mx, float(p[1]))
+            except (ValueError, IndexError):
+                continue
+            for nm, v in zip(names, p[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------ CPU arm
+def cpu_reference_arm(n_frames, threads, warm=1):
+    """Oracle port of the reference CPU path, frame by frame like run_eval_known_skeleton.py:68-90:
+    4x _warp_image + regress_pose_use_skeleton (torch CPU fp32) + 2x landmarks_from_hand_pose.
+    Returns (hand_frames, seconds)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import numpy as np
+    import torch
+    import model_oracle as MO
+    import np_oracle as O
+    import scenario
+    from absolutetrack_b200.lib.models.model_loader import make_random_state_dict
+
+    torch.set_num_threads(threads)
+    sd = make_random_state_dict(0)
+    hm = scenario.hand_model()
+    skel = (torch.from_numpy(hm["joint_rotation_axes"]).float(), torch.from_numpy(hm["joint_rest_positions"] * 0.001).float())
+    st = MO.TemporalState()
+    K = scenario.geometry()["crop_cam"].shape[0]
+    frames = [scenario.synth_frame("noise", i) for i in range(4)]
+    hands = 0
+    valid = np.zeros(2, bool)
+    t0 = None
+    for t in range(warm + n_frames):
+        if t == warm:
+            t0, hands = time.perf_counter(), 0
+        k = t % K
+        fi = scenario.frame_inputs(k)
+        if not fi["crops"]:
+            continue
+        frame = frames[t % 4]
+        imgs = [O.warp_image(scenario.src_camera(k, cam), scenario.dst_camera(k, h, s), np.ascontiguousarray(frame[:, cam, :]))
+                for (h, s, cam) in fi["crops"]]
+        images = torch.from_numpy(np.stack(imgs).astype(np.float32) / 255.0)
+        use_mem = torch.from_numpy(valid[fi["hand_idx"]].copy())
+        out = MO.forward(sd, st, images, torch.from_numpy(fi["intrinsics"]), torch.from_numpy(fi["extrinsics"]),
+                         torch.from_numpy(fi["sample_range"]), torch.from_numpy(fi["hand_idx"]), use_mem,
+                         torch.from_numpy(fi["hand_idx"]), skel)
+        valid[:] = False
+        valid[fi["hand_idx"]] = True
+        for i, h in enumerate(fi["hand_idx"]):
+            w = out["wrist_xfs"][i].numpy().copy()
+            w[:3, 3] *= 1000.0
+            O.landmarks_from_hand_pose(hm, out["joint_angles"][i].numpy(), w, int(h))
+        hands += len(fi["hand_idx"])
+    return hands, time.perf_counter() - t0
+
+
+def run_reference_impl(args, rank):
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    per_step = args.ref_frames
+    warm_h, warm_s = cpu_reference_arm(max(2, per_step // 8), cores)
+    total_h, total_s = 0, 0.0
+    for _ in range(max(1, args.steps)):
+        h, s = cpu_reference_arm(per_step, cores, warm=0)
+        total_h += h; total_s += s
+    v = total_h / total_s
+    sample = f"{per_step} consecutive 2-hand frames per step (4 crops each), oracle port, torch threads={cores}"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * total_s / max(1, args.steps), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "frames_per_step": per_step},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+WORKLOAD = ("synthetic 4-view fisheye frame stream (4x 636x480 u8 per frame, recording_00 geometry), both hands, "
+            "known-skeleton head (BASELINE.json configs[3])")
+
+
+# ------------------------------------------------------------------------------------ GPU arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--frames", type=int, default=256, help="sequences (= frames) per step per GPU")
+    ap.add_argument("--precision", default=os.environ.get("AT_BENCH_PRECISION", "fp32"), choices=["fp32", "bf16"])
+    ap.add_argument("--map-mode", default="fp32", choices=["fp32", "fp64"])
+    ap.add_argument("--ref-frames", type=int, default=24, help="frames per step of the CPU reference arm")
+    ap.add_argument("--cpu-frames", type=int, default=96, help="bounded CPU-baseline sample (frames)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference_impl(args, rank)
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback on the product arm)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    from absolutetrack_b200 import _cabi, synthetic
+    from absolutetrack_b200.lib.common.hand_skinning import skin_landmarks_cuda
+    from absolutetrack_b200.lib.models.model_loader import make_random_state_dict, model_from_state_dict
+    from absolutetrack_b200.lib.tracker.batch_tracker import BatchedHandTracker
+    from absolutetrack_b200.lib.tracker.tracker import crop_resample_cuda
+
+    lib = _cabi.lib()
+    peaks = load_peaks()
+    S = args.frames
+    model = model_from_state_dict(make_random_state_dict(0), precision=args.precision)
+    hm = synthetic.hand_model()
+    tracker = BatchedHandTracker(model, hm, max_slots=2 * S, map_mode=args.map_mode)
+
+    # sequences are sharded by rank (r::world, the reference Sampler's rule, async_dataset.py:558-559)
+    seq_ids = np.arange(S) * world + rank
+    NB = 2  # alternating input batches, each larger than L2 (S*1.22 MB)
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)
+    host, devb, gts = [], [], []
+    for i in range(NB):
+        frames_dev = torch.randint(0, 256, (S, synthetic.H, synthetic.V, synthetic.W), dtype=torch.uint8, device=dev, generator=g)
+        hb = synthetic.make_batch(seq_ids, i, frames=frames_dev.cpu(), first_step=False).pin()
+        host.append(hb)
+        db = hb.to(dev)
+        db.frames = frames_dev
+        devb.append(db)
+        ja, wx = synthetic.gt_poses(seq_ids, i, hb)
+        gts.append(skin_landmarks_cuda(tracker._hm_dev, ja.to(dev), wx.to(dev)))
+    n = int(host[0].sample_range.shape[0])
+    c = int(host[0].crop_params.shape[0])
+    in_bytes = S * synthetic.H * synthetic.V * synthetic.W
+    flush_note = f"inputs {in_bytes / 1e6:.0f} MB per step > 126 MB L2, {NB} alternating batches"
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    windows = []
+
+    def timed(fn, steps, warmup):
+        for i in range(warmup):
+            fn(i)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = lib.at_launch_count()
+        w0 = time.time()
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        e1.record()
+        barrier()
+        windows.append((w0, time.time()))
+        ms = e0.elapsed_time(e1)
+        launches = lib.at_launch_count() - l0
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, launches
+
+    # ---- whole pipeline, device-resident inputs
+    err_sum = torch.zeros(2, dtype=torch.float64, device=dev)
+
+    def step_dev(i):
+        r = tracker.step_device(devb[i % NB])
+        d = (r.landmarks - gts[i % NB]).norm(dim=-1).mean(dim=-1)  # per-hand MPJPE vs GT (mm)
+        err_sum[0] += d.sum()
+        err_sum[1] += d.numel()
+
+    ms_total, launches = timed(step_dev, args.steps, args.warmup)
+    tracker.check()
+    ms_step = ms_total / args.steps
+    value = world * n / (ms_step * 1e-3)
+
+    # ---- end to end from pinned host buffers
+    out_host = [None]
+
+    def step_host(i):
+        out_host[0] = tracker.step(host[i % NB], out_host[0])
+
+    ms_e2e, _ = timed(step_host, args.steps, args.warmup)
+    e2e_value = world * n / (ms_e2e / args.steps * 1e-3)
+    h2d = host[0].nbytes()
+    d2h = sum(v.numel() * v.element_size() for v in out_host[0].values())
+
+    # ---- per-stage timings (device resident) for the roofline
+    b0 = devb[0]
+    crops = [None]
+    feats = [None]
+
+    def st_crop(i):
+        b = devb[i % NB]
+        crops[0] = crop_resample_cuda(
+            b.frames, synthetic.H * synthetic.V * synthetic.W, synthetic.W, synthetic.V * synthetic.W, b.crop_params,
+            (96, 96), torch.uint8, args.map_mode)
+
+    def st_enc(i):
+        feats[0] = model.encode(crops[0])
+
+    ja_d = torch.zeros(n, 22, device=dev)
+    wx_d = torch.eye(4, device=dev).repeat(n, 1, 1)
+
+    def st_fk(i):
+        skin_landmarks_cuda(tracker._hm_dev, ja_d, wx_d, hand_idx=b0.hand_idx)
+
+    ms_crop, _ = timed(st_crop, args.steps, 3)
+    ms_enc, enc_launches = timed(st_enc, args.steps, 3)
+    ms_fk, _ = timed(st_fk, args.steps, 3)
+    ms_crop /= args.steps; ms_enc /= args.steps; ms_fk /= args.steps
+    ms_tail = max(ms_step - ms_crop - ms_enc - ms_fk, 0.0)
+
+    enc_tflops = ENCODER_FLOP_PER_CROP * c / (ms_enc * 1e-3) / 1e12
+    tf_peak = peaks["tf_sust"]
+    crop_bytes = c * (CROP_SRC_BYTES + 96 * 96 * 1 + 256)
+    crop_gbs = crop_bytes / (ms_crop * 1e-3) / 1e9
+    fk_gbs = n * FK_BYTES_PER_HAND / (ms_fk * 1e-3) / 1e9
+
+    if world > 1:
+        dist.all_reduce(err_sum)  # the only collective of the path: metric sums over shards
+    mpjpe = float((err_sum[0] / err_sum[1]).item())
+
+    clocks = None
+    if rank == 0:
+        time.sleep(0.15)
+        sampler.stop()
+        clocks = sampler.summary(windows)
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        hnd, sec = cpu_reference_arm(args.cpu_frames, cores)
+        cpu_baseline = {"value": hnd / sec, "unit": UNIT, "cores": cores, "kind": "port",
+                        "sample": f"{args.cpu_frames} consecutive 2-hand frames of the same stream, frame by frame "
+                                  f"(numpy fp64 warp + fixed-point remap, torch-CPU fp32 network with {cores} threads, numpy FK)"}
+
+    if rank == 0:
+        print(json.dumps({
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": args.precision, "data": "synthetic",
+            "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": S, "hand_frames_per_step_per_gpu": n,
+                       "crops_per_step_per_gpu": c, "map_mode": args.map_mode, "l2": flush_note,
+                       "weights": "seeded random state dict (252 keys), BN folded", "sharding": "sequences r::world"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "api": "BatchedHandTracker.step (pinned host buffers)"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "tensor", "kernel": "per-view encoder (all conv launches of at_encoder_forward)",
+                         "achieved": enc_tflops, "peak": tf_peak, "unit": "TFLOP/s", "frac": enc_tflops / tf_peak,
+                         "traffic": None, "peak_source": peaks["src"] + " bf16 sustained",
+                         "launches_per_step": enc_launches // max(1, args.steps)},
+            "stages": {"crop_ms": ms_crop, "encoder_ms": ms_enc, "tail_ms": ms_tail, "fk_ms": ms_fk,
+                       "crop_gbs": crop_gbs, "crop_hbm_frac": crop_gbs / peaks["hbm"],
+                       "fk_gbs": fk_gbs, "fk_hbm_frac": fk_gbs / peaks["hbm"]},
+            "mpjpe_vs_gt_mm_random_weights": mpjpe,
+            "cpu_baseline": cpu_baseline,
+            "clocks": clocks,
+        }))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

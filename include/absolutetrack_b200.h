@@ -43,6 +43,8 @@ typedef enum AtHeadMode { AT_HEAD_KNOWN_SKELETON = 0, AT_HEAD_PREDICT_SCALE = 1 
 
 int at_version(void);
 const char* at_last_error_string(void);
+/* Number of CUDA kernels this library has launched in this process (all threads). */
+int64_t at_launch_count(void);
 /* 1 when the library was compiled with the tcgen05 encoder (always, for sm_100a builds). */
 int at_has_tcgen05(void);
 

@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libabsolutetrack_b200.so")
 
 AT_U8, AT_F32, AT_BF16 = 0, 1, 2
 AT_MAP_FP32, AT_MAP_FP64 = 0, 1
-AT_PREC_FP32, AT_PREC_BF16 = 0, 1
+AT_PREC_FP32, AT_PREC_BF16, AT_PREC_FP16 = 0, 1, 2
 AT_HEAD_KNOWN_SKELETON, AT_HEAD_PREDICT_SCALE = 0, 1
 
 
@@ -108,6 +108,9 @@ SIGNATURES = {
     "at_model_blob_floats": (_I64, []),
     "at_model_bf16_blob_bytes": (_I64, []),
     "at_model_prepack_bf16": (_I, [_VP, _VP, _VP]),
+    "at_model_prepack_tc": (_I, [_VP, _VP, _I, _VP]),
+    "at_debug_conv_tc_workspace_bytes": (_I64, [_I, _I, _I]),
+    "at_debug_conv_tc": (_I, [_VP, _VP, _I, _VP, _I, _I, _I, _VP, _I, _I, _I, _VP, _VP, _I64, _VP]),
     "at_encoder_workspace_bytes": (_I64, [_I, _I]),
     "at_encoder_forward": (_I, [_VP, _VP, _VP, _I, _I, _VP, _VP, _I64, _I, _VP]),
     "at_tail_workspace_bytes": (_I64, [_I]),

@@ -1,17 +1,820 @@
-// tcgen05 / TMEM / TMA bf16 implicit-GEMM encoder (AT_PREC_BF16).  Placeholder until the
-// tensor-core path lands: fails loudly, never falls back.
+// tcgen05 / TMEM / bulk-TMA implicit-GEMM encoder (AT_PREC_BF16, AT_PREC_FP16).
+//
+// Replaces the cuDNN calls behind the reference backbone (model_utils.py:107-138,
+// backbone_resnet.py:14-158).  Design ("shift-GEMM on a padded planar layout"):
+//
+//  * Activations live in HBM as 16-bit NC/8HW8 planes: plane cg holds channels [8cg, 8cg+8) of
+//    every pixel as one 16-byte unit; pixels of the whole crop batch are laid out in ONE padded
+//    linear order  g = img*Hp*Wp + y*Wp + x  with Hp = H+1, Wp = W+1: one zero column and one
+//    zero row per image are shared between neighbours (x = W is the left pad of the next row,
+//    y = H the top pad of the next image), plus zero guards in front of / behind the batch.
+//  * With that layout a 3x3 tap (r,s) of a stride-1 convolution is a pure SHIFT of the pixel
+//    index by (r-1)*Wp + (s-1).  A CTA loads the input pixels [g0 - Wp - 1, g0 + 128 + Wp + 1)
+//    of each channel plane ONCE with 1-D bulk TMA (cp.async.bulk, contiguous in HBM and in
+//    shared memory) and issues all 9 taps as tcgen05.mma instructions whose A descriptors differ
+//    only in their start address (no-swizzle K-major canonical layout: LBO = plane stride,
+//    SBO = 128 B).  No im2col buffer, no re-load per tap, no tensor maps.
+//  * Stride-2 convolutions read a 4-phase (space-to-depth) copy of their input that the
+//    producing layer's epilogue writes directly, so they are shift-GEMMs too.
+//  * GEMM view: M = 128 padded-linear pixels per tile (TMEM lanes), N = Cout (padded to 16),
+//    K = taps * Cin in chunks of <= 64 channels.  Accumulators live in TMEM (fp32), 2-4 stages.
+//    Warp roles: warp 0 weight producer (bulk TMA ring, or resident weights when they fit),
+//    warp 1 single-thread MMA issuer, warp 2 TMEM allocator + activation producer, warps 4-11
+//    two epilogue groups (tcgen05.ld -> +bias +residual, ReLU -> 16-bit pack -> coalesced 16 B
+//    stores, pads written as zeros so the layout invariant is kept without memsets).
+//  * Persistent grid of one CTA per SM (148), tiles round-robin so neighbouring tiles (which
+//    share halo pixels) are in flight together and the halo re-reads hit L2.
+#include <algorithm>
+#include <mutex>
+#include <string.h>
+
 #include "conv.cuh"
+#include "tc_ptx.cuh"
 
 namespace at {
-int64_t encoder_workspace_bytes_bf16(int c) { return (int64_t)c * 0 + 256; }
-int encoder_forward_bf16(const float*, const void*, const void*, int, int, float*, void*, int64_t, cudaStream_t) {
-  set_error("AT_PREC_BF16 encoder is not built into this library");
-  return AT_ERR_UNSUPPORTED;
+namespace tc {
+
+constexpr int kTileM = 128;
+constexpr int kThreads = 384;
+constexpr int kMaxTaps = 9;
+constexpr int kSmemBudget = 220 * 1024;
+
+struct ConvTcParams {
+  const uint4* a_src[4];
+  long long a_plane_px;
+  const uint4* w;
+  const float* bias;
+  const uint4* res;
+  long long res_plane_px;
+  uint4* out;
+  long long out_plane_px;
+  uint4* out_ph[4];
+  long long out_ph_plane_px;
+  float* out_f32;
+  int out_mode, relu, fmt;
+  int n_src, n_taps, n_kchunks, kc;
+  int n, cout;
+  int tap_src[kMaxTaps], tap_shift[kMaxTaps];
+  int min_shift, npix;
+  int H, W, Hp, Wp, Hp2, Wp2;
+  long long n_img, P;
+  int mt;
+  long long n_tiles;
+  int ra, ws, as, w_resident;
+  uint32_t smem_a_off, smem_w_off, smem_bias_off, smem_bar_off;
+  uint32_t a_slot_bytes, a_plane_bytes, w_block_bytes, tmem_cols, acc_cols;
+};
+
+__global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  using namespace ptx;
+  const uint32_t sbase = smem_u32(smem);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t bar0 = sbase + p.smem_bar_off;
+  const uint32_t a_full = bar0, a_empty = a_full + 8 * p.ra;
+  const uint32_t w_full = a_empty + 8 * p.ra, w_empty = w_full + 8 * p.ws;
+  const uint32_t acc_full = w_empty + 8 * p.ws, acc_empty = acc_full + 8 * p.as;
+  const uint32_t tmem_slot = acc_empty + 8 * p.as;
+  float* bias_s = reinterpret_cast<float*>(smem + p.smem_bias_off);
+
+  if (warp == 0 && lane == 0) {
+    for (int i = 0; i < p.ra; ++i) { mbar_init(a_full + 8 * i, 1); mbar_init(a_empty + 8 * i, 1); }
+    for (int i = 0; i < p.ws; ++i) { mbar_init(w_full + 8 * i, 1); mbar_init(w_empty + 8 * i, 1); }
+    for (int i = 0; i < p.as; ++i) { mbar_init(acc_full + 8 * i, 1); mbar_init(acc_empty + 8 * i, 4); }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, p.tmem_cols);
+    tmem_relinquish();
+  }
+  for (int i = threadIdx.x; i < p.n; i += kThreads) bias_s[i] = i < p.cout ? p.bias[i] : 0.f;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem + (tmem_slot - sbase));
+
+  const long long first_tile = blockIdx.x;
+  const int n_my = first_tile < p.n_tiles ? (int)((p.n_tiles - first_tile + gridDim.x - 1) / gridDim.x) : 0;
+  const int nk = p.n_kchunks;
+  const int nblocks = nk * p.n_taps;
+  const int planes_per_chunk = p.kc >> 3;
+
+  if (warp == 0) {
+    if (lane == 0) {  // ---------------- weight producer
+      const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(p.w);
+      if (p.w_resident) {
+        if (n_my > 0)
+          for (int b = 0; b < nblocks; ++b) {
+            mbar_expect_tx(w_full + 8 * b, p.w_block_bytes);
+            bulk_g2s(sbase + p.smem_w_off + b * p.w_block_bytes, wsrc + (size_t)b * p.w_block_bytes, p.w_block_bytes,
+                     w_full + 8 * b);
+          }
+      } else {
+        long long q = 0;
+        for (int it = 0; it < n_my; ++it)
+          for (int b = 0; b < nblocks; ++b, ++q) {
+            const int s = (int)(q % p.ws);
+            mbar_wait(w_empty + 8 * s, (uint32_t)(((q / p.ws) & 1) ^ 1));
+            mbar_expect_tx(w_full + 8 * s, p.w_block_bytes);
+            bulk_g2s(sbase + p.smem_w_off + s * p.w_block_bytes, wsrc + (size_t)b * p.w_block_bytes, p.w_block_bytes,
+                     w_full + 8 * s);
+          }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {  // ---------------- MMA issuer
+      const uint32_t idesc = umma_idesc(kTileM, p.n, p.fmt);
+      const uint32_t b_lbo = (uint32_t)p.n * 16u;
+      long long qa = 0, qw = 0;
+      for (int it = 0; it < n_my; ++it) {
+        const int as_ = it % p.as;
+        mbar_wait(acc_empty + 8 * as_, (uint32_t)(((it / p.as) & 1) ^ 1));
+        tc_fence_after();
+        const uint32_t d_base = tmem_base + as_ * p.acc_cols;
+        for (int kci = 0; kci < nk; ++kci, ++qa) {
+          const int sa = (int)(qa % p.ra);
+          mbar_wait(a_full + 8 * sa, (uint32_t)((qa / p.ra) & 1));
+          tc_fence_after();
+          const uint32_t a_slot = sbase + p.smem_a_off + sa * p.a_slot_bytes;
+          for (int t = 0; t < p.n_taps; ++t) {
+            int sw;
+            if (p.w_resident) {
+              sw = kci * p.n_taps + t;
+              if (it == 0) {
+                mbar_wait(w_full + 8 * sw, 0);
+                tc_fence_after();
+              }
+            } else {
+              sw = (int)(qw % p.ws);
+              mbar_wait(w_full + 8 * sw, (uint32_t)((qw / p.ws) & 1));
+              tc_fence_after();
+              ++qw;
+            }
+            const uint32_t w_blk = sbase + p.smem_w_off + sw * p.w_block_bytes;
+            const uint32_t a_tap = a_slot + p.tap_src[t] * planes_per_chunk * p.a_plane_bytes +
+                                   (uint32_t)(p.tap_shift[t] - p.min_shift) * 16u;
+            for (int m = 0; m < p.mt; ++m)
+              for (int j = 0; j < (p.kc >> 4); ++j) {
+                const uint64_t adesc = umma_desc(a_tap + m * (kTileM * 16) + 2 * j * p.a_plane_bytes, p.a_plane_bytes, 128);
+                const uint64_t bdesc = umma_desc(w_blk + 2 * j * b_lbo, b_lbo, 128);
+                umma_f16(d_base + m * p.n, adesc, bdesc, idesc, (uint32_t)((kci | t | j) != 0));
+              }
+            if (!p.w_resident) umma_commit(w_empty + 8 * sw);
+          }
+          umma_commit(a_empty + 8 * sa);
+        }
+        umma_commit(acc_full + 8 * as_);
+      }
+    }
+  } else if (warp == 2) {
+    if (lane == 0) {  // ---------------- activation producer
+      long long qa = 0;
+      for (int it = 0; it < n_my; ++it) {
+        const long long g0 = (first_tile + (long long)it * gridDim.x) * (kTileM * p.mt) + p.min_shift;
+        for (int kci = 0; kci < nk; ++kci, ++qa) {
+          const int sa = (int)(qa % p.ra);
+          mbar_wait(a_empty + 8 * sa, (uint32_t)(((qa / p.ra) & 1) ^ 1));
+          mbar_expect_tx(a_full + 8 * sa, p.a_slot_bytes);
+          uint32_t dst = sbase + p.smem_a_off + sa * p.a_slot_bytes;
+          for (int s = 0; s < p.n_src; ++s)
+            for (int pl = 0; pl < planes_per_chunk; ++pl, dst += p.a_plane_bytes)
+              bulk_g2s(dst, p.a_src[s] + ((long long)(kci * planes_per_chunk + pl) * p.a_plane_px + g0), p.a_plane_bytes,
+                       a_full + 8 * sa);
+        }
+      }
+    }
+  } else if (warp >= 4) {  // ---------------- epilogue: two groups of 4 warps
+    const int grp = (warp - 4) >> 2;
+    const int qd = warp & 3;  // TMEM lane quarter this warp may access
+    const long long HW = (long long)p.Hp * p.Wp;
+    for (int it = grp; it < n_my; it += 2) {
+      const int as_ = it % p.as;
+      mbar_wait(acc_full + 8 * as_, (uint32_t)((it / p.as) & 1));
+      tc_fence_after();
+      const long long tile = first_tile + (long long)it * gridDim.x;
+      for (int m = 0; m < p.mt; ++m) {
+        const long long g = tile * (kTileM * p.mt) + m * kTileM + qd * 32 + lane;
+        const long long img = g / HW;
+        const int rem = (int)(g - img * HW);
+        const int y = rem / p.Wp, x = rem - y * p.Wp;
+        const bool valid = g < p.P && y < p.H && x < p.W;
+        const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16) + as_ * p.acc_cols + m * p.n;
+        long long o1 = 0;
+        int ph = 0;
+        if (p.out_mode == 1) {
+          ph = (y & 1) * 2 + (x & 1);
+          o1 = img * ((long long)p.Hp2 * p.Wp2) + (y >> 1) * p.Wp2 + (x >> 1);
+        } else if (p.out_mode == 2) {
+          o1 = ((img * p.H + y) * p.W + x) * p.cout;
+        }
+        for (int c0 = 0; c0 < p.n; c0 += 16) {
+          uint32_t v[16];
+          tmem_ld_x16(taddr + c0, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int cg = (c0 >> 3) + h;
+            if (cg * 8 >= p.cout) break;
+            float o[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) o[i] = __uint_as_float(v[h * 8 + i]) + bias_s[cg * 8 + i];
+            if (p.res != nullptr && valid) {
+              const uint4 r = __ldg(p.res + (long long)cg * p.res_plane_px + g);
+              float a, b;
+              unpack2(r.x, p.fmt, a, b); o[0] += a; o[1] += b;
+              unpack2(r.y, p.fmt, a, b); o[2] += a; o[3] += b;
+              unpack2(r.z, p.fmt, a, b); o[4] += a; o[5] += b;
+              unpack2(r.w, p.fmt, a, b); o[6] += a; o[7] += b;
+            }
+            if (p.relu) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) o[i] = fmaxf(o[i], 0.f);
+            }
+            if (p.out_mode == 2) {
+              if (valid) {
+                float4* op = reinterpret_cast<float4*>(p.out_f32 + o1 + cg * 8);
+                op[0] = make_float4(o[0], o[1], o[2], o[3]);
+                op[1] = make_float4(o[4], o[5], o[6], o[7]);
+              }
+            } else {
+              uint4 pk = make_uint4(0u, 0u, 0u, 0u);
+              if (valid) {
+                pk.x = pack2(o[0], o[1], p.fmt);
+                pk.y = pack2(o[2], o[3], p.fmt);
+                pk.z = pack2(o[4], o[5], p.fmt);
+                pk.w = pack2(o[6], o[7], p.fmt);
+              }
+              if (p.out_mode == 0)
+                p.out[(long long)cg * p.out_plane_px + g] = pk;
+              else if (valid)
+                p.out_ph[ph][(long long)cg * p.out_ph_plane_px + o1] = pk;
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(acc_empty + 8 * as_);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    __syncwarp();
+    tmem_dealloc(tmem_base, p.tmem_cols);
+  }
 }
+
+// ------------------------------------------------------------------------------------------
+// geometry
+struct Level {
+  int H, W, Hp, Wp, C;
+  long long n_img, P, guard, plane_px;
+  long long planes() const { return C / 8; }
+  long long buf_units() const { return planes() * plane_px; }  // 16-byte units
+};
+
+Level make_level(int H, int W, int C, long long n_img) {
+  Level L;
+  L.H = H; L.W = W; L.Hp = H + 1; L.Wp = W + 1; L.C = C; L.n_img = n_img;
+  L.P = n_img * L.Hp * L.Wp;
+  L.guard = round_up(L.Wp + 2, 8) + 8;
+  L.plane_px = L.guard + round_up(L.P, 1024) + L.guard;
+  return L;
+}
+
+// zero the front guard, everything behind the last image, and (optionally) the pad cells
+__global__ void zero_halo_kernel(uint4* base, long long n_planes, Level L, int zero_pads) {
+  const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+  const long long tail = L.plane_px - L.guard - L.P;  // cells behind the images (incl. back guard)
+  const long long pads_per_img = zero_pads ? (L.Hp + L.Wp - 1) : 0;
+  const long long per_plane = L.guard + tail + pads_per_img * L.n_img;
+  const long long total = per_plane * n_planes;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long pl = i / per_plane;
+    long long k = i - pl * per_plane;
+    uint4* plane = base + pl * L.plane_px;
+    if (k < L.guard) {
+      plane[k] = z;
+    } else if ((k -= L.guard) < tail) {
+      plane[L.guard + L.P + k] = z;
+    } else {
+      k -= tail;
+      const long long img = k / pads_per_img;
+      const int c = (int)(k - img * pads_per_img);
+      // pad column x = W for y in [0,H), then pad row y = H for x in [0,Wp)
+      const long long cell = c < L.H ? (long long)c * L.Wp + L.W : (long long)L.H * L.Wp + (c - L.H);
+      plane[L.guard + img * L.Hp * L.Wp + cell] = z;
+    }
+  }
+}
+
+int zero_halo(uint4* base, long long n_planes, const Level& L, bool pads, cudaStream_t s) {
+  const long long per_plane = L.guard + (L.plane_px - L.guard - L.P) + (pads ? (L.Hp + L.Wp - 1) * L.n_img : 0);
+  const long long total = per_plane * n_planes;
+  const int blocks = (int)std::min<long long>((total + 255) / 256, 148 * 8);
+  zero_halo_kernel<<<blocks, 256, 0, s>>>(base, n_planes, L, pads ? 1 : 0);
+  return check_launch("zero_halo_kernel");
+}
+
+// ------------------------------------------------------------------------------------------
+// packed 16-bit weights: per layer, blocks [kchunk][tap], each block [kc/8][n_pad][8]
+struct TcLayer {
+  int64_t offset;  // bytes into the tc blob
+  int n_pad, kc, nk;
+};
+TcLayer g_tc[L_COUNT];
+int64_t g_tc_bytes = 0;
+std::once_flag g_tc_once;
+
+void build_tc_table() {
+  const ConvLayer* T = layer_table();
+  int64_t off = 0;
+  for (int i = 0; i < L_COUNT; ++i) {
+    g_tc[i].offset = -1;
+    if (i < L_LAYER1 || i > L_PROJ) continue;
+    g_tc[i].n_pad = (int)round_up(T[i].cout, 16);
+    g_tc[i].kc = T[i].cin < 64 ? T[i].cin : 64;
+    g_tc[i].nk = T[i].cin / g_tc[i].kc;
+    g_tc[i].offset = off;
+    off += (int64_t)T[i].ksize * T[i].ksize * T[i].cin * g_tc[i].n_pad * 2;
+    off = round_up(off, 128);
+  }
+  g_tc_bytes = off + 128;
+}
+const TcLayer* tc_table() {
+  std::call_once(g_tc_once, build_tc_table);
+  return g_tc;
+}
+
+__global__ void prepack_kernel(const float* __restrict__ w /*[taps][cin][coutP]*/, uint16_t* __restrict__ out, int taps,
+                               int cin, int cout, int coutP, int n_pad, int kc, int fmt) {
+  const long long total = (long long)taps * cin * n_pad;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  // i -> (kci, t, kk, nn, e)
+  const int e = (int)(i & 7);
+  long long r = i >> 3;
+  const int nn = (int)(r % n_pad); r /= n_pad;
+  const int kk = (int)(r % (kc / 8)); r /= (kc / 8);
+  const int t = (int)(r % taps);
+  const int kci = (int)(r / taps);
+  const int ci = kci * kc + kk * 8 + e;
+  const float v = nn < cout ? w[((long long)t * cin + ci) * coutP + nn] : 0.f;
+  out[i] = ptx::pack1(v, fmt);
+}
+
+// ------------------------------------------------------------------------------------------
+// stem: conv3x3(1->32)+BN+ReLU+maxpool2 (model_utils.py:119-124), fp32 math, writes the level-1
+// planar layout (pads as zeros).  One thread = one padded cell x 8 channels.
+template <typename TIn>
+__global__ void __launch_bounds__(256) stem_tc_kernel(const TIn* __restrict__ crops, const float* __restrict__ w,
+                                                      const float* __restrict__ bias, uint4* __restrict__ out /*plane0,px0*/,
+                                                      Level L, int fmt) {
+  __shared__ float sw[9 * 32];
+  __shared__ float sb[32];
+  for (int i = threadIdx.x; i < 9 * 32; i += blockDim.x) sw[i] = w[i];
+  if (threadIdx.x < 32) sb[threadIdx.x] = bias[threadIdx.x];
+  __syncthreads();
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= L.P * 4) return;
+  const int cg = (int)(gid & 3);
+  const long long g = gid >> 2;
+  const long long img = g / (L.Hp * L.Wp);
+  const int rem = (int)(g - img * L.Hp * L.Wp);
+  const int py = rem / L.Wp, px = rem - py * L.Wp;
+  uint4 pk = make_uint4(0u, 0u, 0u, 0u);
+  if (py < L.H && px < L.W) {
+    const int H = 2 * L.H, W = 2 * L.W;
+    const TIn* ip = crops + img * H * W;
+    float patch[4][4];
+#pragma unroll
+    for (int dy = 0; dy < 4; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < 4; ++dx) {
+        const int y = 2 * py - 1 + dy, x = 2 * px - 1 + dx;
+        float v = 0.f;
+        if ((unsigned)y < (unsigned)H && (unsigned)x < (unsigned)W) {
+          if (sizeof(TIn) == 1)
+            v = __fdiv_rn((float)ip[y * W + x], 255.0f);
+          else
+            v = (float)ip[y * W + x];
+        }
+        patch[dy][dx] = v;
+      }
+    float res[8];
+#pragma unroll
+    for (int ch = 0; ch < 8; ++ch) {
+      const int co = cg * 8 + ch;
+      float best = 0.f;
+#pragma unroll
+      for (int oy = 0; oy < 2; ++oy)
+#pragma unroll
+        for (int ox = 0; ox < 2; ++ox) {
+          float s = sb[co];
+#pragma unroll
+          for (int r = 0; r < 3; ++r)
+#pragma unroll
+            for (int q = 0; q < 3; ++q) s = fmaf(patch[oy + r][ox + q], sw[(r * 3 + q) * 32 + co], s);
+          best = fmaxf(best, s);
+        }
+      res[ch] = best;
+    }
+    pk.x = ptx::pack2(res[0], res[1], fmt);
+    pk.y = ptx::pack2(res[2], res[3], fmt);
+    pk.z = ptx::pack2(res[4], res[5], fmt);
+    pk.w = ptx::pack2(res[6], res[7], fmt);
+  }
+  out[(long long)cg * L.plane_px + g] = pk;
+}
+
+// ------------------------------------------------------------------------------------------
+// layout converters (debug entry point + tests)
+// fp32 NHWC [n,H,W,C] -> planar 16-bit.  phase_split: H,W are the FULL-resolution sizes and the
+// four (H/2 x W/2) phase images are written to base + ph * phase_units.
+__global__ void pack_planar_kernel(const float* __restrict__ in, uint4* __restrict__ base /*plane0,px0*/, Level L,
+                                   int phase_split, long long phase_units, int fullH, int fullW, int fmt) {
+  const long long total = L.n_img * fullH * fullW * (L.C / 8);
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int cg = (int)(i % (L.C / 8));
+  long long r = i / (L.C / 8);
+  const int x = (int)(r % fullW); r /= fullW;
+  const int y = (int)(r % fullH);
+  const long long img = r / fullH;
+  const float* ip = in + ((img * fullH + y) * fullW + x) * L.C + cg * 8;
+  uint4 pk;
+  pk.x = ptx::pack2(ip[0], ip[1], fmt);
+  pk.y = ptx::pack2(ip[2], ip[3], fmt);
+  pk.z = ptx::pack2(ip[4], ip[5], fmt);
+  pk.w = ptx::pack2(ip[6], ip[7], fmt);
+  if (phase_split) {
+    const int ph = (y & 1) * 2 + (x & 1);
+    base[ph * phase_units + (long long)cg * L.plane_px + img * L.Hp * L.Wp + (y >> 1) * L.Wp + (x >> 1)] = pk;
+  } else {
+    base[(long long)cg * L.plane_px + img * L.Hp * L.Wp + y * L.Wp + x] = pk;
+  }
+}
+
+__global__ void unpack_planar_kernel(const uint4* __restrict__ base, float* __restrict__ out, Level L, int cout, int fmt) {
+  const long long total = L.n_img * L.H * L.W * (L.C / 8);
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int cg = (int)(i % (L.C / 8));
+  long long r = i / (L.C / 8);
+  const int x = (int)(r % L.W); r /= L.W;
+  const int y = (int)(r % L.H);
+  const long long img = r / L.H;
+  const uint4 pk = base[(long long)cg * L.plane_px + img * L.Hp * L.Wp + y * L.Wp + x];
+  float o[8];
+  ptx::unpack2(pk.x, fmt, o[0], o[1]);
+  ptx::unpack2(pk.y, fmt, o[2], o[3]);
+  ptx::unpack2(pk.z, fmt, o[4], o[5]);
+  ptx::unpack2(pk.w, fmt, o[6], o[7]);
+  float* op = out + ((img * L.H + y) * L.W + x) * cout + cg * 8;
+  for (int k = 0; k < 8; ++k)
+    if (cg * 8 + k < cout) op[k] = o[k];
+}
+
+// ------------------------------------------------------------------------------------------
+// launcher
+struct ConvIo {
+  const uint4* a_base;       // plane 0 / pixel 0 of source 0 (phase 0)
+  long long a_plane_px;
+  long long a_phase_units;   // distance between phase images (stride-2 inputs)
+  const uint4* res;          // plane 0 / pixel 0, or null
+  long long res_plane_px;
+  uint4* out;                // mode 0 / mode 1 (phase 0) plane 0 / pixel 0
+  long long out_plane_px;
+  long long out_phase_units;
+  float* out_f32;
+  int out_mode;
+  bool relu;
+};
+
+int g_mt_override = 0;
+
+// `out_level`: geometry of the OUTPUT (= geometry of the input for stride 1, = geometry of each
+// input phase image for stride 2).  `next`: geometry of the phase images written in mode 1.
+int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const Level& OL, const Level* next,
+                   const ConvIo& io, int fmt, cudaStream_t stream) {
+  const ConvLayer& L = layer_table()[layer_id];
+  const TcLayer& T = tc_table()[layer_id];
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget + 4096);
+    if (e != cudaSuccess) {
+      set_error("cudaFuncSetAttribute(conv_tc_kernel): %s", cudaGetErrorString(e));
+      return AT_ERR_CUDA;
+    }
+    attr_set = true;
+  }
+  ConvTcParams p;
+  memset(&p, 0, sizeof(p));
+  const int taps = L.ksize * L.ksize;
+  p.n_taps = taps;
+  p.kc = T.kc; p.n_kchunks = T.nk; p.n = T.n_pad; p.cout = L.cout;
+  p.H = OL.H; p.W = OL.W; p.Hp = OL.Hp; p.Wp = OL.Wp; p.n_img = OL.n_img; p.P = OL.P;
+  int max_shift;
+  if (L.stride == 1) {
+    p.n_src = 1;
+    for (int t = 0; t < taps; ++t) {
+      p.tap_src[t] = 0;
+      p.tap_shift[t] = taps == 9 ? (t / 3 - 1) * OL.Wp + (t % 3 - 1) : 0;
+    }
+    p.min_shift = taps == 9 ? -(OL.Wp + 1) : 0;
+    max_shift = taps == 9 ? OL.Wp + 1 : 0;
+  } else {
+    // tap (r,s) reads input (2y+r-1, 2x+s-1): phase (r!=1, s!=1), shifted by -1 row/col when r/s == 0
+    p.n_src = taps == 9 ? 4 : 1;
+    for (int t = 0; t < taps; ++t) {
+      const int r = taps == 9 ? t / 3 : 1, s = taps == 9 ? t % 3 : 1;
+      p.tap_src[t] = (r != 1) * 2 + (s != 1);
+      p.tap_shift[t] = (r == 0 ? -OL.Wp : 0) + (s == 0 ? -1 : 0);
+    }
+    p.min_shift = taps == 9 ? -(OL.Wp + 1) : 0;
+    max_shift = 0;
+  }
+  for (int s = 0; s < p.n_src; ++s) p.a_src[s] = io.a_base + s * io.a_phase_units;
+  p.a_plane_px = io.a_plane_px;
+  p.w = reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(tc_blob) + T.offset);
+  p.bias = blob + L.bias_offset;
+  p.res = io.res; p.res_plane_px = io.res_plane_px;
+  p.out = io.out; p.out_plane_px = io.out_plane_px;
+  p.out_mode = io.out_mode; p.relu = io.relu ? 1 : 0; p.fmt = fmt;
+  p.out_f32 = io.out_f32;
+  if (io.out_mode == 1) {
+    for (int s = 0; s < 4; ++s) p.out_ph[s] = io.out + s * io.out_phase_units;
+    p.out_ph_plane_px = io.out_plane_px;
+    p.Hp2 = next->Hp; p.Wp2 = next->Wp;
+  }
+  // tile / ring configuration
+  int mt = 1;
+  if (g_mt_override > 0) mt = g_mt_override;
+  while (mt > 1 && round_up(mt * p.n, 32) * 2 > 512) mt >>= 1;
+  p.mt = mt;
+  p.npix = (int)round_up(kTileM * mt + max_shift - p.min_shift, 8);
+  p.a_plane_bytes = (uint32_t)p.npix * 16u;
+  p.a_slot_bytes = (uint32_t)(p.n_src * (p.kc / 8)) * p.a_plane_bytes;
+  p.w_block_bytes = (uint32_t)(p.kc * p.n * 2);
+  const int nblocks = p.n_kchunks * taps;
+  p.w_resident = (int64_t)nblocks * p.w_block_bytes <= 100 * 1024;
+  p.ws = p.w_resident ? nblocks : 4;
+  while (!p.w_resident && p.ws > 2 && (int64_t)p.ws * p.w_block_bytes > 128 * 1024) --p.ws;
+  p.acc_cols = (uint32_t)round_up(mt * p.n, 32);
+  p.as = (int)(512 / p.acc_cols);
+  if (p.as > 4) p.as = 4;
+  uint32_t cols = 32;
+  while (cols < p.as * p.acc_cols) cols <<= 1;
+  p.tmem_cols = cols;
+  const int64_t misc = 4096;
+  int64_t w_bytes = (int64_t)p.ws * p.w_block_bytes;
+  int64_t ra = (kSmemBudget - w_bytes - misc) / p.a_slot_bytes;
+  while (ra < 2 && !p.w_resident && p.ws > 2) {
+    --p.ws;
+    w_bytes = (int64_t)p.ws * p.w_block_bytes;
+    ra = (kSmemBudget - w_bytes - misc) / p.a_slot_bytes;
+  }
+  if (ra > 8) ra = 8;
+  if (ra < 2) {
+    set_error("conv_tc: layer %s does not fit shared memory (a_slot %u B, weights %lld B)", L.name, p.a_slot_bytes,
+              (long long)w_bytes);
+    return AT_ERR_UNSUPPORTED;
+  }
+  p.ra = (int)ra;
+  p.smem_a_off = 0;
+  p.smem_w_off = (uint32_t)round_up((int64_t)p.ra * p.a_slot_bytes, 128);
+  p.smem_bias_off = (uint32_t)round_up(p.smem_w_off + w_bytes, 128);
+  p.smem_bar_off = (uint32_t)round_up(p.smem_bias_off + p.n * 4, 128);
+  const uint32_t smem_bytes = p.smem_bar_off + 8 * (2 * p.ra + 2 * p.ws + 2 * p.as) + 16;
+  p.n_tiles = (OL.P + kTileM * mt - 1) / (kTileM * mt);
+  const int grid = (int)std::min<long long>(p.n_tiles, kNumSMs);
+  if (grid == 0) return AT_OK;
+  conv_tc_kernel<<<grid, kThreads, smem_bytes, stream>>>(p);
+  return check_launch("conv_tc_kernel");
+}
+
+// ------------------------------------------------------------------------------------------
+// encoder orchestration
+constexpr int kChunkCrops = 2048;
+
+struct Plan {
+  Level lv[4];   // activation geometry per resolution level (48, 24, 12, 6)
+  long long buf_units[4];   // one activation buffer per level (16-byte units)
+  long long ps_units[3];    // one phase image set member (phase stride) for the outputs of levels 0..2
+  long long off_lv[4];      // workspace offsets (units): 4 buffers per level (X, T, Y, D)
+  long long off_ps[3];
+  long long total_units;
+};
+
+Plan make_plan(long long nc) {
+  Plan P;
+  const int HW[4] = {48, 24, 12, 6}, C[4] = {32, 64, 128, 256};
+  long long off = 0;
+  for (int l = 0; l < 4; ++l) {
+    P.lv[l] = make_level(HW[l], HW[l], C[l], nc);
+    P.buf_units[l] = P.lv[l].buf_units();
+    P.off_lv[l] = off;
+    off += 4 * P.buf_units[l];
+  }
+  for (int l = 0; l < 3; ++l) {
+    // phase images of level l's output have the geometry of level l+1 but level l's channel count
+    Level ph = make_level(HW[l + 1], HW[l + 1], C[l], nc);
+    P.ps_units[l] = ph.buf_units();
+    P.off_ps[l] = off;
+    off += 4 * P.ps_units[l];
+  }
+  P.total_units = off;
+  return P;
+}
+
+}  // namespace tc
+
+int64_t encoder_workspace_bytes_bf16(int c) {
+  const long long nc = c < tc::kChunkCrops ? (c > 0 ? c : 1) : tc::kChunkCrops;
+  return tc::make_plan(nc).total_units * 16 + 256;
+}
+
+int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* crops, int crop_dtype, int c, float* features,
+                         void* workspace, int64_t workspace_bytes, int fmt, cudaStream_t s) {
+  using namespace tc;
+  const ConvLayer* T = layer_table();
+  uint4* ws = reinterpret_cast<uint4*>(round_up((int64_t)(uintptr_t)workspace, 128));
+  for (int c0 = 0; c0 < c; c0 += kChunkCrops) {
+    const long long nc = std::min(c - c0, kChunkCrops);
+    const Plan P = make_plan(nc);
+    int rc;
+    // zero guards (and the pads of the phase-split buffers, which the epilogue does not touch)
+    for (int l = 0; l < 4; ++l)
+      if ((rc = zero_halo(ws + P.off_lv[l], 4 * P.lv[l].planes(), P.lv[l], false, s))) return rc;
+    Level phl[3];
+    for (int l = 0; l < 3; ++l) {
+      phl[l] = make_level(P.lv[l + 1].H, P.lv[l + 1].W, P.lv[l].C, nc);
+      if ((rc = zero_halo(ws + P.off_ps[l], 4 * phl[l].planes(), phl[l], true, s))) return rc;
+    }
+    auto buf = [&](int l, int i) { return ws + P.off_lv[l] + i * P.buf_units[l] + P.lv[l].guard; };
+    // stem -> X of level 0
+    {
+      const Level& L0 = P.lv[0];
+      const long long total = L0.P * 4;
+      const unsigned blocks = (unsigned)((total + 255) / 256);
+      const ConvLayer& S = T[L_STEM];
+      if (crop_dtype == AT_U8)
+        stem_tc_kernel<uint8_t><<<blocks, 256, 0, s>>>((const uint8_t*)crops + (size_t)c0 * 96 * 96, blob + S.weight_offset,
+                                                        blob + S.bias_offset, buf(0, 0), L0, fmt);
+      else
+        stem_tc_kernel<float><<<blocks, 256, 0, s>>>((const float*)crops + (size_t)c0 * 96 * 96, blob + S.weight_offset,
+                                                      blob + S.bias_offset, buf(0, 0), L0, fmt);
+      if ((rc = check_launch("stem_tc_kernel"))) return rc;
+    }
+    const int nblocks[4] = {2, 3, 5, 2};
+    int id = L_LAYER1;
+    int cur = 0;  // index (0 = X, 2 = Y) of the buffer holding the current activation of the level
+    for (int l = 0; l < 4; ++l) {
+      const Level& LV = P.lv[l];
+      for (int b = 0; b < nblocks[l]; ++b) {
+        const bool first = l > 0 && b == 0;
+        const bool last = b == nblocks[l] - 1 && l < 3;
+        ConvIo io;
+        memset(&io, 0, sizeof(io));
+        uint4* Tm = buf(l, 1);
+        const uint4* resid;
+        if (first) {
+          // conv1 (3x3 stride 2) and the 1x1 stride-2 shortcut both read the phase-split output of level l-1
+          const uint4* src = ws + P.off_ps[l - 1] + phl[l - 1].guard;
+          io.a_base = src; io.a_plane_px = phl[l - 1].plane_px; io.a_phase_units = P.ps_units[l - 1];
+          io.out = Tm; io.out_plane_px = LV.plane_px; io.out_mode = 0; io.relu = true;
+          if ((rc = launch_conv_tc(id, blob, tc_blob, LV, nullptr, io, fmt, s))) return rc;
+          io.out = buf(l, 3); io.relu = false;
+          if ((rc = launch_conv_tc(id + 2, blob, tc_blob, LV, nullptr, io, fmt, s))) return rc;
+          resid = buf(l, 3);
+          cur = 2;  // so that the block output goes to X
+        } else {
+          io.a_base = buf(l, cur); io.a_plane_px = LV.plane_px;
+          io.out = Tm; io.out_plane_px = LV.plane_px; io.out_mode = 0; io.relu = true;
+          if ((rc = launch_conv_tc(id, blob, tc_blob, LV, nullptr, io, fmt, s))) return rc;
+          resid = buf(l, cur);
+        }
+        memset(&io, 0, sizeof(io));
+        io.a_base = Tm; io.a_plane_px = LV.plane_px;
+        io.res = resid; io.res_plane_px = LV.plane_px; io.relu = true;
+        if (last) {
+          io.out = ws + P.off_ps[l] + phl[l].guard; io.out_plane_px = phl[l].plane_px; io.out_phase_units = P.ps_units[l];
+          io.out_mode = 1;
+          if ((rc = launch_conv_tc(id + 1, blob, tc_blob, LV, &phl[l], io, fmt, s))) return rc;
+        } else {
+          cur = 2 - cur;
+          io.out = buf(l, cur); io.out_plane_px = LV.plane_px; io.out_mode = 0;
+          if ((rc = launch_conv_tc(id + 1, blob, tc_blob, LV, nullptr, io, fmt, s))) return rc;
+        }
+        id += first ? 3 : 2;
+      }
+      cur = 0;
+    }
+    // proj 1x1 256->72, fp32 NHWC features.  The last block of level 3 wrote X or Y: recompute which.
+    {
+      // level 3 has 2 blocks: block 0 (first) writes X (cur: 2 -> 0), block 1 writes Y
+      ConvIo io;
+      memset(&io, 0, sizeof(io));
+      io.a_base = buf(3, 2); io.a_plane_px = P.lv[3].plane_px;
+      io.out_mode = 2; io.out_f32 = features + (size_t)c0 * 36 * 72; io.relu = false;
+      if ((rc = launch_conv_tc(L_PROJ, blob, tc_blob, P.lv[3], nullptr, io, fmt, s))) return rc;
+    }
+  }
+  (void)workspace_bytes;
+  return AT_OK;
+}
+
 }  // namespace at
 
-extern "C" int64_t at_model_bf16_blob_bytes(void) { return 256; }
-extern "C" int at_model_prepack_bf16(const float*, void*, void*) {
-  at::set_error("AT_PREC_BF16 encoder is not built into this library");
-  return AT_ERR_UNSUPPORTED;
+extern "C" int64_t at_model_bf16_blob_bytes(void) {
+  at::tc::tc_table();
+  return at::tc::g_tc_bytes;
+}
+
+extern "C" int at_model_prepack_tc(const float* blob, void* tc_blob, int precision, void* stream) {
+  using namespace at;
+  AT_REQUIRE(blob && tc_blob, "at_model_prepack_tc: NULL pointer");
+  AT_REQUIRE(precision == AT_PREC_BF16 || precision == AT_PREC_FP16, "at_model_prepack_tc: precision must be bf16 or fp16");
+  const ConvLayer* T = layer_table();
+  const tc::TcLayer* TT = tc::tc_table();
+  for (int i = L_LAYER1; i <= L_PROJ; ++i) {
+    const int taps = T[i].ksize * T[i].ksize;
+    const long long total = (long long)taps * T[i].cin * TT[i].n_pad;
+    tc::prepack_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        blob + T[i].weight_offset, reinterpret_cast<uint16_t*>(reinterpret_cast<uint8_t*>(tc_blob) + TT[i].offset), taps,
+        T[i].cin, T[i].cout, (int)round_up(T[i].cout, 4), TT[i].n_pad, TT[i].kc, precision == AT_PREC_BF16 ? 1 : 0);
+    int rc = check_launch("prepack_kernel");
+    if (rc) return rc;
+  }
+  return AT_OK;
+}
+
+extern "C" int at_model_prepack_bf16(const float* blob, void* bf16_blob, void* stream) {
+  return at_model_prepack_tc(blob, bf16_blob, AT_PREC_BF16, stream);
+}
+
+// Debug / test entry: one backbone conv layer through the tcgen05 path on fp32 NHWC tensors.
+// in [n,H,W,cin] -> out [n,Ho,Wo,cout]; res (optional) [n,Ho,Wo,cout].  workspace: at_debug_conv_tc_workspace_bytes.
+extern "C" int64_t at_debug_conv_tc_workspace_bytes(int n_img, int H, int W) {
+  using namespace at;
+  tc::Level a = tc::make_level(H, W, 256, n_img);
+  return a.buf_units() * 16 * 16 + 4096;
+}
+
+extern "C" int at_debug_conv_tc(const float* blob, const void* tc_blob, int layer_id, const float* in, int n_img, int H,
+                                int W, const float* res, int relu, int precision, int mt, float* out, void* workspace,
+                                int64_t workspace_bytes, void* stream_) {
+  using namespace at;
+  AT_REQUIRE(layer_id >= L_LAYER1 && layer_id <= L_PROJ, "at_debug_conv_tc: layer_id must be a backbone conv");
+  AT_REQUIRE(precision == AT_PREC_BF16 || precision == AT_PREC_FP16, "at_debug_conv_tc: bad precision");
+  AT_REQUIRE(workspace_bytes >= at_debug_conv_tc_workspace_bytes(n_img, H, W), "at_debug_conv_tc: workspace too small");
+  cudaStream_t s = (cudaStream_t)stream_;
+  const int fmt = precision == AT_PREC_BF16 ? 1 : 0;
+  const ConvLayer& L = layer_table()[layer_id];
+  const int Ho = H / L.stride, Wo = W / L.stride;
+  tc::Level OL = tc::make_level(Ho, Wo, (int)round_up(L.cout, 8), n_img);   // output geometry
+  tc::Level IL = tc::make_level(Ho, Wo, L.cin, n_img);                      // input (phase) geometry
+  uint4* ws = reinterpret_cast<uint4*>(round_up((int64_t)(uintptr_t)workspace, 128));
+  const long long quarter = at_debug_conv_tc_workspace_bytes(n_img, H, W) / 16 / 4;
+  uint4* a_buf = ws;                 // up to 4 phase images
+  uint4* r_buf = ws + 2 * quarter;
+  uint4* o_buf = ws + 3 * quarter;
+  int rc;
+  const int n_ph = L.stride == 2 ? 4 : 1;
+  for (int ph = 0; ph < n_ph; ++ph)
+    if ((rc = tc::zero_halo(a_buf + ph * IL.buf_units(), IL.planes(), IL, true, s))) return rc;
+  {
+    const long long total = (long long)n_img * H * W * (L.cin / 8);
+    tc::pack_planar_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(in, a_buf + IL.guard, IL, L.stride == 2,
+                                                                            IL.buf_units(), H, W, fmt);
+    if ((rc = check_launch("pack_planar_kernel"))) return rc;
+  }
+  tc::ConvIo io;
+  memset(&io, 0, sizeof(io));
+  if (res != nullptr) {
+    if ((rc = tc::zero_halo(r_buf, OL.planes(), OL, true, s))) return rc;
+    const long long total = (long long)n_img * Ho * Wo * (OL.C / 8);
+    AT_REQUIRE(L.cout % 8 == 0, "at_debug_conv_tc: residual needs cout % 8 == 0");
+    tc::pack_planar_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(res, r_buf + OL.guard, OL, 0, 0, Ho, Wo, fmt);
+    if ((rc = check_launch("pack_planar_kernel"))) return rc;
+    io.res = r_buf + OL.guard; io.res_plane_px = OL.plane_px;
+  }
+  io.a_base = a_buf + IL.guard; io.a_plane_px = IL.plane_px; io.a_phase_units = IL.buf_units();
+  io.relu = relu != 0;
+  tc::g_mt_override = mt;
+  if (layer_id == L_PROJ) {
+    io.out_mode = 2; io.out_f32 = out;
+    rc = tc::launch_conv_tc(layer_id, blob, tc_blob, OL, nullptr, io, fmt, s);
+    tc::g_mt_override = 0;
+    return rc;
+  }
+  if ((rc = tc::zero_halo(o_buf, OL.planes(), OL, false, s))) return rc;
+  io.out = o_buf + OL.guard; io.out_plane_px = OL.plane_px; io.out_mode = 0;
+  rc = tc::launch_conv_tc(layer_id, blob, tc_blob, OL, nullptr, io, fmt, s);
+  tc::g_mt_override = 0;
+  if (rc) return rc;
+  const long long total = (long long)n_img * Ho * Wo * (OL.C / 8);
+  tc::unpack_planar_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(o_buf + OL.guard, out, OL, L.cout, fmt);
+  return check_launch("unpack_planar_kernel");
 }

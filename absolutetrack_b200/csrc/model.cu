@@ -151,15 +151,15 @@ extern "C" int64_t at_model_blob_floats(void) { return at::blob_floats(); }
 
 extern "C" int64_t at_encoder_workspace_bytes(int c, int precision) {
   if (c < 0) return AT_ERR_INVALID_ARGUMENT;
-  if (precision == AT_PREC_BF16) return at::encoder_workspace_bytes_bf16(c);
+  if (precision == AT_PREC_BF16 || precision == AT_PREC_FP16) return at::encoder_workspace_bytes_bf16(c);
   // X, T, Y (full) + D (half)
   return (int64_t)sizeof(float) * (at::kActFloatsPerCrop * 3 + at::kActFloatsPerCrop / 2) * (int64_t)c + 256;
 }
 
 namespace at {
 // tcgen05 path (conv_tc.cu)
-int encoder_forward_bf16(const float* blob, const void* bf16_blob, const void* crops, int crop_dtype, int c,
-                         float* features, void* workspace, int64_t workspace_bytes, cudaStream_t s);
+int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* crops, int crop_dtype, int c,
+                         float* features, void* workspace, int64_t workspace_bytes, int fmt, cudaStream_t s);
 int64_t encoder_workspace_bytes_bf16(int c);
 }  // namespace at
 
@@ -178,10 +178,10 @@ extern "C" int at_encoder_forward(const float* blob, const void* bf16_blob, cons
   }
   if (precision == AT_PREC_FP32)
     return at::encoder_forward_f32(blob, crops, crop_dtype, c, features, workspace, (cudaStream_t)stream);
-  if (precision == AT_PREC_BF16) {
-    AT_REQUIRE(bf16_blob != nullptr, "at_encoder_forward: bf16_blob required for AT_PREC_BF16");
+  if (precision == AT_PREC_BF16 || precision == AT_PREC_FP16) {
+    AT_REQUIRE(bf16_blob != nullptr, "at_encoder_forward: the prepacked 16-bit blob is required for AT_PREC_BF16/FP16");
     return at::encoder_forward_bf16(blob, bf16_blob, crops, crop_dtype, c, features, workspace, workspace_bytes,
-                                    (cudaStream_t)stream);
+                                    precision == AT_PREC_BF16 ? 1 : 0, (cudaStream_t)stream);
   }
   at::set_error("at_encoder_forward: bad precision %d", precision);
   return AT_ERR_INVALID_ARGUMENT;

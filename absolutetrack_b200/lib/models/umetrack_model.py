@@ -59,7 +59,7 @@ class _Workspace:
 class UmeTrackModel(nn.Module):
     """Holds the BN-folded weight blob and the SimpleConvRNN state (temporal.py:41-42)."""
 
-    PRECISIONS = {"fp32": _cabi.AT_PREC_FP32, "bf16": _cabi.AT_PREC_BF16}
+    PRECISIONS = {"fp32": _cabi.AT_PREC_FP32, "bf16": _cabi.AT_PREC_BF16, "fp16": _cabi.AT_PREC_FP16}
 
     def __init__(self, blob: torch.Tensor, model_opts: Optional[ModelOpts] = None, precision: str = "fp32"):
         super().__init__()
@@ -71,6 +71,7 @@ class UmeTrackModel(nn.Module):
         self._input_size: Tuple[int, int] = (96, 96)
         self.precision = precision
         self._bf16_blob: Optional[torch.Tensor] = None
+        self._bf16_prec = -1
         # recurrent state (plain attributes, like the reference: not buffers, not moved by .to())
         self._mem_features = torch.empty(0)      # [cap, 6, 6, 18]  (NHWC)
         self._prev_extrinsics = torch.empty(0)   # [cap, 4, 4]
@@ -124,14 +125,17 @@ class UmeTrackModel(nn.Module):
             raise ValueError(f"precision must be one of {sorted(self.PRECISIONS)}") from None
 
     def _bf16_weights(self, device):
-        if self._bf16_blob is None or self._bf16_blob.device != device:
+        """Prepacked 16-bit UMMA operand blob of the tcgen05 encoder (bf16 or fp16)."""
+        prec = self._precision_code()
+        if self._bf16_blob is None or self._bf16_blob.device != device or self._bf16_prec != prec:
             lib = _cabi.lib()
-            buf = torch.empty(lib.at_model_bf16_blob_bytes(), dtype=torch.uint8, device=device)
-            _cabi.check(
-                lib.at_model_prepack_bf16(self._blob.data_ptr(), buf.data_ptr(), _cabi.stream_ptr(device)),
-                "at_model_prepack_bf16",
-            )
-            self._bf16_blob = buf
+            buf = torch.zeros(lib.at_model_bf16_blob_bytes(), dtype=torch.uint8, device=device)
+            with torch.cuda.device(device):
+                _cabi.check(
+                    lib.at_model_prepack_tc(self._blob.data_ptr(), buf.data_ptr(), prec, _cabi.stream_ptr(device)),
+                    "at_model_prepack_tc",
+                )
+            self._bf16_blob, self._bf16_prec = buf, prec
         return self._bf16_blob
 
     def encode(self, crops: torch.Tensor) -> torch.Tensor:
@@ -151,7 +155,7 @@ class UmeTrackModel(nn.Module):
         assert tuple(crops.shape[1:]) == self._input_size, f"expected [c,96,96] crops, got {tuple(crops.shape)}"
         feats = torch.empty(c, 6, 6, 72, dtype=torch.float32, device=dev)
         prec = self._precision_code()
-        bf = self._bf16_weights(dev) if prec == _cabi.AT_PREC_BF16 else None
+        bf = self._bf16_weights(dev) if prec != _cabi.AT_PREC_FP32 else None
         nbytes = lib.at_encoder_workspace_bytes(c, prec)
         ws = self._ws_enc.get(nbytes, dev)
         with torch.cuda.device(dev):

@@ -38,7 +38,7 @@ typedef enum AtStatus {
 
 typedef enum AtDType { AT_U8 = 0, AT_F32 = 1, AT_BF16 = 2 } AtDType;
 typedef enum AtMapMode { AT_MAP_FP32 = 0, AT_MAP_FP64 = 1 } AtMapMode;
-typedef enum AtPrecision { AT_PREC_FP32 = 0, AT_PREC_BF16 = 1 } AtPrecision;
+typedef enum AtPrecision { AT_PREC_FP32 = 0, AT_PREC_BF16 = 1, AT_PREC_FP16 = 2 } AtPrecision;
 typedef enum AtHeadMode { AT_HEAD_KNOWN_SKELETON = 0, AT_HEAD_PREDICT_SCALE = 1 } AtHeadMode;
 
 int at_version(void);
@@ -138,10 +138,13 @@ typedef struct AtLayerInfo {
 int at_model_layer_table(AtLayerInfo* table, int capacity);
 /* Total float count of the blob. */
 int64_t at_model_blob_floats(void);
-/* Prepack the bf16 operand blob used by the tcgen05 encoder from the fp32 blob.
- * bf16_blob must hold at_model_bf16_blob_bytes() bytes. */
+/* Prepack the 16-bit operand blob used by the tcgen05 encoder (AT_PREC_BF16 / AT_PREC_FP16) from
+ * the fp32 blob: per backbone conv, blocks [k-chunk][tap] of [kc/8][Cout padded to 16][8] elements
+ * (the no-swizzle K-major UMMA canonical layout, so a block is one bulk-TMA copy).
+ * tc_blob must hold at_model_bf16_blob_bytes() bytes. */
 int64_t at_model_bf16_blob_bytes(void);
-int at_model_prepack_bf16(const float* blob, void* bf16_blob, void* stream);
+int at_model_prepack_tc(const float* blob, void* tc_blob, int precision, void* stream);
+int at_model_prepack_bf16(const float* blob, void* bf16_blob, void* stream); /* = prepack_tc(AT_PREC_BF16) */
 
 /* Per-view encoder: crops [c,96,96] (AT_U8 grey levels, or AT_F32 already /255) ->
  * features [c,6,6,72] float32 (NHWC; the reference's [c,72,6,6] transposed).
@@ -150,6 +153,14 @@ int64_t at_encoder_workspace_bytes(int c, int precision);
 int at_encoder_forward(const float* blob, const void* bf16_blob, const void* crops, int crop_dtype,
                        int c, float* features, void* workspace, int64_t workspace_bytes,
                        int precision, void* stream);
+
+/* Test/debug entry: ONE backbone conv layer (layer_id from at_model_layer_table, 1..28) through the
+ * tcgen05 path on float32 NHWC tensors: in [n,H,W,cin] -> out [n,H/stride,W/stride,cout], optional
+ * residual res [n,H/stride,W/stride,cout], optional ReLU.  mt = 128-pixel sub-tiles per CTA tile (0 = default). */
+int64_t at_debug_conv_tc_workspace_bytes(int n_img, int H, int W);
+int at_debug_conv_tc(const float* blob, const void* tc_blob, int layer_id, const float* in, int n_img, int H, int W,
+                     const float* res, int relu, int precision, int mt, float* out, void* workspace,
+                     int64_t workspace_bytes, void* stream);
 
 /* Recurrent state of SimpleConvRNN (temporal.py:41-42,105-125), owned by the caller. */
 typedef struct AtTemporalState {

@@ -65,6 +65,16 @@ struct ConvTcParams {
   uint32_t a_slot_bytes, a_plane_bytes, w_block_bytes, tmem_cols, acc_cols;
 };
 
+// Ring cursor without divisions: slot index + phase parity.
+struct Ring {
+  int slot = 0;
+  uint32_t phase = 0;
+  __device__ __forceinline__ void advance(int n) {
+    if (++slot == n) { slot = 0; phase ^= 1u; }
+  }
+};
+
+template <int NTAPS, int KSTEPS>
 __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   using namespace ptx;
@@ -93,15 +103,16 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem + (tmem_slot - sbase));
 
-  const long long first_tile = blockIdx.x;
-  const int n_my = first_tile < p.n_tiles ? (int)((p.n_tiles - first_tile + gridDim.x - 1) / gridDim.x) : 0;
+  const int first_tile = blockIdx.x;
+  const int n_tiles = (int)p.n_tiles;
+  const int n_my = first_tile < n_tiles ? (n_tiles - first_tile + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   const int nk = p.n_kchunks;
-  const int nblocks = nk * p.n_taps;
-  const int planes_per_chunk = p.kc >> 3;
+  constexpr int kPlanesPerChunk = KSTEPS * 2;
 
   if (warp == 0) {
     if (lane == 0) {  // ---------------- weight producer
       const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(p.w);
+      const int nblocks = nk * NTAPS;
       if (p.w_resident) {
         if (n_my > 0)
           for (int b = 0; b < nblocks; ++b) {
@@ -110,121 +121,161 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                      w_full + 8 * b);
           }
       } else {
-        long long q = 0;
+        Ring r;
         for (int it = 0; it < n_my; ++it)
-          for (int b = 0; b < nblocks; ++b, ++q) {
-            const int s = (int)(q % p.ws);
-            mbar_wait(w_empty + 8 * s, (uint32_t)(((q / p.ws) & 1) ^ 1));
-            mbar_expect_tx(w_full + 8 * s, p.w_block_bytes);
-            bulk_g2s(sbase + p.smem_w_off + s * p.w_block_bytes, wsrc + (size_t)b * p.w_block_bytes, p.w_block_bytes,
-                     w_full + 8 * s);
+          for (int b = 0; b < nblocks; ++b) {
+            mbar_wait(w_empty + 8 * r.slot, r.phase ^ 1u);
+            mbar_expect_tx(w_full + 8 * r.slot, p.w_block_bytes);
+            bulk_g2s(sbase + p.smem_w_off + r.slot * p.w_block_bytes, wsrc + (size_t)b * p.w_block_bytes,
+                     p.w_block_bytes, w_full + 8 * r.slot);
+            r.advance(p.ws);
           }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {  // ---------------- MMA issuer
-      const uint32_t idesc = umma_idesc(kTileM, p.n, p.fmt);
-      const uint32_t b_lbo = (uint32_t)p.n * 16u;
-      long long qa = 0, qw = 0;
-      for (int it = 0; it < n_my; ++it) {
-        const int as_ = it % p.as;
-        mbar_wait(acc_empty + 8 * as_, (uint32_t)(((it / p.as) & 1) ^ 1));
+    // ---------------- MMA issuer: the whole warp runs the control flow converged (warp-uniform
+    // values stay in uniform registers), one elected lane issues tcgen05.mma / commit.
+    // Descriptors are 64-bit constants whose low word is advanced by precomputed 16-byte offsets.
+    const uint32_t tm = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t idesc = umma_idesc(kTileM, p.n, p.fmt);
+    const uint32_t desc_hi = (128u >> 4) | (1u << 14);                       // SBO = 128 B, version 1
+    const uint32_t a_lo0 = ((p.a_plane_bytes >> 4) << 16) + ((sbase + p.smem_a_off) >> 4);
+    const uint32_t b_lo0 = ((uint32_t)p.n << 16) + ((sbase + p.smem_w_off) >> 4);   // LBO = n*16 B
+    const uint32_t a_slot16 = p.a_slot_bytes >> 4, w_blk16 = p.w_block_bytes >> 4;
+    const uint32_t a_kstep16 = (2 * p.a_plane_bytes) >> 4, b_kstep16 = (uint32_t)(2 * p.n);
+    uint32_t tap_off[NTAPS];
+#pragma unroll
+    for (int t = 0; t < NTAPS; ++t)
+      tap_off[t] = ((uint32_t)p.tap_src[t] * kPlanesPerChunk * p.a_plane_bytes >> 4) + (uint32_t)(p.tap_shift[t] - p.min_shift);
+    Ring ra, rw, rc;
+    for (int it = 0; it < n_my; ++it) {
+      mbar_wait(acc_empty + 8 * rc.slot, rc.phase ^ 1u);
+      tc_fence_after();
+      const uint32_t d_base = tm + rc.slot * p.acc_cols;
+      for (int kci = 0; kci < nk; ++kci) {
+        mbar_wait(a_full + 8 * ra.slot, ra.phase);
         tc_fence_after();
-        const uint32_t d_base = tmem_base + as_ * p.acc_cols;
-        for (int kci = 0; kci < nk; ++kci, ++qa) {
-          const int sa = (int)(qa % p.ra);
-          mbar_wait(a_full + 8 * sa, (uint32_t)((qa / p.ra) & 1));
-          tc_fence_after();
-          const uint32_t a_slot = sbase + p.smem_a_off + sa * p.a_slot_bytes;
-          for (int t = 0; t < p.n_taps; ++t) {
-            int sw;
-            if (p.w_resident) {
-              sw = kci * p.n_taps + t;
-              if (it == 0) {
-                mbar_wait(w_full + 8 * sw, 0);
-                tc_fence_after();
-              }
-            } else {
-              sw = (int)(qw % p.ws);
-              mbar_wait(w_full + 8 * sw, (uint32_t)((qw / p.ws) & 1));
-              tc_fence_after();
-              ++qw;
-            }
-            const uint32_t w_blk = sbase + p.smem_w_off + sw * p.w_block_bytes;
-            const uint32_t a_tap = a_slot + p.tap_src[t] * planes_per_chunk * p.a_plane_bytes +
-                                   (uint32_t)(p.tap_shift[t] - p.min_shift) * 16u;
-            for (int m = 0; m < p.mt; ++m)
-              for (int j = 0; j < (p.kc >> 4); ++j) {
-                const uint64_t adesc = umma_desc(a_tap + m * (kTileM * 16) + 2 * j * p.a_plane_bytes, p.a_plane_bytes, 128);
-                const uint64_t bdesc = umma_desc(w_blk + 2 * j * b_lbo, b_lbo, 128);
-                umma_f16(d_base + m * p.n, adesc, bdesc, idesc, (uint32_t)((kci | t | j) != 0));
-              }
-            if (!p.w_resident) umma_commit(w_empty + 8 * sw);
+        const uint32_t a_lo = a_lo0 + ra.slot * a_slot16;
+        if (p.w_resident) {
+          if (it == 0) {
+            for (int t = 0; t < NTAPS; ++t) mbar_wait(w_full + 8 * (kci * NTAPS + t), 0);
+            tc_fence_after();
           }
-          umma_commit(a_empty + 8 * sa);
+          if (elect_one()) {
+            const uint32_t b_lo = b_lo0 + kci * NTAPS * w_blk16;
+#pragma unroll
+            for (int t = 0; t < NTAPS; ++t)
+              for (int m = 0; m < p.mt; ++m) {
+#pragma unroll
+                for (int j = 0; j < KSTEPS; ++j) {
+                  const uint64_t ad = ((uint64_t)desc_hi << 32) | (a_lo + tap_off[t] + m * kTileM + j * a_kstep16);
+                  const uint64_t bd = ((uint64_t)desc_hi << 32) | (b_lo + t * w_blk16 + j * b_kstep16);
+                  umma_f16(d_base + m * p.n, ad, bd, idesc, (uint32_t)((kci | t | j) != 0));
+                }
+              }
+            umma_commit(a_empty + 8 * ra.slot);
+          }
+          __syncwarp();
+        } else {
+#pragma unroll
+          for (int t = 0; t < NTAPS; ++t) {
+            mbar_wait(w_full + 8 * rw.slot, rw.phase);
+            tc_fence_after();
+            if (elect_one()) {
+              const uint32_t b_lo = b_lo0 + rw.slot * w_blk16;
+              for (int m = 0; m < p.mt; ++m) {
+#pragma unroll
+                for (int j = 0; j < KSTEPS; ++j) {
+                  const uint64_t ad = ((uint64_t)desc_hi << 32) | (a_lo + tap_off[t] + m * kTileM + j * a_kstep16);
+                  const uint64_t bd = ((uint64_t)desc_hi << 32) | (b_lo + j * b_kstep16);
+                  umma_f16(d_base + m * p.n, ad, bd, idesc, (uint32_t)((kci | t | j) != 0));
+                }
+              }
+              umma_commit(w_empty + 8 * rw.slot);
+              if (t == NTAPS - 1) umma_commit(a_empty + 8 * ra.slot);
+            }
+            __syncwarp();
+            rw.advance(p.ws);
+          }
         }
-        umma_commit(acc_full + 8 * as_);
+        ra.advance(p.ra);
       }
+      if (elect_one()) umma_commit(acc_full + 8 * rc.slot);
+      __syncwarp();
+      rc.advance(p.as);
     }
   } else if (warp == 2) {
     if (lane == 0) {  // ---------------- activation producer
-      long long qa = 0;
+      Ring ra;
       for (int it = 0; it < n_my; ++it) {
-        const long long g0 = (first_tile + (long long)it * gridDim.x) * (kTileM * p.mt) + p.min_shift;
-        for (int kci = 0; kci < nk; ++kci, ++qa) {
-          const int sa = (int)(qa % p.ra);
-          mbar_wait(a_empty + 8 * sa, (uint32_t)(((qa / p.ra) & 1) ^ 1));
-          mbar_expect_tx(a_full + 8 * sa, p.a_slot_bytes);
-          uint32_t dst = sbase + p.smem_a_off + sa * p.a_slot_bytes;
-          for (int s = 0; s < p.n_src; ++s)
-            for (int pl = 0; pl < planes_per_chunk; ++pl, dst += p.a_plane_bytes)
-              bulk_g2s(dst, p.a_src[s] + ((long long)(kci * planes_per_chunk + pl) * p.a_plane_px + g0), p.a_plane_bytes,
-                       a_full + 8 * sa);
+        const long long g0 = (long long)(first_tile + it * (int)gridDim.x) * (kTileM * p.mt) + p.min_shift;
+        for (int kci = 0; kci < nk; ++kci) {
+          mbar_wait(a_empty + 8 * ra.slot, ra.phase ^ 1u);
+          mbar_expect_tx(a_full + 8 * ra.slot, p.a_slot_bytes);
+          uint32_t dst = sbase + p.smem_a_off + ra.slot * p.a_slot_bytes;
+          for (int s = 0; s < p.n_src; ++s) {
+            const uint4* src = p.a_src[s] + ((long long)(kci * kPlanesPerChunk) * p.a_plane_px + g0);
+            for (int pl = 0; pl < kPlanesPerChunk; ++pl, dst += p.a_plane_bytes, src += p.a_plane_px)
+              bulk_g2s(dst, src, p.a_plane_bytes, a_full + 8 * ra.slot);
+          }
+          ra.advance(p.ra);
         }
       }
     }
-  } else if (warp >= 4) {  // ---------------- epilogue: two groups of 4 warps
+  } else if (warp >= 4) {  // ---------------- epilogue: two groups of 4 warps, alternating tiles
     const int grp = (warp - 4) >> 2;
     const int qd = warp & 3;  // TMEM lane quarter this warp may access
-    const long long HW = (long long)p.Hp * p.Wp;
+    const unsigned HW = (unsigned)(p.Hp * p.Wp);
+    const int tiles_px = kTileM * p.mt;
+    Ring rc;
+    if (grp == 1) rc.advance(p.as);
     for (int it = grp; it < n_my; it += 2) {
-      const int as_ = it % p.as;
-      mbar_wait(acc_full + 8 * as_, (uint32_t)((it / p.as) & 1));
+      mbar_wait(acc_full + 8 * rc.slot, rc.phase);
       tc_fence_after();
-      const long long tile = first_tile + (long long)it * gridDim.x;
+      const int tile = first_tile + it * (int)gridDim.x;
       for (int m = 0; m < p.mt; ++m) {
-        const long long g = tile * (kTileM * p.mt) + m * kTileM + qd * 32 + lane;
-        const long long img = g / HW;
-        const int rem = (int)(g - img * HW);
-        const int y = rem / p.Wp, x = rem - y * p.Wp;
-        const bool valid = g < p.P && y < p.H && x < p.W;
-        const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16) + as_ * p.acc_cols + m * p.n;
+        const unsigned g = (unsigned)(tile * tiles_px + m * kTileM + qd * 32 + lane);
+        const unsigned img = g / HW;
+        const unsigned rem = g - img * HW;
+        const unsigned y = rem / (unsigned)p.Wp, x = rem - y * (unsigned)p.Wp;
+        const bool valid = (long long)g < p.P && y < (unsigned)p.H && x < (unsigned)p.W;
+        const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16) + rc.slot * p.acc_cols + m * p.n;
         long long o1 = 0;
         int ph = 0;
         if (p.out_mode == 1) {
-          ph = (y & 1) * 2 + (x & 1);
-          o1 = img * ((long long)p.Hp2 * p.Wp2) + (y >> 1) * p.Wp2 + (x >> 1);
+          ph = (int)((y & 1) * 2 + (x & 1));
+          o1 = (long long)img * (p.Hp2 * p.Wp2) + (y >> 1) * p.Wp2 + (x >> 1);
         } else if (p.out_mode == 2) {
-          o1 = ((img * p.H + y) * p.W + x) * p.cout;
+          o1 = ((long long)(img * p.H + y) * p.W + x) * p.cout;
         }
         for (int c0 = 0; c0 < p.n; c0 += 16) {
           uint32_t v[16];
           tmem_ld_x16(taddr + c0, v);
+          uint4 r[2];
+          const bool has_res = p.res != nullptr && valid;
+          if (has_res) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+              if (((c0 >> 3) + h) * 8 < p.cout) r[h] = __ldg(p.res + (long long)((c0 >> 3) + h) * p.res_plane_px + g);
+          }
           tmem_ld_wait();
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
             const int cg = (c0 >> 3) + h;
             if (cg * 8 >= p.cout) break;
             float o[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) o[i] = __uint_as_float(v[h * 8 + i]) + bias_s[cg * 8 + i];
-            if (p.res != nullptr && valid) {
-              const uint4 r = __ldg(p.res + (long long)cg * p.res_plane_px + g);
+            const float4 b0 = *reinterpret_cast<const float4*>(bias_s + cg * 8);
+            const float4 b1 = *reinterpret_cast<const float4*>(bias_s + cg * 8 + 4);
+            o[0] = __uint_as_float(v[h * 8 + 0]) + b0.x; o[1] = __uint_as_float(v[h * 8 + 1]) + b0.y;
+            o[2] = __uint_as_float(v[h * 8 + 2]) + b0.z; o[3] = __uint_as_float(v[h * 8 + 3]) + b0.w;
+            o[4] = __uint_as_float(v[h * 8 + 4]) + b1.x; o[5] = __uint_as_float(v[h * 8 + 5]) + b1.y;
+            o[6] = __uint_as_float(v[h * 8 + 6]) + b1.z; o[7] = __uint_as_float(v[h * 8 + 7]) + b1.w;
+            if (has_res) {
               float a, b;
-              unpack2(r.x, p.fmt, a, b); o[0] += a; o[1] += b;
-              unpack2(r.y, p.fmt, a, b); o[2] += a; o[3] += b;
-              unpack2(r.z, p.fmt, a, b); o[4] += a; o[5] += b;
-              unpack2(r.w, p.fmt, a, b); o[6] += a; o[7] += b;
+              unpack2(r[h].x, p.fmt, a, b); o[0] += a; o[1] += b;
+              unpack2(r[h].y, p.fmt, a, b); o[2] += a; o[3] += b;
+              unpack2(r[h].z, p.fmt, a, b); o[4] += a; o[5] += b;
+              unpack2(r[h].w, p.fmt, a, b); o[6] += a; o[7] += b;
             }
             if (p.relu) {
 #pragma unroll
@@ -254,7 +305,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(acc_empty + 8 * as_);
+      if (lane == 0) mbar_arrive(acc_empty + 8 * rc.slot);
+      rc.advance(p.as);
+      rc.advance(p.as);
     }
   }
   tc_fence_before();
@@ -502,7 +555,12 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   const TcLayer& T = tc_table()[layer_id];
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget + 4096);
+    cudaError_t e = cudaSuccess;
+    const int lim = kSmemBudget + 4096;
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc_kernel<9, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc_kernel<9, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc_kernel<1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc_kernel<1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(conv_tc_kernel): %s", cudaGetErrorString(e));
       return AT_ERR_CUDA;
@@ -590,7 +648,15 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   p.n_tiles = (OL.P + kTileM * mt - 1) / (kTileM * mt);
   const int grid = (int)std::min<long long>(p.n_tiles, kNumSMs);
   if (grid == 0) return AT_OK;
-  conv_tc_kernel<<<grid, kThreads, smem_bytes, stream>>>(p);
+  const int ksteps = p.kc >> 4;
+  if (taps == 9 && ksteps == 2) conv_tc_kernel<9, 2><<<grid, kThreads, smem_bytes, stream>>>(p);
+  else if (taps == 9 && ksteps == 4) conv_tc_kernel<9, 4><<<grid, kThreads, smem_bytes, stream>>>(p);
+  else if (taps == 1 && ksteps == 2) conv_tc_kernel<1, 2><<<grid, kThreads, smem_bytes, stream>>>(p);
+  else if (taps == 1 && ksteps == 4) conv_tc_kernel<1, 4><<<grid, kThreads, smem_bytes, stream>>>(p);
+  else {
+    set_error("conv_tc: unsupported taps=%d kc=%d", taps, p.kc);
+    return AT_ERR_UNSUPPORTED;
+  }
   return check_launch("conv_tc_kernel");
 }
 

@@ -26,6 +26,7 @@
 //    share halo pixels) are in flight together and the halo re-reads hit L2.
 #include <algorithm>
 #include <mutex>
+#include <stdlib.h>
 #include <string.h>
 
 #include "conv.cuh"
@@ -63,6 +64,7 @@ struct ConvTcParams {
   int ra, ws, as, w_resident;
   uint32_t smem_a_off, smem_w_off, smem_bias_off, smem_bar_off;
   uint32_t a_slot_bytes, a_plane_bytes, w_block_bytes, tmem_cols, acc_cols;
+  long long* prof;  // optional [grid][16] cycle counters (debug)
 };
 
 // Ring cursor without divisions: slot index + phase parity.
@@ -107,7 +109,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
   const int n_tiles = (int)p.n_tiles;
   const int n_my = first_tile < n_tiles ? (n_tiles - first_tile + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   const int nk = p.n_kchunks;
-  constexpr int kPlanesPerChunk = KSTEPS * 2;
+  // NTAPS == 8 is the stem GEMM: 8 MMAs (4 pooling phases x 2 rows), one 8-channel input plane,
+  // the two K halves of an MMA are two neighbouring pixels (LBO = 16 B), 4 accumulators.
+  constexpr bool kStem = NTAPS == 8;
+  constexpr int kPlanesPerChunk = kStem ? 1 : KSTEPS * 2;
 
   if (warp == 0) {
     if (lane == 0) {  // ---------------- weight producer
@@ -139,7 +144,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
     const uint32_t tm = __shfl_sync(0xffffffffu, tmem_base, 0);
     const uint32_t idesc = umma_idesc(kTileM, p.n, p.fmt);
     const uint32_t desc_hi = (128u >> 4) | (1u << 14);                       // SBO = 128 B, version 1
-    const uint32_t a_lo0 = ((p.a_plane_bytes >> 4) << 16) + ((sbase + p.smem_a_off) >> 4);
+    const uint32_t a_lo0 = ((kStem ? 1u : (p.a_plane_bytes >> 4)) << 16) + ((sbase + p.smem_a_off) >> 4);
     const uint32_t b_lo0 = ((uint32_t)p.n << 16) + ((sbase + p.smem_w_off) >> 4);   // LBO = n*16 B
     const uint32_t a_slot16 = p.a_slot_bytes >> 4, w_blk16 = p.w_block_bytes >> 4;
     const uint32_t a_kstep16 = (2 * p.a_plane_bytes) >> 4, b_kstep16 = (uint32_t)(2 * p.n);
@@ -148,12 +153,17 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
     for (int t = 0; t < NTAPS; ++t)
       tap_off[t] = ((uint32_t)p.tap_src[t] * kPlanesPerChunk * p.a_plane_bytes >> 4) + (uint32_t)(p.tap_shift[t] - p.min_shift);
     Ring ra, rw, rc;
+    long long t_acc = 0, t_a = 0, t_w = 0, t_start = clock64(), t0;
     for (int it = 0; it < n_my; ++it) {
+      t0 = clock64();
       mbar_wait(acc_empty + 8 * rc.slot, rc.phase ^ 1u);
+      t_acc += clock64() - t0;
       tc_fence_after();
       const uint32_t d_base = tm + rc.slot * p.acc_cols;
       for (int kci = 0; kci < nk; ++kci) {
+        t0 = clock64();
         mbar_wait(a_full + 8 * ra.slot, ra.phase);
+        t_a += clock64() - t0;
         tc_fence_after();
         const uint32_t a_lo = a_lo0 + ra.slot * a_slot16;
         if (p.w_resident) {
@@ -170,7 +180,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                 for (int j = 0; j < KSTEPS; ++j) {
                   const uint64_t ad = ((uint64_t)desc_hi << 32) | (a_lo + tap_off[t] + m * kTileM + j * a_kstep16);
                   const uint64_t bd = ((uint64_t)desc_hi << 32) | (b_lo + t * w_blk16 + j * b_kstep16);
-                  umma_f16(d_base + m * p.n, ad, bd, idesc, (uint32_t)((kci | t | j) != 0));
+                  if (kStem)
+                    umma_f16(d_base + (t >> 1) * p.n, ad, bd, idesc, (uint32_t)(t & 1));
+                  else
+                    umma_f16(d_base + m * p.n, ad, bd, idesc, (uint32_t)((kci | t | j) != 0));
                 }
               }
             umma_commit(a_empty + 8 * ra.slot);
@@ -179,7 +192,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
         } else {
 #pragma unroll
           for (int t = 0; t < NTAPS; ++t) {
+            t0 = clock64();
             mbar_wait(w_full + 8 * rw.slot, rw.phase);
+            t_w += clock64() - t0;
             tc_fence_after();
             if (elect_one()) {
               const uint32_t b_lo = b_lo0 + rw.slot * w_blk16;
@@ -188,7 +203,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                 for (int j = 0; j < KSTEPS; ++j) {
                   const uint64_t ad = ((uint64_t)desc_hi << 32) | (a_lo + tap_off[t] + m * kTileM + j * a_kstep16);
                   const uint64_t bd = ((uint64_t)desc_hi << 32) | (b_lo + j * b_kstep16);
-                  umma_f16(d_base + m * p.n, ad, bd, idesc, (uint32_t)((kci | t | j) != 0));
+                  if (kStem)
+                    umma_f16(d_base + (t >> 1) * p.n, ad, bd, idesc, (uint32_t)(t & 1));
+                  else
+                    umma_f16(d_base + m * p.n, ad, bd, idesc, (uint32_t)((kci | t | j) != 0));
                 }
               }
               umma_commit(w_empty + 8 * rw.slot);
@@ -203,6 +221,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
       if (elect_one()) umma_commit(acc_full + 8 * rc.slot);
       __syncwarp();
       rc.advance(p.as);
+    }
+    if (p.prof != nullptr && lane == 0) {
+      long long* o = p.prof + blockIdx.x * 16;
+      o[0] = clock64() - t_start; o[1] = t_acc; o[2] = t_a; o[3] = t_w; o[4] = n_my;
     }
   } else if (warp == 2) {
     if (lane == 0) {  // ---------------- activation producer
@@ -229,10 +251,30 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
     const int tiles_px = kTileM * p.mt;
     Ring rc;
     if (grp == 1) rc.advance(p.as);
+    long long e_wait = 0, e_start = clock64();
+    const int ncg = (p.cout + 7) >> 3;
     for (int it = grp; it < n_my; it += 2) {
-      mbar_wait(acc_full + 8 * rc.slot, rc.phase);
-      tc_fence_after();
       const int tile = first_tile + it * (int)gridDim.x;
+      // residual prefetch for the first sub-tile (first 8 channel groups) BEFORE waiting for the
+      // accumulator: hides the global-load latency behind the MMAs of this tile
+      uint4 rpre[8];
+      bool pre_valid = false;
+      if (p.res != nullptr) {
+        const unsigned g = (unsigned)(tile * tiles_px + qd * 32 + lane);
+        const unsigned img = g / HW;
+        const unsigned rem = g - img * HW;
+        const unsigned y = rem / (unsigned)p.Wp, x = rem - y * (unsigned)p.Wp;
+        pre_valid = (long long)g < p.P && y < (unsigned)p.H && x < (unsigned)p.W;
+        if (pre_valid) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            if (i < ncg) rpre[i] = __ldg(p.res + (long long)i * p.res_plane_px + g);
+        }
+      }
+      const long long e0 = clock64();
+      mbar_wait(acc_full + 8 * rc.slot, rc.phase);
+      e_wait += clock64() - e0;
+      tc_fence_after();
       for (int m = 0; m < p.mt; ++m) {
         const unsigned g = (unsigned)(tile * tiles_px + m * kTileM + qd * 32 + lane);
         const unsigned img = g / HW;
@@ -248,21 +290,42 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
         } else if (p.out_mode == 2) {
           o1 = ((long long)(img * p.H + y) * p.W + x) * p.cout;
         }
+        const bool has_res = p.res != nullptr && valid;
+#pragma unroll 1
         for (int c0 = 0; c0 < p.n; c0 += 16) {
           uint32_t v[16];
           tmem_ld_x16(taddr + c0, v);
+          if (kStem) {  // 2x2 max-pool = elementwise max of the four phase accumulators
+#pragma unroll 1
+            for (int q = 1; q < 4; ++q) {
+              uint32_t u[16];
+              tmem_ld_wait();
+              tmem_ld_x16(taddr + q * p.n + c0, u);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 16; ++i) v[i] = __float_as_uint(fmaxf(__uint_as_float(v[i]), __uint_as_float(u[i])));
+            }
+          }
           uint4 r[2];
-          const bool has_res = p.res != nullptr && valid;
           if (has_res) {
 #pragma unroll
-            for (int h = 0; h < 2; ++h)
-              if (((c0 >> 3) + h) * 8 < p.cout) r[h] = __ldg(p.res + (long long)((c0 >> 3) + h) * p.res_plane_px + g);
+            for (int h = 0; h < 2; ++h) {
+              const int cg = (c0 >> 3) + h;
+              if (m == 0 && cg < 8) {
+                // select from the prefetched registers with compile-time indices
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                  if (i == cg) r[h] = rpre[i];
+              } else if (cg < ncg) {
+                r[h] = __ldg(p.res + (long long)cg * p.res_plane_px + g);
+              }
+            }
           }
           tmem_ld_wait();
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
             const int cg = (c0 >> 3) + h;
-            if (cg * 8 >= p.cout) break;
+            if (cg >= ncg) break;
             float o[8];
             const float4 b0 = *reinterpret_cast<const float4*>(bias_s + cg * 8);
             const float4 b1 = *reinterpret_cast<const float4*>(bias_s + cg * 8 + 4);
@@ -308,6 +371,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
       if (lane == 0) mbar_arrive(acc_empty + 8 * rc.slot);
       rc.advance(p.as);
       rc.advance(p.as);
+    }
+    if (p.prof != nullptr && lane == 0 && qd == 0) {
+      long long* o = p.prof + blockIdx.x * 16 + 8 + grp * 2;
+      o[0] = clock64() - e_start; o[1] = e_wait;
     }
   }
   tc_fence_before();
@@ -385,7 +452,13 @@ void build_tc_table() {
   int64_t off = 0;
   for (int i = 0; i < L_COUNT; ++i) {
     g_tc[i].offset = -1;
-    if (i < L_LAYER1 || i > L_PROJ) continue;
+    if (i > L_PROJ) continue;
+    if (i == L_STEM) {  // stem GEMM: 8 blocks (4 pooling phases x 2 rows) of [2 pixels][32][8]
+      g_tc[i].n_pad = 32; g_tc[i].kc = 16; g_tc[i].nk = 1;
+      g_tc[i].offset = off;
+      off += 8 * 1024;
+      continue;
+    }
     g_tc[i].n_pad = (int)round_up(T[i].cout, 16);
     g_tc[i].kc = T[i].cin < 64 ? T[i].cin : 64;
     g_tc[i].nk = T[i].cin / g_tc[i].kc;
@@ -418,67 +491,119 @@ __global__ void prepack_kernel(const float* __restrict__ w /*[taps][cin][coutP]*
 }
 
 // ------------------------------------------------------------------------------------------
+// Stem as a tensor-core GEMM (conv3x3(1->32)+BN+ReLU+maxpool2, model_utils.py:119-124).
+// Input plane S: cell g of the level-1 geometry holds the 2x2 block of crop pixels under pooled
+// pixel g as channels (pa*2+pb) of one 16-byte unit (4 values + 4 zeros).  The conv output at
+// pooling phase (oy,ox) is then a 2x2-shift GEMM over S; one MMA covers two horizontally
+// neighbouring cells (its two K halves, LBO = 16 B).  The epilogue takes the max of the four
+// phase accumulators (= the max-pool), adds the bias and applies ReLU.
+__global__ void prepack_stem_kernel(const float* __restrict__ w /*[9][32]*/, uint16_t* __restrict__ out, int fmt) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 8 * 512) return;
+  const int e = i & 7, nn = (i >> 3) & 31, h = (i >> 8) & 1, t = i >> 9;
+  const int op = t >> 1, q = t & 1, oy = op >> 1, ox = op & 1;
+  const int dy = (oy == 0 ? -1 : 0) + q, dx = (ox == 0 ? -1 : 0) + h;
+  const int pa = e >> 1, pb = e & 1;
+  const int r = 2 * dy + pa - oy + 1, c = 2 * dx + pb - ox + 1;
+  float v = 0.f;
+  if (e < 4 && r >= 0 && r <= 2 && c >= 0 && c <= 2) v = w[(r * 3 + c) * 32 + nn];
+  out[i] = ptx::pack1(v, fmt);
+}
+
+template <typename TIn>
+__global__ void __launch_bounds__(256) stem_pack_kernel(const TIn* __restrict__ crops, uint4* __restrict__ out /*px0*/, Level L,
+                                                        int fmt) {
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= L.P) return;
+  const int HWp = L.Hp * L.Wp;
+  const int img = (int)(g / HWp);
+  const int rem = (int)(g - (long long)img * HWp);
+  const int py = rem / L.Wp, px = rem - py * L.Wp;
+  uint4 pk = make_uint4(0u, 0u, 0u, 0u);
+  if (py < L.H && px < L.W) {
+    const int W = 2 * L.W;
+    const TIn* ip = crops + (size_t)img * (2 * L.H) * W + (2 * py) * W + 2 * px;
+    float v00, v01, v10, v11;
+    if (sizeof(TIn) == 1) {
+      const uchar2 a = __ldg(reinterpret_cast<const uchar2*>(ip)), b = __ldg(reinterpret_cast<const uchar2*>(ip + W));
+      v00 = __fdiv_rn((float)a.x, 255.0f); v01 = __fdiv_rn((float)a.y, 255.0f);
+      v10 = __fdiv_rn((float)b.x, 255.0f); v11 = __fdiv_rn((float)b.y, 255.0f);
+    } else {
+      const float2 a = __ldg(reinterpret_cast<const float2*>(ip)), b = __ldg(reinterpret_cast<const float2*>(ip + W));
+      v00 = a.x; v01 = a.y; v10 = b.x; v11 = b.y;
+    }
+    pk.x = ptx::pack2(v00, v01, fmt);
+    pk.y = ptx::pack2(v10, v11, fmt);
+  }
+  out[g] = pk;
+}
+
 // stem: conv3x3(1->32)+BN+ReLU+maxpool2 (model_utils.py:119-124), fp32 math, writes the level-1
-// planar layout (pads as zeros).  One thread = one padded cell x 8 channels.
+// planar layout (pads as zeros).  64 consecutive padded cells x 4 channel groups per block
+// iteration; the 72 weights of a thread's channel group stay in registers across iterations.
+constexpr int kStemIters = 8;
 template <typename TIn>
 __global__ void __launch_bounds__(256) stem_tc_kernel(const TIn* __restrict__ crops, const float* __restrict__ w,
                                                       const float* __restrict__ bias, uint4* __restrict__ out /*plane0,px0*/,
                                                       Level L, int fmt) {
-  __shared__ float sw[9 * 32];
-  __shared__ float sb[32];
-  for (int i = threadIdx.x; i < 9 * 32; i += blockDim.x) sw[i] = w[i];
-  if (threadIdx.x < 32) sb[threadIdx.x] = bias[threadIdx.x];
-  __syncthreads();
-  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (gid >= L.P * 4) return;
-  const int cg = (int)(gid & 3);
-  const long long g = gid >> 2;
-  const long long img = g / (L.Hp * L.Wp);
-  const int rem = (int)(g - img * L.Hp * L.Wp);
-  const int py = rem / L.Wp, px = rem - py * L.Wp;
-  uint4 pk = make_uint4(0u, 0u, 0u, 0u);
-  if (py < L.H && px < L.W) {
-    const int H = 2 * L.H, W = 2 * L.W;
-    const TIn* ip = crops + img * H * W;
-    float patch[4][4];
+  const int cg = threadIdx.x >> 6;
+  float wr[9][8], br[8];
 #pragma unroll
-    for (int dy = 0; dy < 4; ++dy)
+  for (int t = 0; t < 9; ++t)
 #pragma unroll
-      for (int dx = 0; dx < 4; ++dx) {
-        const int y = 2 * py - 1 + dy, x = 2 * px - 1 + dx;
-        float v = 0.f;
-        if ((unsigned)y < (unsigned)H && (unsigned)x < (unsigned)W) {
-          if (sizeof(TIn) == 1)
-            v = __fdiv_rn((float)ip[y * W + x], 255.0f);
-          else
-            v = (float)ip[y * W + x];
+    for (int ch = 0; ch < 8; ++ch) wr[t][ch] = __ldg(w + t * 32 + cg * 8 + ch);
+#pragma unroll
+  for (int ch = 0; ch < 8; ++ch) br[ch] = __ldg(bias + cg * 8 + ch);
+  const int HWp = L.Hp * L.Wp;
+  const int H = 2 * L.H, W = 2 * L.W;
+  for (int k = 0; k < kStemIters; ++k) {
+    const long long g = ((long long)blockIdx.x * kStemIters + k) * 64 + (threadIdx.x & 63);
+    if (g >= L.P) return;
+    const int img = (int)(g / HWp);
+    const int rem = (int)(g - (long long)img * HWp);
+    const int py = rem / L.Wp, px = rem - py * L.Wp;
+    uint4 pk = make_uint4(0u, 0u, 0u, 0u);
+    if (py < L.H && px < L.W) {
+      const TIn* ip = crops + (size_t)img * H * W;
+      float patch[4][4];
+#pragma unroll
+      for (int dy = 0; dy < 4; ++dy)
+#pragma unroll
+        for (int dx = 0; dx < 4; ++dx) {
+          const int y = 2 * py - 1 + dy, x = 2 * px - 1 + dx;
+          float v = 0.f;
+          if ((unsigned)y < (unsigned)H && (unsigned)x < (unsigned)W) {
+            if (sizeof(TIn) == 1)
+              v = __fdiv_rn((float)__ldg(ip + y * W + x), 255.0f);
+            else
+              v = (float)__ldg(ip + y * W + x);
+          }
+          patch[dy][dx] = v;
         }
-        patch[dy][dx] = v;
+      float res[8];
+#pragma unroll
+      for (int ch = 0; ch < 8; ++ch) {
+        float best = 0.f;  // ReLU then max == max(0, max of the four)
+#pragma unroll
+        for (int oy = 0; oy < 2; ++oy)
+#pragma unroll
+          for (int ox = 0; ox < 2; ++ox) {
+            float acc = br[ch];
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+              for (int q = 0; q < 3; ++q) acc = fmaf(patch[oy + r][ox + q], wr[r * 3 + q][ch], acc);
+            best = fmaxf(best, acc);
+          }
+        res[ch] = best;
       }
-    float res[8];
-#pragma unroll
-    for (int ch = 0; ch < 8; ++ch) {
-      const int co = cg * 8 + ch;
-      float best = 0.f;
-#pragma unroll
-      for (int oy = 0; oy < 2; ++oy)
-#pragma unroll
-        for (int ox = 0; ox < 2; ++ox) {
-          float s = sb[co];
-#pragma unroll
-          for (int r = 0; r < 3; ++r)
-#pragma unroll
-            for (int q = 0; q < 3; ++q) s = fmaf(patch[oy + r][ox + q], sw[(r * 3 + q) * 32 + co], s);
-          best = fmaxf(best, s);
-        }
-      res[ch] = best;
+      pk.x = ptx::pack2(res[0], res[1], fmt);
+      pk.y = ptx::pack2(res[2], res[3], fmt);
+      pk.z = ptx::pack2(res[4], res[5], fmt);
+      pk.w = ptx::pack2(res[6], res[7], fmt);
     }
-    pk.x = ptx::pack2(res[0], res[1], fmt);
-    pk.y = ptx::pack2(res[2], res[3], fmt);
-    pk.z = ptx::pack2(res[4], res[5], fmt);
-    pk.w = ptx::pack2(res[6], res[7], fmt);
+    out[(long long)cg * L.plane_px + g] = pk;
   }
-  out[(long long)cg * L.plane_px + g] = pk;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -546,6 +671,7 @@ struct ConvIo {
 };
 
 int g_mt_override = 0;
+long long* g_prof = nullptr;
 
 // `out_level`: geometry of the OUTPUT (= geometry of the input for stride 1, = geometry of each
 // input phase image for stride 2).  `next`: geometry of the phase images written in mode 1.
@@ -561,6 +687,7 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
     if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc_kernel<9, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc_kernel<1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc_kernel<1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc_kernel<8, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(conv_tc_kernel): %s", cudaGetErrorString(e));
       return AT_ERR_CUDA;
@@ -569,12 +696,22 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   }
   ConvTcParams p;
   memset(&p, 0, sizeof(p));
-  const int taps = L.ksize * L.ksize;
+  const bool is_stem = layer_id == L_STEM;
+  const int taps = is_stem ? 8 : L.ksize * L.ksize;
   p.n_taps = taps;
   p.kc = T.kc; p.n_kchunks = T.nk; p.n = T.n_pad; p.cout = L.cout;
   p.H = OL.H; p.W = OL.W; p.Hp = OL.Hp; p.Wp = OL.Wp; p.n_img = OL.n_img; p.P = OL.P;
   int max_shift;
-  if (L.stride == 1) {
+  if (is_stem) {
+    p.n_src = 1;
+    for (int t = 0; t < 8; ++t) {
+      const int op = t >> 1, q = t & 1, oy = op >> 1, ox = op & 1;
+      p.tap_src[t] = 0;
+      p.tap_shift[t] = ((oy == 0 ? -1 : 0) + q) * OL.Wp + (ox == 0 ? -1 : 0);
+    }
+    p.min_shift = -(OL.Wp + 1);
+    max_shift = OL.Wp + 1;
+  } else if (L.stride == 1) {
     p.n_src = 1;
     for (int t = 0; t < taps; ++t) {
       p.tap_src[t] = 0;
@@ -601,6 +738,7 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   p.out = io.out; p.out_plane_px = io.out_plane_px;
   p.out_mode = io.out_mode; p.relu = io.relu ? 1 : 0; p.fmt = fmt;
   p.out_f32 = io.out_f32;
+  p.prof = g_prof;
   if (io.out_mode == 1) {
     for (int s = 0; s < 4; ++s) p.out_ph[s] = io.out + s * io.out_phase_units;
     p.out_ph_plane_px = io.out_plane_px;
@@ -608,31 +746,43 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   }
   // tile / ring configuration
   int mt = 1;
+  {
+    // experiment knobs: AT_TC_MT<N> = sub-tiles per tile for layers with padded Cout == N
+    char name[32];
+    snprintf(name, sizeof(name), "AT_TC_MT%d", p.n);
+    const char* e = getenv(name);
+    if (e) mt = atoi(e);
+  }
   if (g_mt_override > 0) mt = g_mt_override;
-  while (mt > 1 && round_up(mt * p.n, 32) * 2 > 512) mt >>= 1;
-  p.mt = mt;
-  p.npix = (int)round_up(kTileM * mt + max_shift - p.min_shift, 8);
-  p.a_plane_bytes = (uint32_t)p.npix * 16u;
-  p.a_slot_bytes = (uint32_t)(p.n_src * (p.kc / 8)) * p.a_plane_bytes;
-  p.w_block_bytes = (uint32_t)(p.kc * p.n * 2);
+  if (p.n_src > 1 || is_stem) mt = 1;  // the 4-phase stride-2 inputs already fill the A ring
+  while (mt > 1 && round_up(mt * p.n, 32) > 512) mt >>= 1;
   const int nblocks = p.n_kchunks * taps;
-  p.w_resident = (int64_t)nblocks * p.w_block_bytes <= 100 * 1024;
-  p.ws = p.w_resident ? nblocks : 4;
-  while (!p.w_resident && p.ws > 2 && (int64_t)p.ws * p.w_block_bytes > 128 * 1024) --p.ws;
-  p.acc_cols = (uint32_t)round_up(mt * p.n, 32);
+  const int64_t misc = 4096;
+  int64_t w_bytes = 0, ra = 0;
+  for (;; mt >>= 1) {
+    p.mt = mt;
+    p.npix = (int)round_up(kTileM * mt + max_shift - p.min_shift, 8);
+    p.a_plane_bytes = (uint32_t)p.npix * 16u;
+    p.a_slot_bytes = (uint32_t)(is_stem ? 1 : p.n_src * (p.kc / 8)) * p.a_plane_bytes;
+    p.w_block_bytes = (uint32_t)(p.kc * p.n * 2);
+    p.w_resident = (int64_t)nblocks * p.w_block_bytes <= 100 * 1024;
+    p.ws = p.w_resident ? nblocks : 4;
+    while (!p.w_resident && p.ws > 2 && (int64_t)p.ws * p.w_block_bytes > 128 * 1024) --p.ws;
+    w_bytes = (int64_t)p.ws * p.w_block_bytes;
+    ra = (kSmemBudget - w_bytes - misc) / p.a_slot_bytes;
+    while (ra < 2 && !p.w_resident && p.ws > 2) {
+      --p.ws;
+      w_bytes = (int64_t)p.ws * p.w_block_bytes;
+      ra = (kSmemBudget - w_bytes - misc) / p.a_slot_bytes;
+    }
+    if (ra >= 2 || mt == 1) break;
+  }
+  p.acc_cols = (uint32_t)round_up((is_stem ? 4 : mt) * p.n, 32);
   p.as = (int)(512 / p.acc_cols);
   if (p.as > 4) p.as = 4;
   uint32_t cols = 32;
   while (cols < p.as * p.acc_cols) cols <<= 1;
   p.tmem_cols = cols;
-  const int64_t misc = 4096;
-  int64_t w_bytes = (int64_t)p.ws * p.w_block_bytes;
-  int64_t ra = (kSmemBudget - w_bytes - misc) / p.a_slot_bytes;
-  while (ra < 2 && !p.w_resident && p.ws > 2) {
-    --p.ws;
-    w_bytes = (int64_t)p.ws * p.w_block_bytes;
-    ra = (kSmemBudget - w_bytes - misc) / p.a_slot_bytes;
-  }
   if (ra > 8) ra = 8;
   if (ra < 2) {
     set_error("conv_tc: layer %s does not fit shared memory (a_slot %u B, weights %lld B)", L.name, p.a_slot_bytes,
@@ -649,7 +799,8 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   const int grid = (int)std::min<long long>(p.n_tiles, kNumSMs);
   if (grid == 0) return AT_OK;
   const int ksteps = p.kc >> 4;
-  if (taps == 9 && ksteps == 2) conv_tc_kernel<9, 2><<<grid, kThreads, smem_bytes, stream>>>(p);
+  if (is_stem) conv_tc_kernel<8, 1><<<grid, kThreads, smem_bytes, stream>>>(p);
+  else if (taps == 9 && ksteps == 2) conv_tc_kernel<9, 2><<<grid, kThreads, smem_bytes, stream>>>(p);
   else if (taps == 9 && ksteps == 4) conv_tc_kernel<9, 4><<<grid, kThreads, smem_bytes, stream>>>(p);
   else if (taps == 1 && ksteps == 2) conv_tc_kernel<1, 2><<<grid, kThreads, smem_bytes, stream>>>(p);
   else if (taps == 1 && ksteps == 4) conv_tc_kernel<1, 4><<<grid, kThreads, smem_bytes, stream>>>(p);
@@ -719,19 +870,21 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
       if ((rc = zero_halo(ws + P.off_ps[l], 4 * phl[l].planes(), phl[l], true, s))) return rc;
     }
     auto buf = [&](int l, int i) { return ws + P.off_lv[l] + i * P.buf_units[l] + P.lv[l].guard; };
-    // stem -> X of level 0
+    // stem: pack the crops into the 2x2-block plane S (first plane of the unused D buffer of
+    // level 0), then the stem GEMM writes X of level 0
     {
       const Level& L0 = P.lv[0];
-      const long long total = L0.P * 4;
-      const unsigned blocks = (unsigned)((total + 255) / 256);
-      const ConvLayer& S = T[L_STEM];
+      const unsigned blocks = (unsigned)((L0.P + 255) / 256);
       if (crop_dtype == AT_U8)
-        stem_tc_kernel<uint8_t><<<blocks, 256, 0, s>>>((const uint8_t*)crops + (size_t)c0 * 96 * 96, blob + S.weight_offset,
-                                                        blob + S.bias_offset, buf(0, 0), L0, fmt);
+        stem_pack_kernel<uint8_t><<<blocks, 256, 0, s>>>((const uint8_t*)crops + (size_t)c0 * 96 * 96, buf(0, 3), L0, fmt);
       else
-        stem_tc_kernel<float><<<blocks, 256, 0, s>>>((const float*)crops + (size_t)c0 * 96 * 96, blob + S.weight_offset,
-                                                      blob + S.bias_offset, buf(0, 0), L0, fmt);
-      if ((rc = check_launch("stem_tc_kernel"))) return rc;
+        stem_pack_kernel<float><<<blocks, 256, 0, s>>>((const float*)crops + (size_t)c0 * 96 * 96, buf(0, 3), L0, fmt);
+      if ((rc = check_launch("stem_pack_kernel"))) return rc;
+      ConvIo io;
+      memset(&io, 0, sizeof(io));
+      io.a_base = buf(0, 3); io.a_plane_px = L0.plane_px;
+      io.out = buf(0, 0); io.out_plane_px = L0.plane_px; io.out_mode = 0; io.relu = true;
+      if ((rc = launch_conv_tc(L_STEM, blob, tc_blob, L0, nullptr, io, fmt, s))) return rc;
     }
     const int nblocks[4] = {2, 3, 5, 2};
     int id = L_LAYER1;
@@ -804,6 +957,13 @@ extern "C" int at_model_prepack_tc(const float* blob, void* tc_blob, int precisi
   AT_REQUIRE(precision == AT_PREC_BF16 || precision == AT_PREC_FP16, "at_model_prepack_tc: precision must be bf16 or fp16");
   const ConvLayer* T = layer_table();
   const tc::TcLayer* TT = tc::tc_table();
+  tc::prepack_stem_kernel<<<16, 256, 0, (cudaStream_t)stream>>>(
+      blob + T[L_STEM].weight_offset, reinterpret_cast<uint16_t*>(reinterpret_cast<uint8_t*>(tc_blob) + TT[L_STEM].offset),
+      precision == AT_PREC_BF16 ? 1 : 0);
+  {
+    int rc = check_launch("prepack_stem_kernel");
+    if (rc) return rc;
+  }
   for (int i = L_LAYER1; i <= L_PROJ; ++i) {
     const int taps = T[i].ksize * T[i].ksize;
     const long long total = (long long)taps * T[i].cin * TT[i].n_pad;
@@ -822,6 +982,10 @@ extern "C" int at_model_prepack_bf16(const float* blob, void* bf16_blob, void* s
 
 // Debug / test entry: one backbone conv layer through the tcgen05 path on fp32 NHWC tensors.
 // in [n,H,W,cin] -> out [n,Ho,Wo,cout]; res (optional) [n,Ho,Wo,cout].  workspace: at_debug_conv_tc_workspace_bytes.
+/* Debug: when non-NULL every conv_tc launch writes [148][16] cycle counters there
+ * (MMA warp: total, wait acc_empty, wait a_full, wait w_full, tiles; epilogue groups at +8: total, wait). */
+extern "C" void at_debug_set_prof(long long* dev_ptr) { at::tc::g_prof = dev_ptr; }
+
 extern "C" int64_t at_debug_conv_tc_workspace_bytes(int n_img, int H, int W) {
   using namespace at;
   tc::Level a = tc::make_level(H, W, 256, n_img);

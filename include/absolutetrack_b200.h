@@ -162,6 +162,8 @@ int at_debug_conv_tc(const float* blob, const void* tc_blob, int layer_id, const
                      const float* res, int relu, int precision, int mt, float* out, void* workspace,
                      int64_t workspace_bytes, void* stream);
 
+void at_debug_set_prof(long long* dev_ptr); /* debug: per-CTA cycle counters of conv_tc launches */
+
 /* Recurrent state of SimpleConvRNN (temporal.py:41-42,105-125), owned by the caller. */
 typedef struct AtTemporalState {
   float* mem_features;    /* [capacity,6,6,18] NHWC */

@@ -110,6 +110,7 @@ SIGNATURES = {
     "at_model_prepack_bf16": (_I, [_VP, _VP, _VP]),
     "at_model_prepack_tc": (_I, [_VP, _VP, _I, _VP]),
     "at_debug_set_prof": (None, [_VP]),
+    "at_debug_set_prof_seq": (None, [_VP]),
     "at_debug_conv_tc_workspace_bytes": (_I64, [_I, _I, _I]),
     "at_debug_conv_tc": (_I, [_VP, _VP, _I, _VP, _I, _I, _I, _VP, _I, _I, _I, _VP, _VP, _I64, _VP]),
     "at_encoder_workspace_bytes": (_I64, [_I, _I]),

@@ -40,6 +40,11 @@ constexpr int kThreads = 384;
 constexpr int kMaxTaps = 9;
 constexpr int kSmemBudget = 220 * 1024;
 
+// q = n / d for the bounded n of this kernel: q = umulhi(n, magic) >> shift (host: make_divider)
+struct Divider {
+  uint32_t magic, shift, d;
+};
+
 struct ConvTcParams {
   const uint4* a_src[4];
   long long a_plane_px;
@@ -64,7 +69,9 @@ struct ConvTcParams {
   int ra, ws, as, w_resident;
   uint32_t smem_a_off, smem_w_off, smem_bias_off, smem_bar_off;
   uint32_t a_slot_bytes, a_plane_bytes, w_block_bytes, tmem_cols, acc_cols;
+  Divider div_hw, div_wp;  // g / (Hp*Wp), rem / Wp
   long long* prof;  // optional [grid][16] cycle counters (debug)
+  int dbg;          // debug knobs (AT_TC_DBG): 1 no epilogue, 2 no A copies
 };
 
 // Ring cursor without divisions: slot index + phase parity.
@@ -76,7 +83,17 @@ struct Ring {
   }
 };
 
-template <int NTAPS, int KSTEPS>
+__device__ __forceinline__ uint32_t fast_div(uint32_t n, const Divider& dv) { return __umulhi(n, dv.magic) >> dv.shift; }
+
+// one 32- or 16-column slab of an accumulator row -> +bias (+residual) -> ReLU -> 16-bit pack -> store
+struct EpiCoord {
+  bool valid;
+  long long g;      // padded-linear pixel index (planar modes)
+  long long o1;     // mode 1: index inside a phase image; mode 2: float index of channel 0
+  int ph;
+};
+
+template <int NTAPS, int KSTEPS, int MT>
 __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   using namespace ptx;
@@ -88,6 +105,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
   const uint32_t acc_full = w_empty + 8 * p.ws, acc_empty = acc_full + 8 * p.as;
   const uint32_t tmem_slot = acc_empty + 8 * p.as;
   float* bias_s = reinterpret_cast<float*>(smem + p.smem_bias_off);
+  if (p.prof != nullptr && threadIdx.x == 0) p.prof[blockIdx.x * 16 + 5] = (long long)globaltimer_ns();
 
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < p.ra; ++i) { mbar_init(a_full + 8 * i, 1); mbar_init(a_empty + 8 * i, 1); }
@@ -113,6 +131,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
   // the two K halves of an MMA are two neighbouring pixels (LBO = 16 B), 4 accumulators.
   constexpr bool kStem = NTAPS == 8;
   constexpr int kPlanesPerChunk = kStem ? 1 : KSTEPS * 2;
+  constexpr int kTilePx = kTileM * MT;
 
   if (warp == 0) {
     if (lane == 0) {  // ---------------- weight producer
@@ -139,8 +158,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
     }
   } else if (warp == 1) {
     // ---------------- MMA issuer: the whole warp runs the control flow converged (warp-uniform
-    // values stay in uniform registers), one elected lane issues tcgen05.mma / commit.
-    // Descriptors are 64-bit constants whose low word is advanced by precomputed 16-byte offsets.
+    // values stay in uniform registers), one elected lane issues tcgen05.mma / commit.  Taps,
+    // K steps and sub-tiles are compile-time so the issue block is straight-line code: two
+    // uniform adds per descriptor, no loop control between the MMAs.
     const uint32_t tm = __shfl_sync(0xffffffffu, tmem_base, 0);
     const uint32_t idesc = umma_idesc(kTileM, p.n, p.fmt);
     const uint32_t desc_hi = (128u >> 4) | (1u << 14);                       // SBO = 128 B, version 1
@@ -154,18 +174,21 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
       tap_off[t] = ((uint32_t)p.tap_src[t] * kPlanesPerChunk * p.a_plane_bytes >> 4) + (uint32_t)(p.tap_shift[t] - p.min_shift);
     Ring ra, rw, rc;
     long long t_acc = 0, t_a = 0, t_w = 0, t_start = clock64(), t0;
+    const bool prof = p.prof != nullptr;
+    if (prof && lane == 0) p.prof[blockIdx.x * 16 + 7] = (long long)globaltimer_ns();
     for (int it = 0; it < n_my; ++it) {
-      t0 = clock64();
+      if (prof) t0 = clock64();
       mbar_wait(acc_empty + 8 * rc.slot, rc.phase ^ 1u);
-      t_acc += clock64() - t0;
+      if (prof) t_acc += clock64() - t0;
       tc_fence_after();
       const uint32_t d_base = tm + rc.slot * p.acc_cols;
       for (int kci = 0; kci < nk; ++kci) {
-        t0 = clock64();
+        if (prof) t0 = clock64();
         mbar_wait(a_full + 8 * ra.slot, ra.phase);
-        t_a += clock64() - t0;
+        if (prof) t_a += clock64() - t0;
         tc_fence_after();
         const uint32_t a_lo = a_lo0 + ra.slot * a_slot16;
+        const uint32_t acc0 = kci != 0;
         if (p.w_resident) {
           if (it == 0) {
             for (int t = 0; t < NTAPS; ++t) mbar_wait(w_full + 8 * (kci * NTAPS + t), 0);
@@ -174,39 +197,39 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
           if (elect_one()) {
             const uint32_t b_lo = b_lo0 + kci * NTAPS * w_blk16;
 #pragma unroll
-            for (int t = 0; t < NTAPS; ++t)
-              for (int m = 0; m < p.mt; ++m) {
+            for (int t = 0; t < NTAPS; ++t) {
 #pragma unroll
-                for (int j = 0; j < KSTEPS; ++j) {
-                  const uint64_t ad = ((uint64_t)desc_hi << 32) | (a_lo + tap_off[t] + m * kTileM + j * a_kstep16);
-                  const uint64_t bd = ((uint64_t)desc_hi << 32) | (b_lo + t * w_blk16 + j * b_kstep16);
+              for (int j = 0; j < KSTEPS; ++j) {
+                const uint64_t bd = ((uint64_t)desc_hi << 32) | (b_lo + (t * KSTEPS + j) * b_kstep16);
+#pragma unroll
+                for (int m = 0; m < MT; ++m) {
+                  const uint64_t ad = ((uint64_t)desc_hi << 32) | (a_lo + tap_off[t] + j * a_kstep16 + m * kTileM);
                   if (kStem)
                     umma_f16(d_base + (t >> 1) * p.n, ad, bd, idesc, (uint32_t)(t & 1));
                   else
-                    umma_f16(d_base + m * p.n, ad, bd, idesc, (uint32_t)((kci | t | j) != 0));
+                    umma_f16(d_base + m * p.n, ad, bd, idesc, (t | j) != 0 ? 1u : acc0);
                 }
               }
+            }
             umma_commit(a_empty + 8 * ra.slot);
           }
           __syncwarp();
         } else {
 #pragma unroll
           for (int t = 0; t < NTAPS; ++t) {
-            t0 = clock64();
+            if (prof) t0 = clock64();
             mbar_wait(w_full + 8 * rw.slot, rw.phase);
-            t_w += clock64() - t0;
+            if (prof) t_w += clock64() - t0;
             tc_fence_after();
             if (elect_one()) {
               const uint32_t b_lo = b_lo0 + rw.slot * w_blk16;
-              for (int m = 0; m < p.mt; ++m) {
 #pragma unroll
-                for (int j = 0; j < KSTEPS; ++j) {
-                  const uint64_t ad = ((uint64_t)desc_hi << 32) | (a_lo + tap_off[t] + m * kTileM + j * a_kstep16);
-                  const uint64_t bd = ((uint64_t)desc_hi << 32) | (b_lo + j * b_kstep16);
-                  if (kStem)
-                    umma_f16(d_base + (t >> 1) * p.n, ad, bd, idesc, (uint32_t)(t & 1));
-                  else
-                    umma_f16(d_base + m * p.n, ad, bd, idesc, (uint32_t)((kci | t | j) != 0));
+              for (int j = 0; j < KSTEPS; ++j) {
+                const uint64_t bd = ((uint64_t)desc_hi << 32) | (b_lo + j * b_kstep16);
+#pragma unroll
+                for (int m = 0; m < MT; ++m) {
+                  const uint64_t ad = ((uint64_t)desc_hi << 32) | (a_lo + tap_off[t] + j * a_kstep16 + m * kTileM);
+                  umma_f16(d_base + m * p.n, ad, bd, idesc, (t | j) != 0 ? 1u : acc0);
                 }
               }
               umma_commit(w_empty + 8 * rw.slot);
@@ -222,7 +245,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
       __syncwarp();
       rc.advance(p.as);
     }
-    if (p.prof != nullptr && lane == 0) {
+    if (prof && lane == 0) {
       long long* o = p.prof + blockIdx.x * 16;
       o[0] = clock64() - t_start; o[1] = t_acc; o[2] = t_a; o[3] = t_w; o[4] = n_my;
     }
@@ -230,9 +253,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
     if (lane == 0) {  // ---------------- activation producer
       Ring ra;
       for (int it = 0; it < n_my; ++it) {
-        const long long g0 = (long long)(first_tile + it * (int)gridDim.x) * (kTileM * p.mt) + p.min_shift;
+        const long long g0 = (long long)(first_tile + it * (int)gridDim.x) * kTilePx + p.min_shift;
         for (int kci = 0; kci < nk; ++kci) {
           mbar_wait(a_empty + 8 * ra.slot, ra.phase ^ 1u);
+          if ((p.dbg & 2) && (it > 0 || kci >= p.ra)) { mbar_arrive(a_full + 8 * ra.slot); ra.advance(p.ra); continue; }
           mbar_expect_tx(a_full + 8 * ra.slot, p.a_slot_bytes);
           uint32_t dst = sbase + p.smem_a_off + ra.slot * p.a_slot_bytes;
           for (int s = 0; s < p.n_src; ++s) {
@@ -247,121 +271,121 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
   } else if (warp >= 4) {  // ---------------- epilogue: two groups of 4 warps, alternating tiles
     const int grp = (warp - 4) >> 2;
     const int qd = warp & 3;  // TMEM lane quarter this warp may access
-    const unsigned HW = (unsigned)(p.Hp * p.Wp);
-    const int tiles_px = kTileM * p.mt;
     Ring rc;
     if (grp == 1) rc.advance(p.as);
     long long e_wait = 0, e_start = clock64();
+    const bool prof = p.prof != nullptr;
     const int ncg = (p.cout + 7) >> 3;
+    const bool has_res = p.res != nullptr;
+    const int n_slabs = (p.n + 31) >> 5;  // 32-column slabs (the last one may hold 16)
     for (int it = grp; it < n_my; it += 2) {
       const int tile = first_tile + it * (int)gridDim.x;
-      // residual prefetch for the first sub-tile (first 8 channel groups) BEFORE waiting for the
-      // accumulator: hides the global-load latency behind the MMAs of this tile
-      uint4 rpre[8];
-      bool pre_valid = false;
-      if (p.res != nullptr) {
-        const unsigned g = (unsigned)(tile * tiles_px + qd * 32 + lane);
-        const unsigned img = g / HW;
-        const unsigned rem = g - img * HW;
-        const unsigned y = rem / (unsigned)p.Wp, x = rem - y * (unsigned)p.Wp;
-        pre_valid = (long long)g < p.P && y < (unsigned)p.H && x < (unsigned)p.W;
-        if (pre_valid) {
+      const uint32_t gbase = (uint32_t)tile * kTilePx + qd * 32 + lane;
+      // residual of the first slab: issued BEFORE waiting for the accumulator so that the
+      // global-load latency hides behind the MMAs of this tile.  Pads / the tail behind the
+      // last image are readable (zeros or stale finite data) and masked by `valid` below.
+      uint4 rcur[4], rnext[4];
+      if (has_res) {
 #pragma unroll
-          for (int i = 0; i < 8; ++i)
-            if (i < ncg) rpre[i] = __ldg(p.res + (long long)i * p.res_plane_px + g);
-        }
+        for (int i = 0; i < 4; ++i)
+          if (i < ncg) rcur[i] = __ldg(p.res + (long long)i * p.res_plane_px + gbase);
       }
-      const long long e0 = clock64();
+      const long long e0 = prof ? clock64() : 0;
       mbar_wait(acc_full + 8 * rc.slot, rc.phase);
-      e_wait += clock64() - e0;
+      if (prof) e_wait += clock64() - e0;
       tc_fence_after();
-      for (int m = 0; m < p.mt; ++m) {
-        const unsigned g = (unsigned)(tile * tiles_px + m * kTileM + qd * 32 + lane);
-        const unsigned img = g / HW;
-        const unsigned rem = g - img * HW;
-        const unsigned y = rem / (unsigned)p.Wp, x = rem - y * (unsigned)p.Wp;
-        const bool valid = (long long)g < p.P && y < (unsigned)p.H && x < (unsigned)p.W;
-        const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16) + rc.slot * p.acc_cols + m * p.n;
-        long long o1 = 0;
-        int ph = 0;
-        if (p.out_mode == 1) {
-          ph = (int)((y & 1) * 2 + (x & 1));
-          o1 = (long long)img * (p.Hp2 * p.Wp2) + (y >> 1) * p.Wp2 + (x >> 1);
-        } else if (p.out_mode == 2) {
-          o1 = ((long long)(img * p.H + y) * p.W + x) * p.cout;
-        }
-        const bool has_res = p.res != nullptr && valid;
+      if (!(p.dbg & 1)) {
 #pragma unroll 1
-        for (int c0 = 0; c0 < p.n; c0 += 16) {
-          uint32_t v[16];
-          tmem_ld_x16(taddr + c0, v);
-          if (kStem) {  // 2x2 max-pool = elementwise max of the four phase accumulators
-#pragma unroll 1
-            for (int q = 1; q < 4; ++q) {
-              uint32_t u[16];
-              tmem_ld_wait();
-              tmem_ld_x16(taddr + q * p.n + c0, u);
-              tmem_ld_wait();
-#pragma unroll
-              for (int i = 0; i < 16; ++i) v[i] = __float_as_uint(fmaxf(__uint_as_float(v[i]), __uint_as_float(u[i])));
-            }
+        for (int m = 0; m < MT; ++m) {
+          const uint32_t g = gbase + m * kTileM;
+          const uint32_t img = fast_div(g, p.div_hw);
+          const uint32_t rem = g - img * p.div_hw.d;
+          const uint32_t y = fast_div(rem, p.div_wp), x = rem - y * p.div_wp.d;
+          const bool valid = (long long)g < p.P && y < (uint32_t)p.H && x < (uint32_t)p.W;
+          const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16) + rc.slot * p.acc_cols + m * p.n;
+          long long o1 = 0;
+          uint4* out_ph = nullptr;
+          if (p.out_mode == 1) {
+            out_ph = p.out_ph[(y & 1) * 2 + (x & 1)];
+            o1 = (long long)img * (p.Hp2 * p.Wp2) + (y >> 1) * p.Wp2 + (x >> 1);
+          } else if (p.out_mode == 2) {
+            o1 = ((long long)(img * p.H + y) * p.W + x) * p.cout;
           }
-          uint4 r[2];
-          if (has_res) {
+#pragma unroll 1
+          for (int sl = 0; sl < n_slabs; ++sl) {
+            const int c0 = sl << 5;
+            const bool wide = c0 + 32 <= p.n;
+            uint32_t v[32];
+            if (wide) tmem_ld_x32(taddr + c0, v);
+            else tmem_ld_x16(taddr + c0, *reinterpret_cast<uint32_t(*)[16]>(v));
+            if (kStem) {  // 2x2 max-pool = elementwise max of the four phase accumulators
+#pragma unroll 1
+              for (int q = 1; q < 4; ++q) {
+                uint32_t u[32];
+                tmem_ld_wait();
+                tmem_ld_x32(taddr + q * p.n + c0, u);
+                tmem_ld_wait();
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-              const int cg = (c0 >> 3) + h;
-              if (m == 0 && cg < 8) {
-                // select from the prefetched registers with compile-time indices
-#pragma unroll
-                for (int i = 0; i < 8; ++i)
-                  if (i == cg) r[h] = rpre[i];
-              } else if (cg < ncg) {
-                r[h] = __ldg(p.res + (long long)cg * p.res_plane_px + g);
+                for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(fmaxf(__uint_as_float(v[i]), __uint_as_float(u[i])));
               }
             }
-          }
-          tmem_ld_wait();
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const int cg = (c0 >> 3) + h;
-            if (cg >= ncg) break;
-            float o[8];
-            const float4 b0 = *reinterpret_cast<const float4*>(bias_s + cg * 8);
-            const float4 b1 = *reinterpret_cast<const float4*>(bias_s + cg * 8 + 4);
-            o[0] = __uint_as_float(v[h * 8 + 0]) + b0.x; o[1] = __uint_as_float(v[h * 8 + 1]) + b0.y;
-            o[2] = __uint_as_float(v[h * 8 + 2]) + b0.z; o[3] = __uint_as_float(v[h * 8 + 3]) + b0.w;
-            o[4] = __uint_as_float(v[h * 8 + 4]) + b1.x; o[5] = __uint_as_float(v[h * 8 + 5]) + b1.y;
-            o[6] = __uint_as_float(v[h * 8 + 6]) + b1.z; o[7] = __uint_as_float(v[h * 8 + 7]) + b1.w;
+            // prefetch the residual of the next slab (same sub-tile, or slab 0 of the next sub-tile)
             if (has_res) {
-              float a, b;
-              unpack2(r[h].x, p.fmt, a, b); o[0] += a; o[1] += b;
-              unpack2(r[h].y, p.fmt, a, b); o[2] += a; o[3] += b;
-              unpack2(r[h].z, p.fmt, a, b); o[4] += a; o[5] += b;
-              unpack2(r[h].w, p.fmt, a, b); o[6] += a; o[7] += b;
-            }
-            if (p.relu) {
+              const bool last_sl = sl + 1 == n_slabs;
+              if (!last_sl || m + 1 < MT) {
+                const int cgn = last_sl ? 0 : (c0 >> 3) + 4;
+                const uint32_t gn = last_sl ? g + kTileM : g;
 #pragma unroll
-              for (int i = 0; i < 8; ++i) o[i] = fmaxf(o[i], 0.f);
+                for (int i = 0; i < 4; ++i)
+                  if (cgn + i < ncg) rnext[i] = __ldg(p.res + (long long)(cgn + i) * p.res_plane_px + gn);
+              }
             }
-            if (p.out_mode == 2) {
-              if (valid) {
-                float4* op = reinterpret_cast<float4*>(p.out_f32 + o1 + cg * 8);
-                op[0] = make_float4(o[0], o[1], o[2], o[3]);
-                op[1] = make_float4(o[4], o[5], o[6], o[7]);
+            tmem_ld_wait();
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+              const int cg = (c0 >> 3) + h;
+              if (cg >= ncg || (!wide && h >= 2)) break;
+              float o[8];
+              const float4 b0 = *reinterpret_cast<const float4*>(bias_s + cg * 8);
+              const float4 b1 = *reinterpret_cast<const float4*>(bias_s + cg * 8 + 4);
+              o[0] = __uint_as_float(v[h * 8 + 0]) + b0.x; o[1] = __uint_as_float(v[h * 8 + 1]) + b0.y;
+              o[2] = __uint_as_float(v[h * 8 + 2]) + b0.z; o[3] = __uint_as_float(v[h * 8 + 3]) + b0.w;
+              o[4] = __uint_as_float(v[h * 8 + 4]) + b1.x; o[5] = __uint_as_float(v[h * 8 + 5]) + b1.y;
+              o[6] = __uint_as_float(v[h * 8 + 6]) + b1.z; o[7] = __uint_as_float(v[h * 8 + 7]) + b1.w;
+              if (has_res) {
+                float a, b;
+                unpack2(rcur[h].x, p.fmt, a, b); o[0] += a; o[1] += b;
+                unpack2(rcur[h].y, p.fmt, a, b); o[2] += a; o[3] += b;
+                unpack2(rcur[h].z, p.fmt, a, b); o[4] += a; o[5] += b;
+                unpack2(rcur[h].w, p.fmt, a, b); o[6] += a; o[7] += b;
               }
-            } else {
-              uint4 pk = make_uint4(0u, 0u, 0u, 0u);
-              if (valid) {
-                pk.x = pack2(o[0], o[1], p.fmt);
-                pk.y = pack2(o[2], o[3], p.fmt);
-                pk.z = pack2(o[4], o[5], p.fmt);
-                pk.w = pack2(o[6], o[7], p.fmt);
+              if (p.relu) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) o[i] = fmaxf(o[i], 0.f);
               }
-              if (p.out_mode == 0)
-                p.out[(long long)cg * p.out_plane_px + g] = pk;
-              else if (valid)
-                p.out_ph[ph][(long long)cg * p.out_ph_plane_px + o1] = pk;
+              if (p.out_mode == 2) {
+                if (valid) {
+                  float4* op = reinterpret_cast<float4*>(p.out_f32 + o1 + cg * 8);
+                  op[0] = make_float4(o[0], o[1], o[2], o[3]);
+                  op[1] = make_float4(o[4], o[5], o[6], o[7]);
+                }
+              } else {
+                uint4 pk = make_uint4(0u, 0u, 0u, 0u);
+                if (valid) {
+                  pk.x = pack2(o[0], o[1], p.fmt);
+                  pk.y = pack2(o[2], o[3], p.fmt);
+                  pk.z = pack2(o[4], o[5], p.fmt);
+                  pk.w = pack2(o[6], o[7], p.fmt);
+                }
+                if (p.out_mode == 0)
+                  p.out[(long long)cg * p.out_plane_px + g] = pk;
+                else if (valid)
+                  out_ph[(long long)cg * p.out_ph_plane_px + o1] = pk;
+              }
+            }
+            if (has_res) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i) rcur[i] = rnext[i];
             }
           }
         }
@@ -372,7 +396,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
       rc.advance(p.as);
       rc.advance(p.as);
     }
-    if (p.prof != nullptr && lane == 0 && qd == 0) {
+    if (prof && lane == 0 && qd == 0) {
       long long* o = p.prof + blockIdx.x * 16 + 8 + grp * 2;
       o[0] = clock64() - e_start; o[1] = e_wait;
     }
@@ -383,6 +407,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
     __syncwarp();
     tmem_dealloc(tmem_base, p.tmem_cols);
   }
+  if (p.prof != nullptr && threadIdx.x == 0) p.prof[blockIdx.x * 16 + 6] = (long long)globaltimer_ns();
 }
 
 // ------------------------------------------------------------------------------------------
@@ -671,7 +696,19 @@ struct ConvIo {
 };
 
 int g_mt_override = 0;
+
+// q = n / d as umulhi(n, magic) >> shift; exact for n < 2^23 and the divisors of this kernel
+Divider make_divider(uint32_t d) {
+  Divider dv;
+  const int s = d >= 256 ? 40 : 32;
+  const unsigned long long m = ((1ull << s) + d - 1) / d;
+  dv.magic = (uint32_t)m;
+  dv.shift = (uint32_t)(s - 32);
+  dv.d = d;
+  return dv;
+}
 long long* g_prof = nullptr;
+int g_prof_seq = -1;  // >= 0: launch k writes its counters at g_prof + k * 148 * 16
 
 // `out_level`: geometry of the OUTPUT (= geometry of the input for stride 1, = geometry of each
 // input phase image for stride 2).  `next`: geometry of the phase images written in mode 1.
@@ -683,11 +720,11 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   if (!attr_set) {
     cudaError_t e = cudaSuccess;
     const int lim = kSmemBudget + 4096;
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc_kernel<9, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc_kernel<9, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc_kernel<1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc_kernel<1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc_kernel<8, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
+#define AT_TC_ATTR(T, K, M) \
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc_kernel<T, K, M>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
+    AT_TC_ATTR(9, 2, 1) AT_TC_ATTR(9, 2, 2) AT_TC_ATTR(9, 2, 4) AT_TC_ATTR(9, 4, 1) AT_TC_ATTR(9, 4, 2) AT_TC_ATTR(9, 4, 4)
+    AT_TC_ATTR(1, 2, 1) AT_TC_ATTR(1, 4, 1) AT_TC_ATTR(1, 4, 2) AT_TC_ATTR(8, 1, 1)
+#undef AT_TC_ATTR
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(conv_tc_kernel): %s", cudaGetErrorString(e));
       return AT_ERR_CUDA;
@@ -739,6 +776,8 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   p.out_mode = io.out_mode; p.relu = io.relu ? 1 : 0; p.fmt = fmt;
   p.out_f32 = io.out_f32;
   p.prof = g_prof;
+  { const char* e = getenv("AT_TC_DBG"); p.dbg = e ? atoi(e) : 0; }
+  if (g_prof != nullptr && g_prof_seq >= 0) p.prof = g_prof + (long long)(g_prof_seq++) * kNumSMs * 16;
   if (io.out_mode == 1) {
     for (int s = 0; s < 4; ++s) p.out_ph[s] = io.out + s * io.out_phase_units;
     p.out_ph_plane_px = io.out_plane_px;
@@ -755,6 +794,9 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   }
   if (g_mt_override > 0) mt = g_mt_override;
   if (p.n_src > 1 || is_stem) mt = 1;  // the 4-phase stride-2 inputs already fill the A ring
+  if (mt == 3) mt = 2;
+  if (mt > 4) mt = 4;
+  if (taps == 1 && mt > (p.kc == 64 ? 2 : 1)) mt = p.kc == 64 ? 2 : 1;
   while (mt > 1 && round_up(mt * p.n, 32) > 512) mt >>= 1;
   const int nblocks = p.n_kchunks * taps;
   const int64_t misc = 4096;
@@ -799,13 +841,18 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   const int grid = (int)std::min<long long>(p.n_tiles, kNumSMs);
   if (grid == 0) return AT_OK;
   const int ksteps = p.kc >> 4;
-  if (is_stem) conv_tc_kernel<8, 1><<<grid, kThreads, smem_bytes, stream>>>(p);
-  else if (taps == 9 && ksteps == 2) conv_tc_kernel<9, 2><<<grid, kThreads, smem_bytes, stream>>>(p);
-  else if (taps == 9 && ksteps == 4) conv_tc_kernel<9, 4><<<grid, kThreads, smem_bytes, stream>>>(p);
-  else if (taps == 1 && ksteps == 2) conv_tc_kernel<1, 2><<<grid, kThreads, smem_bytes, stream>>>(p);
-  else if (taps == 1 && ksteps == 4) conv_tc_kernel<1, 4><<<grid, kThreads, smem_bytes, stream>>>(p);
-  else {
-    set_error("conv_tc: unsupported taps=%d kc=%d", taps, p.kc);
+  p.div_hw = make_divider((uint32_t)(OL.Hp * OL.Wp));
+  p.div_wp = make_divider((uint32_t)OL.Wp);
+  bool launched = true;
+#define AT_TC_CASE(T, K, M) \
+  else if (taps == T && ksteps == K && mt == M) conv_tc_kernel<T, K, M><<<grid, kThreads, smem_bytes, stream>>>(p);
+  if (is_stem) conv_tc_kernel<8, 1, 1><<<grid, kThreads, smem_bytes, stream>>>(p);
+  AT_TC_CASE(9, 2, 1) AT_TC_CASE(9, 2, 2) AT_TC_CASE(9, 2, 4) AT_TC_CASE(9, 4, 1) AT_TC_CASE(9, 4, 2) AT_TC_CASE(9, 4, 4)
+  AT_TC_CASE(1, 2, 1) AT_TC_CASE(1, 4, 1) AT_TC_CASE(1, 4, 2)
+  else launched = false;
+#undef AT_TC_CASE
+  if (!launched) {
+    set_error("conv_tc: unsupported taps=%d kc=%d mt=%d", taps, p.kc, mt);
     return AT_ERR_UNSUPPORTED;
   }
   return check_launch("conv_tc_kernel");
@@ -984,7 +1031,8 @@ extern "C" int at_model_prepack_bf16(const float* blob, void* bf16_blob, void* s
 // in [n,H,W,cin] -> out [n,Ho,Wo,cout]; res (optional) [n,Ho,Wo,cout].  workspace: at_debug_conv_tc_workspace_bytes.
 /* Debug: when non-NULL every conv_tc launch writes [148][16] cycle counters there
  * (MMA warp: total, wait acc_empty, wait a_full, wait w_full, tiles; epilogue groups at +8: total, wait). */
-extern "C" void at_debug_set_prof(long long* dev_ptr) { at::tc::g_prof = dev_ptr; }
+extern "C" void at_debug_set_prof(long long* dev_ptr) { at::tc::g_prof = dev_ptr; at::tc::g_prof_seq = -1; }
+extern "C" void at_debug_set_prof_seq(long long* dev_ptr) { at::tc::g_prof = dev_ptr; at::tc::g_prof_seq = 0; }
 
 extern "C" int64_t at_debug_conv_tc_workspace_bytes(int n_img, int H, int W) {
   using namespace at;

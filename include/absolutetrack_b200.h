@@ -163,6 +163,7 @@ int at_debug_conv_tc(const float* blob, const void* tc_blob, int layer_id, const
                      int64_t workspace_bytes, void* stream);
 
 void at_debug_set_prof(long long* dev_ptr); /* debug: per-CTA cycle counters of conv_tc launches */
+void at_debug_set_prof_seq(long long* dev_ptr); /* debug: same, launch k of the sequence writes at dev_ptr + k*148*16 */
 
 /* Recurrent state of SimpleConvRNN (temporal.py:41-42,105-125), owned by the caller. */
 typedef struct AtTemporalState {

@@ -29,6 +29,13 @@ for lid, n_img, H, use_res in cases:
         lib.at_debug_set_prof(None)
         torch.cuda.synchronize()
     assert rc == 0, lib.at_last_error_string()
+    P = prof.double()
+    span = (P[:, 6].max() - P[:, 5].min()).item() / 1e3
+    skew = (P[:, 5].max() - P[:, 5].min()).item() / 1e3
+    pro = (P[:, 7] - P[:, 5]).mean().item() / 1e3
+    endskew = (P[:, 6].max() - P[:, 6].min()).item() / 1e3
+    mm = P[:, 0]
+    print(f"   span={span:.1f}us start_skew={skew:.1f}us prologue={pro:.1f}us end_skew={endskew:.1f}us mma_total min/mean/max={mm.min().item()/1.9e3:.1f}/{mm.mean().item()/1.9e3:.1f}/{mm.max().item()/1.9e3:.1f}us")
     p = prof.double().mean(0).tolist()
     tiles = p[4]
     flops = 2.0 * n_img * Ho * Ho * L["cout"] * L["cin"] * L["ksize"] ** 2

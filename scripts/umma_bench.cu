@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(128, 1) bench(int mode, int n, int iters, int 
     if (elect_one()) {
       for (int i = 0; i < iters; i += 8) {
 #pragma unroll
-        for (int u = 0; u < 8; ++u) umma_f16(tm + (u & 1) * n, ad, bd, idesc, 1);
+        for (int u = 0; u < 8; ++u) umma_f16(tm + (u & (nacc - 1)) * n, ad, bd, idesc, 1);
       }
       umma_commit(smem_u32(&bar));
     }
@@ -109,14 +109,15 @@ int main() {
   long long* d; cudaMalloc(&d, 8);
   cudaFuncSetAttribute(bench, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   const int iters = 1800;
-  for (int mode : {0, 2})
+  for (int mode : {0})
     for (int n : {32, 64, 128, 256})
-      for (int style : {1, 2, 3}) {
-        const int nacc = 2;
+      for (int nacc : {1, 2, 4})
+      for (int style : {2, 3}) {
+        if (nacc * n > 512) continue;
         bench<<<148, 128, 200 * 1024>>>(mode, n, iters, nacc, style, d);
         cudaError_t e = cudaDeviceSynchronize();
         long long h = 0; cudaMemcpy(&h, d, 8, cudaMemcpyDeviceToHost);
-        printf("mode %d n %3d style %d: %8.1f cycles/MMA (floor %d)  %s\n", mode, n, style, (double)h / iters, n / 2,
+        printf("nacc %d mode %d n %3d style %d: %8.1f cycles/MMA (floor %d)  %s\n", nacc, mode, n, style, (double)h / iters, n / 2,
                e == cudaSuccess ? "" : cudaGetErrorString(e));
       }
   return 0;

@@ -28,6 +28,7 @@
 #include <mutex>
 #include <stdlib.h>
 #include <string.h>
+#include <vector>
 
 #include "conv.cuh"
 #include "tc_ptx.cuh"
@@ -70,6 +71,7 @@ struct ConvTcParams {
   uint32_t smem_a_off, smem_w_off, smem_bias_off, smem_bar_off;
   uint32_t a_slot_bytes, a_plane_bytes, w_block_bytes, tmem_cols, acc_cols;
   Divider div_hw, div_wp;  // g / (Hp*Wp), rem / Wp
+  int slab_shift;          // log2(32-column slabs per accumulator) (0 when not a power of two: MT == 1 then)
   long long* prof;  // optional [grid][16] cycle counters (debug)
   int dbg;          // debug knobs (AT_TC_DBG): 1 no epilogue, 2 no A copies
 };
@@ -93,7 +95,9 @@ struct EpiCoord {
   int ph;
 };
 
-template <int NTAPS, int KSTEPS, int MT>
+// MODE: 0 planar out, 1 planar out + residual, 2 phase-split out + residual, 3 fp32 NHWC out.
+// WRES: the layer's weights stay resident in shared memory (else they stream through a ring).
+template <int NTAPS, int KSTEPS, int MT, int WRES, int MODE>
 __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   using namespace ptx;
@@ -137,7 +141,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
     if (lane == 0) {  // ---------------- weight producer
       const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(p.w);
       const int nblocks = nk * NTAPS;
-      if (p.w_resident) {
+      if (WRES) {
         if (n_my > 0)
           for (int b = 0; b < nblocks; ++b) {
             mbar_expect_tx(w_full + 8 * b, p.w_block_bytes);
@@ -174,8 +178,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
       tap_off[t] = ((uint32_t)p.tap_src[t] * kPlanesPerChunk * p.a_plane_bytes >> 4) + (uint32_t)(p.tap_shift[t] - p.min_shift);
     Ring ra, rw, rc;
     long long t_acc = 0, t_a = 0, t_w = 0, t_start = clock64(), t0;
-    const bool prof = p.prof != nullptr;
-    if (prof && lane == 0) p.prof[blockIdx.x * 16 + 7] = (long long)globaltimer_ns();
+    const bool prof = p.prof != nullptr && (p.dbg & 16);
+    if (p.prof != nullptr && lane == 0) p.prof[blockIdx.x * 16 + 7] = (long long)globaltimer_ns();
     for (int it = 0; it < n_my; ++it) {
       if (prof) t0 = clock64();
       mbar_wait(acc_empty + 8 * rc.slot, rc.phase ^ 1u);
@@ -189,7 +193,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
         tc_fence_after();
         const uint32_t a_lo = a_lo0 + ra.slot * a_slot16;
         const uint32_t acc0 = kci != 0;
-        if (p.w_resident) {
+        if (WRES) {
           if (it == 0) {
             for (int t = 0; t < NTAPS; ++t) mbar_wait(w_full + 8 * (kci * NTAPS + t), 0);
             tc_fence_after();
@@ -245,7 +249,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
       __syncwarp();
       rc.advance(p.as);
     }
-    if (prof && lane == 0) {
+    if (p.prof != nullptr && lane == 0) {
       long long* o = p.prof + blockIdx.x * 16;
       o[0] = clock64() - t_start; o[1] = t_acc; o[2] = t_a; o[3] = t_w; o[4] = n_my;
     }
@@ -255,7 +259,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
       for (int it = 0; it < n_my; ++it) {
         const long long g0 = (long long)(first_tile + it * (int)gridDim.x) * kTilePx + p.min_shift;
         for (int kci = 0; kci < nk; ++kci) {
-          mbar_wait(a_empty + 8 * ra.slot, ra.phase ^ 1u);
+          if (p.dbg & 8) mbar_wait_sleep(a_empty + 8 * ra.slot, ra.phase ^ 1u, 100);
+          else mbar_wait(a_empty + 8 * ra.slot, ra.phase ^ 1u);
           if ((p.dbg & 2) && (it > 0 || kci >= p.ra)) { mbar_arrive(a_full + 8 * ra.slot); ra.advance(p.ra); continue; }
           mbar_expect_tx(a_full + 8 * ra.slot, p.a_slot_bytes);
           uint32_t dst = sbase + p.smem_a_off + ra.slot * p.a_slot_bytes;
@@ -274,45 +279,68 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
     Ring rc;
     if (grp == 1) rc.advance(p.as);
     long long e_wait = 0, e_start = clock64();
-    const bool prof = p.prof != nullptr;
+    const bool prof = p.prof != nullptr && (p.dbg & 16);
     const int ncg = (p.cout + 7) >> 3;
-    const bool has_res = p.res != nullptr;
+    constexpr bool has_res = MODE == 1 || MODE == 2;
+    constexpr int out_mode = MODE == 2 ? 1 : (MODE == 3 ? 2 : 0);
     const int n_slabs = (p.n + 31) >> 5;  // 32-column slabs (the last one may hold 16)
+    const int S = MT * n_slabs;           // slabs of one tile in flat order f = m * n_slabs + sl
+    // Residual ring: 4 slots of one slab (4 channel groups x 16 B per lane).  Slot f & 3 holds flat
+    // slab f; after slab f is consumed the slot is refilled with slab f + 4 of the same tile or,
+    // past the end, with the matching slab of this group's NEXT tile, so every global load is
+    // issued at least 4 slabs (usually one whole tile) before its use.  Needs S < 4 or S % 4 == 0,
+    // which holds for every residual layer (n_slabs is 1, 2, 4 or 8).  Pads and the tail behind
+    // the last image are readable (zeros / finite stale data) and masked by `valid` below.
+    uint4 rr[4][4];
+    auto res_load = [&](uint4 (&dst)[4], uint32_t tile_gbase, int f) {
+      const int m = f >> p.slab_shift, sl = f - (m << p.slab_shift);
+      const uint32_t g = tile_gbase + m * kTileM;
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        if (sl * 4 + i < ncg) dst[i] = __ldg(p.res + (long long)(sl * 4 + i) * p.res_plane_px + g);
+    };
+    if (has_res && grp < n_my) {
+      const uint32_t gb = (uint32_t)(first_tile + grp * (int)gridDim.x) * kTilePx + qd * 32 + lane;
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (k < S) res_load(rr[k], gb, k);
+    }
     for (int it = grp; it < n_my; it += 2) {
       const int tile = first_tile + it * (int)gridDim.x;
       const uint32_t gbase = (uint32_t)tile * kTilePx + qd * 32 + lane;
-      // residual of the first slab: issued BEFORE waiting for the accumulator so that the
-      // global-load latency hides behind the MMAs of this tile.  Pads / the tail behind the
-      // last image are readable (zeros or stale finite data) and masked by `valid` below.
-      uint4 rcur[4], rnext[4];
-      if (has_res) {
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-          if (i < ncg) rcur[i] = __ldg(p.res + (long long)i * p.res_plane_px + gbase);
-      }
+      const bool has_next = it + 2 < n_my;
+      const uint32_t gbase_next = gbase + 2u * gridDim.x * kTilePx;
       const long long e0 = prof ? clock64() : 0;
       mbar_wait(acc_full + 8 * rc.slot, rc.phase);
       if (prof) e_wait += clock64() - e0;
       tc_fence_after();
       if (!(p.dbg & 1)) {
+        bool valid = false;
+        uint32_t g = 0, taddr = 0;
+        long long o1 = 0;
+        uint4* out_ph = nullptr;
 #pragma unroll 1
-        for (int m = 0; m < MT; ++m) {
-          const uint32_t g = gbase + m * kTileM;
-          const uint32_t img = fast_div(g, p.div_hw);
-          const uint32_t rem = g - img * p.div_hw.d;
-          const uint32_t y = fast_div(rem, p.div_wp), x = rem - y * p.div_wp.d;
-          const bool valid = (long long)g < p.P && y < (uint32_t)p.H && x < (uint32_t)p.W;
-          const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16) + rc.slot * p.acc_cols + m * p.n;
-          long long o1 = 0;
-          uint4* out_ph = nullptr;
-          if (p.out_mode == 1) {
-            out_ph = p.out_ph[(y & 1) * 2 + (x & 1)];
-            o1 = (long long)img * (p.Hp2 * p.Wp2) + (y >> 1) * p.Wp2 + (x >> 1);
-          } else if (p.out_mode == 2) {
-            o1 = ((long long)(img * p.H + y) * p.W + x) * p.cout;
-          }
-#pragma unroll 1
-          for (int sl = 0; sl < n_slabs; ++sl) {
+        for (int f0 = 0; f0 < S; f0 += 4) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int f = f0 + k;
+            if (f >= S) break;
+            const int m = MT == 1 ? 0 : f >> p.slab_shift;
+            const int sl = MT == 1 ? f : f - (m << p.slab_shift);
+            if (sl == 0) {  // new sub-tile: decode the pixel of this lane
+              g = gbase + m * kTileM;
+              const uint32_t img = fast_div(g, p.div_hw);
+              const uint32_t rem = g - img * p.div_hw.d;
+              const uint32_t y = fast_div(rem, p.div_wp), x = rem - y * p.div_wp.d;
+              valid = (long long)g < p.P && y < (uint32_t)p.H && x < (uint32_t)p.W;
+              taddr = tmem_base + ((uint32_t)(qd * 32) << 16) + rc.slot * p.acc_cols + m * p.n;
+              if (out_mode == 1) {
+                out_ph = p.out_ph[(y & 1) * 2 + (x & 1)];
+                o1 = (long long)img * (p.Hp2 * p.Wp2) + (y >> 1) * p.Wp2 + (x >> 1);
+              } else if (out_mode == 2) {
+                o1 = ((long long)(img * p.H + y) * p.W + x) * p.cout;
+              }
+            }
             const int c0 = sl << 5;
             const bool wide = c0 + 32 <= p.n;
             uint32_t v[32];
@@ -329,63 +357,61 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                 for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(fmaxf(__uint_as_float(v[i]), __uint_as_float(u[i])));
               }
             }
-            // prefetch the residual of the next slab (same sub-tile, or slab 0 of the next sub-tile)
-            if (has_res) {
-              const bool last_sl = sl + 1 == n_slabs;
-              if (!last_sl || m + 1 < MT) {
-                const int cgn = last_sl ? 0 : (c0 >> 3) + 4;
-                const uint32_t gn = last_sl ? g + kTileM : g;
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                  if (cgn + i < ncg) rnext[i] = __ldg(p.res + (long long)(cgn + i) * p.res_plane_px + gn);
-              }
-            }
             tmem_ld_wait();
+            uint4 pk[4];
 #pragma unroll
             for (int h = 0; h < 4; ++h) {
               const int cg = (c0 >> 3) + h;
-              if (cg >= ncg || (!wide && h >= 2)) break;
               float o[8];
-              const float4 b0 = *reinterpret_cast<const float4*>(bias_s + cg * 8);
-              const float4 b1 = *reinterpret_cast<const float4*>(bias_s + cg * 8 + 4);
+              const float4 b0 = *reinterpret_cast<const float4*>(bias_s + (cg < ncg ? cg : 0) * 8);
+              const float4 b1 = *reinterpret_cast<const float4*>(bias_s + (cg < ncg ? cg : 0) * 8 + 4);
               o[0] = __uint_as_float(v[h * 8 + 0]) + b0.x; o[1] = __uint_as_float(v[h * 8 + 1]) + b0.y;
               o[2] = __uint_as_float(v[h * 8 + 2]) + b0.z; o[3] = __uint_as_float(v[h * 8 + 3]) + b0.w;
               o[4] = __uint_as_float(v[h * 8 + 4]) + b1.x; o[5] = __uint_as_float(v[h * 8 + 5]) + b1.y;
               o[6] = __uint_as_float(v[h * 8 + 6]) + b1.z; o[7] = __uint_as_float(v[h * 8 + 7]) + b1.w;
               if (has_res) {
                 float a, b;
-                unpack2(rcur[h].x, p.fmt, a, b); o[0] += a; o[1] += b;
-                unpack2(rcur[h].y, p.fmt, a, b); o[2] += a; o[3] += b;
-                unpack2(rcur[h].z, p.fmt, a, b); o[4] += a; o[5] += b;
-                unpack2(rcur[h].w, p.fmt, a, b); o[6] += a; o[7] += b;
+                unpack2(rr[k][h].x, p.fmt, a, b); o[0] += a; o[1] += b;
+                unpack2(rr[k][h].y, p.fmt, a, b); o[2] += a; o[3] += b;
+                unpack2(rr[k][h].z, p.fmt, a, b); o[4] += a; o[5] += b;
+                unpack2(rr[k][h].w, p.fmt, a, b); o[6] += a; o[7] += b;
               }
               if (p.relu) {
 #pragma unroll
                 for (int i = 0; i < 8; ++i) o[i] = fmaxf(o[i], 0.f);
               }
-              if (p.out_mode == 2) {
-                if (valid) {
+              if (out_mode == 2) {
+                if (valid && cg < ncg && (wide || h < 2)) {
                   float4* op = reinterpret_cast<float4*>(p.out_f32 + o1 + cg * 8);
                   op[0] = make_float4(o[0], o[1], o[2], o[3]);
                   op[1] = make_float4(o[4], o[5], o[6], o[7]);
                 }
               } else {
-                uint4 pk = make_uint4(0u, 0u, 0u, 0u);
+                pk[h] = make_uint4(0u, 0u, 0u, 0u);
                 if (valid) {
-                  pk.x = pack2(o[0], o[1], p.fmt);
-                  pk.y = pack2(o[2], o[3], p.fmt);
-                  pk.z = pack2(o[4], o[5], p.fmt);
-                  pk.w = pack2(o[6], o[7], p.fmt);
+                  pk[h].x = pack2(o[0], o[1], p.fmt);
+                  pk[h].y = pack2(o[2], o[3], p.fmt);
+                  pk[h].z = pack2(o[4], o[5], p.fmt);
+                  pk[h].w = pack2(o[6], o[7], p.fmt);
                 }
-                if (p.out_mode == 0)
-                  p.out[(long long)cg * p.out_plane_px + g] = pk;
-                else if (valid)
-                  out_ph[(long long)cg * p.out_ph_plane_px + o1] = pk;
               }
             }
+            // refill this ring slot before the stores go out
             if (has_res) {
+              if (f + 4 < S) res_load(rr[k], gbase, f + 4);
+              else if (has_next) res_load(rr[k], gbase_next, S >= 4 ? f + 4 - S : f);
+            }
+            if (out_mode != 2) {
 #pragma unroll
-              for (int i = 0; i < 4; ++i) rcur[i] = rnext[i];
+              for (int h = 0; h < 4; ++h) {
+                const int cg = (c0 >> 3) + h;
+                if (cg < ncg && (wide || h < 2)) {
+                  if (out_mode == 0)
+                    p.out[(long long)cg * p.out_plane_px + g] = pk[h];
+                  else if (valid)
+                    out_ph[(long long)cg * p.out_ph_plane_px + o1] = pk[h];
+                }
+              }
             }
           }
         }
@@ -396,7 +422,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
       rc.advance(p.as);
       rc.advance(p.as);
     }
-    if (prof && lane == 0 && qd == 0) {
+    if (p.prof != nullptr && lane == 0 && qd == 0) {
       long long* o = p.prof + blockIdx.x * 16 + 8 + grp * 2;
       o[0] = clock64() - e_start; o[1] = e_wait;
     }
@@ -716,21 +742,6 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
                    const ConvIo& io, int fmt, cudaStream_t stream) {
   const ConvLayer& L = layer_table()[layer_id];
   const TcLayer& T = tc_table()[layer_id];
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaSuccess;
-    const int lim = kSmemBudget + 4096;
-#define AT_TC_ATTR(T, K, M) \
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc_kernel<T, K, M>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
-    AT_TC_ATTR(9, 2, 1) AT_TC_ATTR(9, 2, 2) AT_TC_ATTR(9, 2, 4) AT_TC_ATTR(9, 4, 1) AT_TC_ATTR(9, 4, 2) AT_TC_ATTR(9, 4, 4)
-    AT_TC_ATTR(1, 2, 1) AT_TC_ATTR(1, 4, 1) AT_TC_ATTR(1, 4, 2) AT_TC_ATTR(8, 1, 1)
-#undef AT_TC_ATTR
-    if (e != cudaSuccess) {
-      set_error("cudaFuncSetAttribute(conv_tc_kernel): %s", cudaGetErrorString(e));
-      return AT_ERR_CUDA;
-    }
-    attr_set = true;
-  }
   ConvTcParams p;
   memset(&p, 0, sizeof(p));
   const bool is_stem = layer_id == L_STEM;
@@ -794,9 +805,8 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   }
   if (g_mt_override > 0) mt = g_mt_override;
   if (p.n_src > 1 || is_stem) mt = 1;  // the 4-phase stride-2 inputs already fill the A ring
-  if (mt == 3) mt = 2;
-  if (mt > 4) mt = 4;
-  if (taps == 1 && mt > (p.kc == 64 ? 2 : 1)) mt = p.kc == 64 ? 2 : 1;
+  if (mt > 2) mt = 2;
+  if (taps == 1) mt = 1;
   while (mt > 1 && round_up(mt * p.n, 32) > 512) mt >>= 1;
   const int nblocks = p.n_kchunks * taps;
   const int64_t misc = 4096;
@@ -843,18 +853,50 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   const int ksteps = p.kc >> 4;
   p.div_hw = make_divider((uint32_t)(OL.Hp * OL.Wp));
   p.div_wp = make_divider((uint32_t)OL.Wp);
-  bool launched = true;
-#define AT_TC_CASE(T, K, M) \
-  else if (taps == T && ksteps == K && mt == M) conv_tc_kernel<T, K, M><<<grid, kThreads, smem_bytes, stream>>>(p);
-  if (is_stem) conv_tc_kernel<8, 1, 1><<<grid, kThreads, smem_bytes, stream>>>(p);
-  AT_TC_CASE(9, 2, 1) AT_TC_CASE(9, 2, 2) AT_TC_CASE(9, 2, 4) AT_TC_CASE(9, 4, 1) AT_TC_CASE(9, 4, 2) AT_TC_CASE(9, 4, 4)
-  AT_TC_CASE(1, 2, 1) AT_TC_CASE(1, 4, 1) AT_TC_CASE(1, 4, 2)
-  else launched = false;
-#undef AT_TC_CASE
-  if (!launched) {
-    set_error("conv_tc: unsupported taps=%d kc=%d mt=%d", taps, p.kc, mt);
+  {
+    const int n_slabs = (p.n + 31) / 32;
+    p.slab_shift = 0;
+    while ((1 << p.slab_shift) < n_slabs) ++p.slab_shift;
+    if ((1 << p.slab_shift) != n_slabs && (mt > 1 || io.res != nullptr)) {
+      set_error("conv_tc: layer %s: %d slabs per accumulator need mt == 1 and no residual", L.name, n_slabs);
+      return AT_ERR_UNSUPPORTED;
+    }
+  }
+  const int mode = io.out_mode == 2 ? 3 : (io.res != nullptr ? (io.out_mode == 1 ? 2 : 1) : 0);
+  if (io.out_mode == 1 && io.res == nullptr) {
+    set_error("conv_tc: phase-split output without a residual is not instantiated");
     return AT_ERR_UNSUPPORTED;
   }
+  using Kernel = void (*)(const ConvTcParams);
+  Kernel fn = nullptr;
+#define AT_TC_CASE(T, K, M, R, O) \
+  if (taps == T && ksteps == K && mt == M && p.w_resident == R && mode == O) fn = conv_tc_kernel<T, K, M, R, O>;
+#define AT_TC_CASE3(T, K, M, R) AT_TC_CASE(T, K, M, R, 0) AT_TC_CASE(T, K, M, R, 1) AT_TC_CASE(T, K, M, R, 2)
+  AT_TC_CASE(8, 1, 1, 1, 0)
+  AT_TC_CASE3(9, 2, 1, 1) AT_TC_CASE3(9, 2, 2, 1)
+  AT_TC_CASE3(9, 4, 1, 1) AT_TC_CASE3(9, 4, 2, 1)
+  AT_TC_CASE3(9, 4, 1, 0) AT_TC_CASE3(9, 4, 2, 0)
+  AT_TC_CASE(1, 2, 1, 1, 0) AT_TC_CASE(1, 4, 1, 1, 0) AT_TC_CASE(1, 4, 1, 1, 3)
+#undef AT_TC_CASE3
+#undef AT_TC_CASE
+  if (fn == nullptr) {
+    set_error("conv_tc: no kernel for taps=%d kc=%d mt=%d resident=%d mode=%d", taps, p.kc, mt, p.w_resident, mode);
+    return AT_ERR_UNSUPPORTED;
+  }
+  {
+    static std::mutex mu;
+    static std::vector<Kernel> configured;
+    std::lock_guard<std::mutex> lock(mu);
+    if (std::find(configured.begin(), configured.end(), fn) == configured.end()) {
+      cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget + 4096);
+      if (e != cudaSuccess) {
+        set_error("cudaFuncSetAttribute(conv_tc_kernel): %s", cudaGetErrorString(e));
+        return AT_ERR_CUDA;
+      }
+      configured.push_back(fn);
+    }
+  }
+  fn<<<grid, kThreads, smem_bytes, stream>>>(p);
   return check_launch("conv_tc_kernel");
 }
 

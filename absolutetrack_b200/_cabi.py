@@ -115,6 +115,8 @@ SIGNATURES = {
     "at_debug_conv_tc": (_I, [_VP, _VP, _I, _VP, _I, _I, _I, _VP, _I, _I, _I, _VP, _VP, _I64, _VP]),
     "at_encoder_workspace_bytes": (_I64, [_I, _I]),
     "at_encoder_forward": (_I, [_VP, _VP, _VP, _I, _I, _VP, _VP, _I64, _I, _VP]),
+    "at_encoder_chunk_crops": (_I, []),
+    "at_encoder_forward_prepared": (_I, [_VP, _VP, _VP, _I, _I, _VP, _VP, _I64, _I, _I, _VP]),
     "at_tail_workspace_bytes": (_I64, [_I]),
     "at_tail_forward": (
         _I,

@@ -110,6 +110,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
   const uint32_t tmem_slot = acc_empty + 8 * p.as;
   float* bias_s = reinterpret_cast<float*>(smem + p.smem_bias_off);
   if (p.prof != nullptr && threadIdx.x == 0) p.prof[blockIdx.x * 16 + 5] = (long long)globaltimer_ns();
+  // programmatic dependent launch: the next conv of the stream may start its prologue (barriers,
+  // TMEM, bias, resident weights: nothing that depends on this grid) as soon as SMs free up
+  pdl_launch_dependents();
 
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < p.ra; ++i) { mbar_init(a_full + 8 * i, 1); mbar_init(a_empty + 8 * i, 1); }
@@ -256,6 +259,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
   } else if (warp == 2) {
     if (lane == 0) {  // ---------------- activation producer
       Ring ra;
+      pdl_wait();  // the previous layer's output must be complete before the first load
       for (int it = 0; it < n_my; ++it) {
         const long long g0 = (long long)(first_tile + it * (int)gridDim.x) * kTilePx + p.min_shift;
         for (int kci = 0; kci < nk; ++kci) {
@@ -292,6 +296,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
     // which holds for every residual layer (n_slabs is 1, 2, 4 or 8).  Pads and the tail behind
     // the last image are readable (zeros / finite stale data) and masked by `valid` below.
     uint4 rr[4][4];
+    pdl_wait();  // before the first residual load / output store
     auto res_load = [&](uint4 (&dst)[4], uint32_t tile_gbase, int f) {
       const int m = f >> p.slab_shift, sl = f - (m << p.slab_shift);
       const uint32_t g = tile_gbase + m * kTileM;
@@ -795,7 +800,8 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
     p.Hp2 = next->Hp; p.Wp2 = next->Wp;
   }
   // tile / ring configuration
-  int mt = 1;
+  // sub-tiles (128 pixels each) per tile: measured best per shape on B200 (scripts/tc_prof.py)
+  int mt = p.n == 64 ? (io.res != nullptr ? 1 : 2) : (p.n <= 128 ? 2 : 1);
   {
     // experiment knobs: AT_TC_MT<N> = sub-tiles per tile for layers with padded Cout == N
     char name[32];
@@ -807,7 +813,7 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   if (p.n_src > 1 || is_stem) mt = 1;  // the 4-phase stride-2 inputs already fill the A ring
   if (mt > 2) mt = 2;
   if (taps == 1) mt = 1;
-  while (mt > 1 && round_up(mt * p.n, 32) > 512) mt >>= 1;
+  while (mt > 1 && round_up(mt * p.n, 32) > 256) mt >>= 1;  // keep >= 2 accumulator stages
   const int nblocks = p.n_kchunks * taps;
   const int64_t misc = 4096;
   int64_t w_bytes = 0, ra = 0;
@@ -896,7 +902,26 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
       configured.push_back(fn);
     }
   }
-  fn<<<grid, kThreads, smem_bytes, stream>>>(p);
+  {
+    static const bool use_pdl = getenv("AT_TC_PDL") == nullptr || atoi(getenv("AT_TC_PDL")) != 0;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = smem_bytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = use_pdl ? 1 : 0;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, fn, p);
+    if (e != cudaSuccess) {
+      count_launch();
+      set_error("conv_tc_kernel launch: %s", cudaGetErrorString(e));
+      return AT_ERR_CUDA;
+    }
+  }
   return check_launch("conv_tc_kernel");
 }
 
@@ -936,28 +961,47 @@ Plan make_plan(long long nc) {
 
 }  // namespace tc
 
+int encoder_chunk_crops() { return tc::kChunkCrops; }
+
 int64_t encoder_workspace_bytes_bf16(int c) {
   const long long nc = c < tc::kChunkCrops ? (c > 0 ? c : 1) : tc::kChunkCrops;
   return tc::make_plan(nc).total_units * 16 + 256;
 }
 
+// Zero what the kernels rely on but never write: the guard in front of every plane (the top /
+// left padding of the first image) and the pad cells of the phase-split buffers.
+int encoder_prepare_workspace(void* workspace, long long nc, cudaStream_t s) {
+  using namespace tc;
+  uint4* ws = reinterpret_cast<uint4*>(round_up((int64_t)(uintptr_t)workspace, 128));
+  const Plan P = make_plan(nc);
+  int rc;
+  for (int l = 0; l < 4; ++l)
+    if ((rc = zero_halo(ws + P.off_lv[l], 4 * P.lv[l].planes(), P.lv[l], false, s))) return rc;
+  for (int l = 0; l < 3; ++l) {
+    Level ph = make_level(P.lv[l + 1].H, P.lv[l + 1].W, P.lv[l].C, nc);
+    if ((rc = zero_halo(ws + P.off_ps[l], 4 * ph.planes(), ph, true, s))) return rc;
+  }
+  return AT_OK;
+}
+
+// prepared_c > 0: the caller guarantees that the workspace was prepared for prepared_c crops per
+// chunk (encoder_prepare_workspace) and only written by this function since.
 int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* crops, int crop_dtype, int c, float* features,
-                         void* workspace, int64_t workspace_bytes, int fmt, cudaStream_t s) {
+                         void* workspace, int64_t workspace_bytes, int fmt, int prepared_c, cudaStream_t s) {
   using namespace tc;
   const ConvLayer* T = layer_table();
+  (void)T;
   uint4* ws = reinterpret_cast<uint4*>(round_up((int64_t)(uintptr_t)workspace, 128));
   for (int c0 = 0; c0 < c; c0 += kChunkCrops) {
     const long long nc = std::min(c - c0, kChunkCrops);
     const Plan P = make_plan(nc);
     int rc;
-    // zero guards (and the pads of the phase-split buffers, which the epilogue does not touch)
-    for (int l = 0; l < 4; ++l)
-      if ((rc = zero_halo(ws + P.off_lv[l], 4 * P.lv[l].planes(), P.lv[l], false, s))) return rc;
-    Level phl[3];
-    for (int l = 0; l < 3; ++l) {
-      phl[l] = make_level(P.lv[l + 1].H, P.lv[l + 1].W, P.lv[l].C, nc);
-      if ((rc = zero_halo(ws + P.off_ps[l], 4 * phl[l].planes(), phl[l], true, s))) return rc;
+    if (nc != prepared_c) {
+      if ((rc = encoder_prepare_workspace(workspace, nc, s))) return rc;
+      prepared_c = (int)nc;
     }
+    Level phl[3];
+    for (int l = 0; l < 3; ++l) phl[l] = make_level(P.lv[l + 1].H, P.lv[l + 1].W, P.lv[l].C, nc);
     auto buf = [&](int l, int i) { return ws + P.off_lv[l] + i * P.buf_units[l] + P.lv[l].guard; };
     // stem: pack the crops into the 2x2-block plane S (first plane of the unused D buffer of
     // level 0), then the stem GEMM writes X of level 0

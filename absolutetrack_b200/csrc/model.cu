@@ -159,13 +159,24 @@ extern "C" int64_t at_encoder_workspace_bytes(int c, int precision) {
 namespace at {
 // tcgen05 path (conv_tc.cu)
 int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* crops, int crop_dtype, int c,
-                         float* features, void* workspace, int64_t workspace_bytes, int fmt, cudaStream_t s);
+                         float* features, void* workspace, int64_t workspace_bytes, int fmt, int prepared_c,
+                         cudaStream_t s);
 int64_t encoder_workspace_bytes_bf16(int c);
+int encoder_chunk_crops();
 }  // namespace at
+
+extern "C" int at_encoder_chunk_crops(void) { return at::encoder_chunk_crops(); }
 
 extern "C" int at_encoder_forward(const float* blob, const void* bf16_blob, const void* crops, int crop_dtype, int c,
                                   float* features, void* workspace, int64_t workspace_bytes, int precision,
                                   void* stream) {
+  return at_encoder_forward_prepared(blob, bf16_blob, crops, crop_dtype, c, features, workspace, workspace_bytes,
+                                     precision, 0, stream);
+}
+
+extern "C" int at_encoder_forward_prepared(const float* blob, const void* bf16_blob, const void* crops, int crop_dtype,
+                                           int c, float* features, void* workspace, int64_t workspace_bytes,
+                                           int precision, int prepared_chunk, void* stream) {
   AT_REQUIRE(c >= 0, "at_encoder_forward: c < 0");
   if (c == 0) return AT_OK;
   AT_REQUIRE(blob && crops && features && workspace, "at_encoder_forward: NULL pointer");
@@ -181,7 +192,7 @@ extern "C" int at_encoder_forward(const float* blob, const void* bf16_blob, cons
   if (precision == AT_PREC_BF16 || precision == AT_PREC_FP16) {
     AT_REQUIRE(bf16_blob != nullptr, "at_encoder_forward: the prepacked 16-bit blob is required for AT_PREC_BF16/FP16");
     return at::encoder_forward_bf16(blob, bf16_blob, crops, crop_dtype, c, features, workspace, workspace_bytes,
-                                    precision == AT_PREC_BF16 ? 1 : 0, (cudaStream_t)stream);
+                                    precision == AT_PREC_BF16 ? 1 : 0, prepared_chunk, (cudaStream_t)stream);
   }
   at::set_error("at_encoder_forward: bad precision %d", precision);
   return AT_ERR_INVALID_ARGUMENT;

@@ -16,6 +16,11 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
   return t;
 }
 
+// programmatic dependent launch: let the next grid of the stream start its prologue early / wait
+// until every grid this one depends on has completed and its writes are visible
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ------------------------------------------------------------------ mbarrier
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");

@@ -76,6 +76,7 @@ class UmeTrackModel(nn.Module):
         self._mem_features = torch.empty(0)      # [cap, 6, 6, 18]  (NHWC)
         self._prev_extrinsics = torch.empty(0)   # [cap, 4, 4]
         self._ws_enc = _Workspace()
+        self._enc_prepared = None  # ((workspace ptr, precision), chunk size the workspace is prepared for)
         self._ws_tail = _Workspace()
         self._status: Optional[torch.Tensor] = None
         self.memory_capacity_hint: Optional[int] = None  # callers that know max(memory_idx)+1 avoid a sync
@@ -158,12 +159,20 @@ class UmeTrackModel(nn.Module):
         bf = self._bf16_weights(dev) if prec != _cabi.AT_PREC_FP32 else None
         nbytes = lib.at_encoder_workspace_bytes(c, prec)
         ws = self._ws_enc.get(nbytes, dev)
+        # the workspace stays prepared (halo cells zeroed) for the chunk size of the previous call
+        # as long as it is the same tensor and only the encoder wrote it
+        key = (ws.data_ptr(), prec)
+        prepared = self._enc_prepared[1] if self._enc_prepared is not None and self._enc_prepared[0] == key else 0
+        self._enc_prepared = None
         with torch.cuda.device(dev):
-            rc = lib.at_encoder_forward(
+            rc = lib.at_encoder_forward_prepared(
                 self._blob.data_ptr(), _cabi.ptr(bf), crops.data_ptr(), dt, c, feats.data_ptr(), ws.data_ptr(),
-                ws.numel(), prec, _cabi.stream_ptr(dev),
+                ws.numel(), prec, prepared, _cabi.stream_ptr(dev),
             )
-        _cabi.check(rc, "at_encoder_forward")
+        _cabi.check(rc, "at_encoder_forward_prepared")
+        if c > 0:
+            chunk = lib.at_encoder_chunk_crops()
+            self._enc_prepared = (key, c % chunk if c % chunk else min(c, chunk))
         return feats
 
     def _forward(self, frame_data, frame_desc, skel_data, head_mode) -> RegressorOutput:

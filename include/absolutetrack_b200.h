@@ -153,6 +153,15 @@ int64_t at_encoder_workspace_bytes(int c, int precision);
 int at_encoder_forward(const float* blob, const void* bf16_blob, const void* crops, int crop_dtype,
                        int c, float* features, void* workspace, int64_t workspace_bytes,
                        int precision, void* stream);
+/* Same call for a workspace the caller keeps between calls.  The 16-bit encoder works on chunks of
+ * at most at_encoder_chunk_crops() crops and relies on halo cells of its activation layout that it
+ * zeroes ("prepares") per chunk size.  prepared_chunk = the size of the LAST chunk of the previous
+ * call on this workspace (min(c, chunk) or c % chunk) when nothing else wrote the workspace since,
+ * else 0; chunks of that size skip the preparation.  AT_PREC_FP32 ignores it. */
+int at_encoder_chunk_crops(void);
+int at_encoder_forward_prepared(const float* blob, const void* bf16_blob, const void* crops, int crop_dtype,
+                                int c, float* features, void* workspace, int64_t workspace_bytes,
+                                int precision, int prepared_chunk, void* stream);
 
 /* Test/debug entry: ONE backbone conv layer (layer_id from at_model_layer_table, 1..28) through the
  * tcgen05 path on float32 NHWC tensors: in [n,H,W,cin] -> out [n,H/stride,W/stride,cout], optional

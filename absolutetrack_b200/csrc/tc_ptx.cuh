@@ -157,7 +157,8 @@ __device__ __forceinline__ uint32_t pack2(float a, float b, int fmt) {
     __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<uint32_t*>(&v);
   }
-  __half2 v = __floats2half2_rn(a, b);
+  // saturate instead of overflowing to inf (fp16 max 65504)
+  __half2 v = __floats2half2_rn(fminf(fmaxf(a, -65504.f), 65504.f), fminf(fmaxf(b, -65504.f), 65504.f));
   return *reinterpret_cast<uint32_t*>(&v);
 }
 __device__ __forceinline__ void unpack2(uint32_t u, int fmt, float& a, float& b) {
@@ -175,7 +176,7 @@ __device__ __forceinline__ uint16_t pack1(float a, int fmt) {
     __nv_bfloat16 v = __float2bfloat16_rn(a);
     return *reinterpret_cast<uint16_t*>(&v);
   }
-  __half v = __float2half_rn(a);
+  __half v = __float2half_rn(fminf(fmaxf(a, -65504.f), 65504.f));
   return *reinterpret_cast<uint16_t*>(&v);
 }
 

@@ -1,0 +1,302 @@
+"""CPU suite (`pytest -m "not gpu"`): the oracle against the reference's golden vectors, the host
+logic, the C-ABI surface and the world_size-2 sharding path over gloo.  No CUDA calls."""
+import ctypes
+import os
+import re
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+import model_oracle as MO
+import np_oracle as O
+import scenario
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+# ------------------------------------------------------------------ C-ABI surface
+def _declared_functions():
+    src = open(os.path.join(ROOT, "include", "absolutetrack_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(at_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_cabi_library_exports_every_declared_symbol():
+    from absolutetrack_b200 import _cabi
+
+    names = _declared_functions()
+    assert len(names) >= 20
+    assert os.path.exists(_cabi.LIB_PATH), "run __graft_entry__.build() first"
+    raw = ctypes.CDLL(_cabi.LIB_PATH)
+    for n in names:
+        assert hasattr(raw, n), f"{n} declared in include/absolutetrack_b200.h but not exported"
+    # the ctypes binding covers the whole header and nothing else
+    assert sorted(_cabi.SIGNATURES) == names
+
+
+def test_cabi_host_side_queries_need_no_gpu():
+    from absolutetrack_b200 import _cabi
+
+    lib = _cabi.lib()
+    assert lib.at_version() >= 100
+    table = _cabi.layer_table()
+    assert len(table) == 46 and table[0]["name"] == "backbone.stem" and table[28]["name"] == "backbone.proj"
+    assert sum(1 for L in table if L["name"].startswith("backbone.")) == 29          # 29 convs, SURVEY 2.1
+    flops = sum(2 * L["cin"] * L["cout"] * L["ksize"] ** 2 * hw for L, hw in zip(table[:29], _backbone_hw()))
+    assert flops == 969_228_288
+    assert lib.at_encoder_workspace_bytes(4, _cabi.AT_PREC_BF16) > 0
+    assert lib.at_encoder_chunk_crops() >= 256
+    assert C_sizeof_crop_params() == 256
+
+
+def _backbone_hw():
+    hw = [96 * 96]                       # stem conv runs at 96x96
+    hw += [48 * 48] * 4                  # layer1
+    hw += [24 * 24] * 7                  # layer2 (conv1 s2, conv2, down, 2 blocks)
+    hw += [12 * 12] * 11
+    hw += [6 * 6] * 5
+    hw += [6 * 6]                        # proj
+    return hw
+
+
+def C_sizeof_crop_params():
+    from absolutetrack_b200 import _cabi
+
+    return ctypes.sizeof(_cabi.AtCropParams)
+
+
+def test_product_path_fails_loudly_without_cuda():
+    from absolutetrack_b200 import _cabi
+    from absolutetrack_b200.lib.models.model_loader import make_random_state_dict, model_from_state_dict
+
+    model = model_from_state_dict(make_random_state_dict(0))
+    with pytest.raises(_cabi.AbsoluteTrackError):
+        model.encode(torch.zeros(1, 96, 96))
+
+
+# ------------------------------------------------------------------ oracle vs reference goldens
+@pytest.mark.parametrize("rec", ["00", "02", "11"])
+def test_oracle_fk_matches_reference_golden_keypoints(gold, rec):
+    """sample_data/user05/recording_*.npy['gt_keypoints'] (written by the reference's eval script)
+    vs the numpy FK restatement, every 4th frame; 1e-3 mm."""
+    G = gold["fk_user05"]
+    p = f"r{rec}_"
+    hm = {k[len(p):]: v for k, v in G.items() if k.startswith(p)}
+    n = 0
+    for h in range(2):
+        idx = np.nonzero(G[p + "valid"][h])[0][::4]
+        lm = O.landmarks_from_hand_pose(hm, G[p + "joint_angles"][idx, h], G[p + "wrist_transforms"][idx, h], h)
+        d = np.abs(lm - G[p + "gt_keypoints"][h][idx])
+        assert d.max() < 1e-3, f"hand {h}: {d.max()} mm"
+        n += len(idx)
+    assert n > 150
+
+
+def test_oracle_warp_is_bit_exact_vs_reference_golden(gold):
+    """tests/golden/warp.npz = reference tracker._warp_image (numpy fp64 map + cv2.remap)."""
+    W = gold["warp"]
+    for i in range(0, len(W["meta"]), 5):
+        k, h, s, kind, seed = (int(v) for v in W["meta"][i])
+        cam = int(scenario.geometry()["crop_cam"][k, h, s])
+        img = scenario.synth_image("noise" if kind == 0 else "smooth", seed)
+        out = O.warp_image(scenario.src_camera(k, cam), scenario.dst_camera(k, h, s), img)
+        assert np.array_equal(out, W["crops"][i]), f"crop {i}"
+
+
+def test_oracle_remap_matches_installed_cv2():
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(5)
+    img = rng.integers(0, 256, (120, 160), dtype=np.uint8)
+    mx = rng.uniform(-3, 163, (96, 96)).astype(np.float32)
+    my = rng.uniform(-3, 123, (96, 96)).astype(np.float32)
+    mx[:4] = -1.0
+    my[:4] = -1.0
+    assert np.array_equal(O.remap_bilinear_u8(img, mx, my), cv2.remap(img, mx, my, cv2.INTER_LINEAR))
+
+
+@pytest.mark.parametrize("head", ["k", "u"])
+def test_model_oracle_matches_reference_golden(gold, head):
+    """tests/golden/model.npz = outputs of the REFERENCE UmeTrackModel (oracle/make_golden_model.py)."""
+    from absolutetrack_b200.lib.models.model_loader import make_random_state_dict
+
+    M = gold["model"]
+    sd = make_random_state_dict(0)
+    n_frames, start, sv = (int(v) for v in M[f"{head}_case"])
+    seq = scenario.model_sequence(n_frames=n_frames, start=start, single_view_frame=None if sv < 0 else sv)
+    hm = scenario.hand_model()
+    skel = (torch.from_numpy(hm["joint_rotation_axes"]).float(), torch.from_numpy(hm["joint_rest_positions"] * 0.001).float())
+    st = MO.TemporalState()
+    for t, fi in enumerate(seq):
+        args = [torch.from_numpy(fi[n]) for n in ("images", "intrinsics", "extrinsics", "sample_range", "memory_idx", "use_memory", "hand_idx")]
+        out = MO.forward(sd, st, *args, skel if head == "k" else None)
+        assert np.abs(out["joint_angles"].numpy() - M[f"{head}{t}_joint_angles"]).max() < 2e-5
+        assert np.abs(out["wrist_xfs"].numpy() - M[f"{head}{t}_wrist_xfs"]).max() < 2e-6
+        assert np.abs(out["sigmas"].numpy() - M[f"{head}{t}_sigmas"]).max() < 2e-5
+
+
+def test_oracle_metrics():
+    rng = np.random.default_rng(0)
+    gt = rng.normal(size=(2, 10, 21, 3))
+    tr = gt + np.array([3.0, 0.0, 4.0])
+    valid = np.ones((2, 10), bool)
+    valid[1, 3] = False
+    assert abs(O.mpjpe(tr, gt, valid) - 5.0) < 1e-12
+    lin = np.arange(10)[None, :, None, None] * np.ones((2, 1, 21, 3))
+    assert O.mean_keypoint_accel(lin, np.ones((2, 10), bool)) < 1e-12      # constant velocity
+
+
+# ------------------------------------------------------------------ host logic
+def test_state_dict_spec_is_the_reference_key_set():
+    from absolutetrack_b200.lib.models.model_loader import make_random_state_dict, pack_state_dict, state_dict_spec
+
+    spec = state_dict_spec()
+    assert len(spec) == 252
+    sd = make_random_state_dict(1)
+    assert sum(v.numel() for k, v in sd.items() if not k.endswith("num_batches_tracked")) == 4_259_371
+    bad = dict(sd)
+    bad.pop("_temporal._temporal_module.0.bias")
+    with pytest.raises(RuntimeError, match="state_dict"):
+        pack_state_dict(bad)
+    bad = dict(sd)
+    bad["extra.weight"] = torch.zeros(1)
+    with pytest.raises(RuntimeError, match="unexpected"):
+        pack_state_dict(bad)
+
+
+def test_bn_folding_matches_conv_plus_batchnorm():
+    """pack_state_dict folds eval-mode BN (eps 1e-5) into [kh][kw][Cin][CoutP] + bias."""
+    import torch.nn.functional as F
+
+    from absolutetrack_b200 import _cabi
+    from absolutetrack_b200.lib.models.model_loader import _layer_keys, make_random_state_dict, pack_state_dict
+
+    sd = make_random_state_dict(3)
+    blob = pack_state_dict(sd)
+    g = torch.Generator().manual_seed(0)
+    for lid in (0, 2, 7, 13, 28, 30, 37):
+        L = _cabi.layer_table()[lid]
+        conv, bn = _layer_keys(L["name"])
+        k, cin, cout = L["ksize"], L["cin"], L["cout"]
+        x = torch.randn(2, cin, 8, 8, generator=g)
+        ref = F.conv2d(x, sd[conv + ".weight"], sd.get(conv + ".bias"), 1, k // 2)
+        if bn:
+            ref = F.batch_norm(ref, sd[bn + ".running_mean"], sd[bn + ".running_var"], sd[bn + ".weight"], sd[bn + ".bias"], False, 0.0, 1e-5)
+        coutp = (cout + 3) // 4 * 4
+        w = blob[L["weight_offset"]: L["weight_offset"] + k * k * cin * coutp].reshape(k, k, cin, coutp)[..., :cout]
+        b = blob[L["bias_offset"]: L["bias_offset"] + cout]
+        got = F.conv2d(x, w.permute(3, 2, 0, 1).contiguous(), b, 1, k // 2)
+        assert (got - ref).abs().max() < 2e-5 * max(1.0, ref.abs().max().item()), L["name"]
+
+
+def test_camera_mirror_matches_oracle_projection():
+    from absolutetrack_b200.lib.common import camera as C
+
+    G = scenario.geometry()
+    k, cam = 7, 2
+    src = C.Fisheye62CameraModel(636, 480, G["cam_f"][cam], G["cam_c"][cam], G["cam_coeffs"][cam], G["camera_to_world"][k, cam])
+    rng = np.random.default_rng(2)
+    pts_eye = np.concatenate([rng.uniform(-200, 200, (50, 2)), rng.uniform(150, 600, (50, 1))], axis=1)
+    got = src.eye_to_window(pts_eye)
+    ref = O.fisheye62_eye_to_window(pts_eye, G["cam_f"][cam], G["cam_c"][cam], tuple(G["cam_coeffs"][cam]))
+    assert np.abs(got - ref).max() < 1e-9
+    world = src.eye_to_world(pts_eye)
+    assert np.abs(src.world_to_eye(world) - pts_eye).max() < 1e-3         # camera.py:36-38 contract (float32 calibration: R is orthonormal to ~1e-7)
+
+
+def test_crop_kernel_params_precompose_the_rotation_in_fp64():
+    from absolutetrack_b200.lib.common import camera as C
+    from absolutetrack_b200.lib.tracker.tracker import pack_crop_params
+
+    G = scenario.geometry()
+    k, h, s = 3, 1, 0
+    cam = int(G["crop_cam"][k, h, s])
+    src = C.Fisheye62CameraModel(636, 480, G["cam_f"][cam], G["cam_c"][cam], G["cam_coeffs"][cam], G["camera_to_world"][k, cam])
+    dst = C.PinholePlaneCameraModel(96, 96, G["crop_f"][k, h, s], G["crop_c"][k, h, s], [], G["crop_c2w"][k, h, s])
+    rec = C.crop_kernel_params(src, dst)
+    buf = pack_crop_params([(5, 2, rec)])
+    assert buf.shape == (1, 256) and buf.dtype == np.uint8
+    from absolutetrack_b200 import _cabi
+
+    P = _cabi.AtCropParams.from_buffer_copy(buf.tobytes())
+    assert (P.frame, P.view, P.src_w, P.src_h) == (5, 2, 636, 480)
+    M = np.array(P.M).reshape(3, 3)
+    Rs, Rd = G["camera_to_world"][k, cam][:3, :3], G["crop_c2w"][k, h, s][:3, :3]
+    assert np.abs(M - Rs.T @ Rd).max() < 1e-12
+    assert abs(abs(np.linalg.det(M)) - 1) < 1e-5                              # right hand: det -1 (mirrorx); float32 calibration
+    assert np.abs(np.array(P.d)).max() < 1e-3                                 # same optical centre, mm
+
+
+def test_bundles_collate_and_to_device_keep_dataclasses():
+    from absolutetrack_b200.lib.data_utils import bundles
+    from absolutetrack_b200.lib.models.umetrack_model import InputFrameData
+
+    a = InputFrameData(torch.zeros(2, 96, 96), torch.zeros(2, 3, 3), torch.zeros(2, 4, 4))
+    b = bundles.to_device(a, torch.device("cpu"))
+    assert isinstance(b, InputFrameData) and b.left_images.shape == (2, 96, 96)
+    c = bundles.collate([a, a])
+    assert isinstance(c, InputFrameData) and c.left_images.shape == (2, 2, 96, 96)
+
+
+def test_hand_model_mirror_and_scale():
+    from absolutetrack_b200.lib.common import hand as H
+    from test_gpu_kernels import _hand_model_tuple
+
+    hm = _hand_model_tuple(scenario.geometry(), "hm_")
+    sc = H.scaled_hand_model(hm, 0.001)
+    assert torch.allclose(sc.joint_rest_positions, hm.joint_rest_positions * 0.001)
+    assert torch.equal(sc.joint_rotation_axes, hm.joint_rotation_axes)
+    assert H.NUM_HANDS == 2 and H.NUM_LANDMARKS_PER_HAND == 21
+
+
+# ------------------------------------------------------------------ multi-process sharding (gloo, world_size 2)
+def _gloo_worker(rank, world, port, out_dir):
+    import torch.distributed as dist
+
+    sys.path.insert(0, ROOT)
+    from absolutetrack_b200 import distributed as D
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    n_seq = 11
+    mine = list(D.shard_indices(n_seq, rank, world))
+    rng = np.random.default_rng(0)
+    gt = torch.from_numpy(rng.normal(size=(n_seq, 21, 3)))
+    tracked = gt + torch.from_numpy(rng.normal(size=(n_seq, 21, 3)))
+    valid = torch.from_numpy(rng.random(n_seq) > 0.2)
+    sums = torch.zeros(2, dtype=torch.float64)
+    D.mpjpe_accumulate(sums, tracked[mine], gt[mine], valid[mine])
+    D.all_reduce_metric_sums(sums)
+    full = torch.zeros(2, dtype=torch.float64)
+    D.mpjpe_accumulate(full, tracked, gt, valid)
+    torch.save({"mine": mine, "sums": sums, "full": full}, os.path.join(out_dir, f"r{rank}.pt"))
+    dist.destroy_process_group()
+
+
+def test_sequences_shard_across_two_ranks_and_metric_sums_all_reduce(tmp_path):
+    import socket
+
+    import torch.multiprocessing as mp
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    mp.spawn(_gloo_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    r0, r1 = (torch.load(tmp_path / f"r{r}.pt") for r in range(2))
+    assert sorted(r0["mine"] + r1["mine"]) == list(range(11)) and not set(r0["mine"]) & set(r1["mine"])
+    assert r0["mine"] == list(range(0, 11, 2))                            # reference Sampler striding
+    for r in (r0, r1):
+        assert torch.allclose(r["sums"], r["full"], rtol=1e-12)           # every rank holds the global sums
+
+
+def test_shard_indices_validate_rank():
+    from absolutetrack_b200 import distributed as D
+
+    with pytest.raises(ValueError):
+        D.shard_indices(4, 2, 2)
+    assert list(D.shard_indices(5, 1, 2)) == [1, 3]
+    assert D.shard(["a", "b", "c"], 0, 2) == ["a", "c"]
+    with pytest.raises(TypeError):
+        D.all_reduce_metric_sums(torch.zeros(2))

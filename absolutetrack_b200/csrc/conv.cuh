@@ -35,6 +35,9 @@ int64_t blob_floats();
 int conv_nhwc_f32(const ConvLayer& L, const float* blob, const float* in, int in_ld, int in_coff, const float* res,
                   int res_ld, float* out, int out_ld, int out_coff, int N, int H, int W, bool relu,
                   cudaStream_t stream);
+int conv_nhwc_tf32x3(const ConvLayer& L, const float* blob, const float* in, int in_ld, int in_coff, const float* res,
+                     int res_ld, float* out, int out_ld, int out_coff, int N, int H, int W, bool relu,
+                     cudaStream_t stream);
 int stem_f32(const ConvLayer& L, const float* blob, const void* crops, int crop_dtype, float* out, int c,
              cudaStream_t stream);
 

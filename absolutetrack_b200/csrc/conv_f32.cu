@@ -6,6 +6,8 @@
 // GEMM view: M = N*Ho*Wo output pixels, N = Cout, K = kh*kw*Cin.  BatchNorm is folded into the
 // weights on the host; the epilogue fuses bias + residual + ReLU and can write into a channel
 // slice of a wider NHWC buffer (concat for free).
+#include <stdlib.h>
+
 #include "conv.cuh"
 
 namespace at {
@@ -179,6 +181,193 @@ __global__ void __launch_bounds__(kConvThreads) conv_nhwc_f32_kernel(ConvArgs a)
   }
 }
 
+
+// ------------------------------------------------------------------------------------------
+// Error-compensated TF32 tensor-core variant ("3xTF32") for the small 6x6 tail convolutions.
+// Every fp32 operand x is split into hi = tf32(x), lo = tf32(x - hi); the product is accumulated
+// as a_lo*b_hi + a_hi*b_lo + a_hi*b_hi in fp32, which keeps ~2^-21 relative accuracy per product
+// (fp32-level: the tail cannot afford a 10-bit mantissa) at 1/3 of the TF32 rate.
+// mma.sync.m16n8k8 (register fragments): the tail is 1 % of the network's FLOPs and its tiles are
+// tiny; the tcgen05/TMEM machinery of the encoder buys nothing here.
+// CTA tile BM=128 pixels x BN (64 or 96) channels, 8 warps as 4(M) x 2(N), BK = 16.
+// hi = x with the low 13 mantissa bits cleared (a valid tf32), lo = x - hi (exact in fp32; the
+// tensor core ignores its low 13 bits).  Two full-rate ALU ops per value instead of two cvt.rna
+// on the conversion pipe; the dropped terms (a_lo*b_lo, the truncation of lo) are ~2^-20 relative.
+__device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
+  hi = __float_as_uint(x) & 0xFFFFE000u;
+  lo = __float_as_uint(x - __uint_as_float(hi));
+}
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kConvThreads) conv_nhwc_tf32x3_kernel(ConvArgs a) {
+  constexpr int BM = 128;
+  constexpr int LDA = BM + 8, LDB = BN + 8;      // +8: conflict-free fragment reads (bank = 8*t + g)
+  constexpr int WN = BN / 2;                     // warp tile 32 x WN
+  constexpr int NT = WN / 8;                     // n8 tiles per warp (4 or 6)
+  constexpr int A_F4 = BM * BK / 4 / kConvThreads;  // 2
+  constexpr int B_F4 = (BK * BN / 4 + kConvThreads - 1) / kConvThreads;  // 1 or 2
+  __shared__ __align__(16) float As[2][BK][LDA];
+  __shared__ __align__(16) float Bs[2][BK][LDB];
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int wm = warp & 3, wn = warp >> 2;
+  const int g = lane >> 2, t = lane & 3;
+  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+
+  int a_row[A_F4], a_kq[A_F4], a_img[A_F4], a_oy[A_F4], a_ox[A_F4];
+  bool a_ok[A_F4];
+#pragma unroll
+  for (int i = 0; i < A_F4; ++i) {
+    const int l = tid + i * kConvThreads;
+    a_row[i] = l / 4;
+    a_kq[i] = l % 4;
+    const int m = m0 + a_row[i];
+    a_ok[i] = m < a.M;
+    const int mm = a_ok[i] ? m : 0;
+    a_img[i] = mm / (a.Ho * a.Wo);
+    const int rem = mm - a_img[i] * (a.Ho * a.Wo);
+    a_oy[i] = rem / a.Wo;
+    a_ox[i] = rem - a_oy[i] * a.Wo;
+  }
+  const bool vec_in = ((a.Cin | a.in_ld | a.in_coff) & 3) == 0;
+  const int kchunks = (a.Cin + BK - 1) / BK;
+  const int steps = a.ksize * a.ksize * kchunks;
+
+  float4 ra[A_F4], rb[B_F4];
+  auto load_step = [&](int step) {
+    const int tap = step / kchunks;
+    const int k0 = (step - tap * kchunks) * BK;
+    const int r = tap / a.ksize, s = tap - r * a.ksize;
+#pragma unroll
+    for (int i = 0; i < A_F4; ++i) {
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      const int iy = a_oy[i] * a.stride + r - a.pad;
+      const int ix = a_ox[i] * a.stride + s - a.pad;
+      const int k = k0 + a_kq[i] * 4;
+      if (a_ok[i] && (unsigned)iy < (unsigned)a.H && (unsigned)ix < (unsigned)a.W && k < a.Cin) {
+        const float* p = a.in + ((int64_t)(a_img[i] * a.H + iy) * a.W + ix) * a.in_ld + a.in_coff + k;
+        if (vec_in) {
+          v = __ldg(reinterpret_cast<const float4*>(p));
+        } else {
+          v.x = __ldg(p);
+          if (k + 1 < a.Cin) v.y = __ldg(p + 1);
+          if (k + 2 < a.Cin) v.z = __ldg(p + 2);
+          if (k + 3 < a.Cin) v.w = __ldg(p + 3);
+        }
+      }
+      ra[i] = v;
+    }
+#pragma unroll
+    for (int i = 0; i < B_F4; ++i) {
+      const int l = tid + i * kConvThreads;
+      const int row = l / (BN / 4), c4 = l - row * (BN / 4);
+      rb[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (row < BK) {
+        const int k = k0 + row, n = n0 + c4 * 4;
+        if (k < a.Cin && n < a.CoutP)
+          rb[i] = __ldg(reinterpret_cast<const float4*>(a.w + ((int64_t)tap * a.Cin + k) * a.CoutP + n));
+      }
+    }
+  };
+  auto store_step = [&](int buf) {
+#pragma unroll
+    for (int i = 0; i < A_F4; ++i) {
+      As[buf][a_kq[i] * 4 + 0][a_row[i]] = ra[i].x;
+      As[buf][a_kq[i] * 4 + 1][a_row[i]] = ra[i].y;
+      As[buf][a_kq[i] * 4 + 2][a_row[i]] = ra[i].z;
+      As[buf][a_kq[i] * 4 + 3][a_row[i]] = ra[i].w;
+    }
+#pragma unroll
+    for (int i = 0; i < B_F4; ++i) {
+      const int l = tid + i * kConvThreads;
+      const int row = l / (BN / 4), c4 = l - row * (BN / 4);
+      if (row < BK) *reinterpret_cast<float4*>(&Bs[buf][row][c4 * 4]) = rb[i];
+    }
+  };
+
+  float acc[2][NT][4];
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < NT; ++j)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) acc[i][j][e] = 0.f;
+
+  load_step(0);
+  store_step(0);
+  __syncthreads();
+  for (int step = 0; step < steps; ++step) {
+    const int buf = step & 1;
+    if (step + 1 < steps) load_step(step + 1);
+#pragma unroll
+    for (int kk = 0; kk < BK; kk += 8) {
+      uint32_t ah[2][4], al[2][4];
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int mr = wm * 32 + i * 16 + g;
+        const float v[4] = {As[buf][kk + t][mr], As[buf][kk + t][mr + 8], As[buf][kk + t + 4][mr], As[buf][kk + t + 4][mr + 8]};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) split_tf32(v[e], ah[i][e], al[i][e]);
+      }
+#pragma unroll
+      for (int j = 0; j < NT; ++j) {
+        const int nc = wn * WN + j * 8 + g;
+        const float v[2] = {Bs[buf][kk + t][nc], Bs[buf][kk + t + 4][nc]};
+        uint32_t bh[2], bl[2];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) split_tf32(v[e], bh[e], bl[e]);
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          mma_tf32(acc[i][j], al[i], bh);
+          mma_tf32(acc[i][j], ah[i], bl);
+          mma_tf32(acc[i][j], ah[i], bh);
+        }
+      }
+    }
+    if (step + 1 < steps) store_step(buf ^ 1);
+    __syncthreads();
+  }
+
+  // epilogue: bias + residual + relu; fragment (i,j): rows g / g+8, columns 2t, 2t+1
+#pragma unroll
+  for (int j = 0; j < NT; ++j) {
+    const int n = n0 + wn * WN + j * 8 + 2 * t;
+    if (n >= a.Cout) continue;
+    const bool two = n + 1 < a.Cout;
+    const float b0 = __ldg(a.bias + n), b1 = two ? __ldg(a.bias + n + 1) : 0.f;
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int m = m0 + wm * 32 + i * 16 + g + h * 8;
+        if (m >= a.M) continue;
+        float v0 = acc[i][j][h * 2] + b0, v1 = acc[i][j][h * 2 + 1] + b1;
+        if (a.res != nullptr) {
+          const float* rp = a.res + (int64_t)m * a.res_ld + n;
+          v0 += __ldg(rp);
+          if (two) v1 += __ldg(rp + 1);
+        }
+        if (a.relu) {
+          v0 = fmaxf(v0, 0.f);
+          v1 = fmaxf(v1, 0.f);
+        }
+        float* op = a.out + (int64_t)m * a.out_ld + a.out_coff + n;
+        if (two && (((a.out_ld | a.out_coff) & 1) == 0)) {
+          *reinterpret_cast<float2*>(op) = make_float2(v0, v1);
+        } else {
+          op[0] = v0;
+          if (two) op[1] = v1;
+        }
+      }
+  }
+}
+
 // Stem: conv3x3(1->32, pad 1, bias) + BN (folded) + ReLU + maxpool 2x2   (model_utils.py:119-124)
 // in: crops [c,96,96] (u8 grey levels -> /255, or f32); out NHWC [c,48,48,32] f32.
 // One thread = one pooled pixel x 8 output channels (4 lanes cover the 32 channels).
@@ -273,6 +462,45 @@ int conv_nhwc_f32(const ConvLayer& L, const float* blob, const float* in, int in
     conv_nhwc_f32_kernel<64, 64><<<grid, kConvThreads, 0, stream>>>(a);
   }
   return check_launch("conv_nhwc_f32_kernel");
+}
+
+// Same contract as conv_nhwc_f32, on the tensor cores with error-compensated TF32 (fp32-level
+// accuracy).  Used by the tail (csrc/tail.cu); AT_TAIL_SIMT=1 routes back to the CUDA-core kernel.
+int conv_nhwc_tf32x3(const ConvLayer& L, const float* blob, const float* in, int in_ld, int in_coff, const float* res,
+                     int res_ld, float* out, int out_ld, int out_coff, int N, int H, int W, bool relu,
+                     cudaStream_t stream) {
+  static const bool simt = getenv("AT_TAIL_SIMT") != nullptr && atoi(getenv("AT_TAIL_SIMT")) != 0;
+  if (simt) return conv_nhwc_f32(L, blob, in, in_ld, in_coff, res, res_ld, out, out_ld, out_coff, N, H, W, relu, stream);
+  ConvArgs a;
+  a.in = in;
+  a.w = blob + L.weight_offset;
+  a.bias = blob + L.bias_offset;
+  a.res = res;
+  a.out = out;
+  a.N = N; a.H = H; a.W = W; a.Cin = L.cin;
+  a.ksize = L.ksize; a.stride = L.stride; a.pad = L.ksize / 2;
+  a.Ho = (H + 2 * a.pad - L.ksize) / L.stride + 1;
+  a.Wo = (W + 2 * a.pad - L.ksize) / L.stride + 1;
+  a.Cout = L.cout;
+  a.CoutP = (int)round_up(L.cout, 4);
+  a.in_ld = in_ld; a.in_coff = in_coff; a.out_ld = out_ld; a.out_coff = out_coff; a.res_ld = res_ld;
+  a.relu = relu ? 1 : 0;
+  const int64_t M = (int64_t)N * a.Ho * a.Wo;
+  if (M == 0) return AT_OK;
+  if (M > 0x7fffffffLL) {
+    set_error("conv_nhwc_tf32x3: M too large");
+    return AT_ERR_INVALID_ARGUMENT;
+  }
+  a.M = (int)M;
+  // 96-wide tiles for Cout in (64, 96]; otherwise 64-wide tiles
+  if (L.cout > 64 && L.cout <= 96) {
+    dim3 grid((unsigned)((M + 127) / 128), 1);
+    conv_nhwc_tf32x3_kernel<96><<<grid, kConvThreads, 0, stream>>>(a);
+  } else {
+    dim3 grid((unsigned)((M + 127) / 128), (unsigned)((L.cout + 63) / 64));
+    conv_nhwc_tf32x3_kernel<64><<<grid, kConvThreads, 0, stream>>>(a);
+  }
+  return check_launch("conv_nhwc_tf32x3_kernel");
 }
 
 int stem_f32(const ConvLayer& L, const float* blob, const void* crops, int crop_dtype, float* out, int c,

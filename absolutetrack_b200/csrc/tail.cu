@@ -450,18 +450,18 @@ extern "C" int at_tail_forward(const float* blob, const AtTailInputs* in, AtTemp
   if (rc) return rc;
   // 2-view fusion (model_utils.py:141-163).  Rows of single-view samples are computed on
   // whatever the workspace holds and ignored afterwards.
-  if ((rc = conv_nhwc_f32(T[L_FUSION + 0], blob, fuse_in, 144, 0, nullptr, 0, f1, 108, 0, n, 6, 6, true, s))) return rc;
-  if ((rc = conv_nhwc_f32(T[L_FUSION + 1], blob, f1, 108, 0, nullptr, 0, f2, 72, 0, n, 6, 6, true, s))) return rc;
-  if ((rc = conv_nhwc_f32(T[L_FUSION + 2], blob, f2, 72, 0, nullptr, 0, f3, 72, 0, n, 6, 6, false, s))) return rc;
+  if ((rc = conv_nhwc_tf32x3(T[L_FUSION + 0], blob, fuse_in, 144, 0, nullptr, 0, f1, 108, 0, n, 6, 6, true, s))) return rc;
+  if ((rc = conv_nhwc_tf32x3(T[L_FUSION + 1], blob, f1, 108, 0, nullptr, 0, f2, 72, 0, n, 6, 6, true, s))) return rc;
+  if ((rc = conv_nhwc_tf32x3(T[L_FUSION + 2], blob, f2, 72, 0, nullptr, 0, f3, 72, 0, n, 6, 6, false, s))) return rc;
   {
     const int64_t tot = (int64_t)n * kPix * kFeat;
     post_fusion_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(f3, in->intrinsics, in->sample_range, n, c, temp_in);
     if ((rc = check_launch("post_fusion_kernel"))) return rc;
   }
   // SimpleConvRNN step (temporal.py:76-91): 3x conv1x1(90->90), ReLU after the first two
-  if ((rc = conv_nhwc_f32(T[L_TEMPORAL + 0], blob, temp_in, 90, 0, nullptr, 0, t1, 90, 0, n, 6, 6, true, s))) return rc;
-  if ((rc = conv_nhwc_f32(T[L_TEMPORAL + 1], blob, t1, 90, 0, nullptr, 0, t2, 90, 0, n, 6, 6, true, s))) return rc;
-  if ((rc = conv_nhwc_f32(T[L_TEMPORAL + 2], blob, t2, 90, 0, nullptr, 0, t3, 90, 0, n, 6, 6, false, s))) return rc;
+  if ((rc = conv_nhwc_tf32x3(T[L_TEMPORAL + 0], blob, temp_in, 90, 0, nullptr, 0, t1, 90, 0, n, 6, 6, true, s))) return rc;
+  if ((rc = conv_nhwc_tf32x3(T[L_TEMPORAL + 1], blob, t1, 90, 0, nullptr, 0, t2, 90, 0, n, 6, 6, true, s))) return rc;
+  if ((rc = conv_nhwc_tf32x3(T[L_TEMPORAL + 2], blob, t2, 90, 0, nullptr, 0, t3, 90, 0, n, 6, 6, false, s))) return rc;
   const int hc = known ? 76 : 72;
   if (known) {
     const ConvLayer& L = T[L_SKEL];
@@ -477,11 +477,11 @@ extern "C" int at_tail_forward(const float* blob, const AtTailInputs* in, AtTemp
   }
   // pose head (model_utils.py:195-208): 2 BasicBlocks + conv1x1 + global average pool
   const int hb = known ? L_HEAD_K : L_HEAD_U;
-  if ((rc = conv_nhwc_f32(T[hb + 0], blob, head_in, hc, 0, nullptr, 0, h1, hc, 0, n, 6, 6, true, s))) return rc;
-  if ((rc = conv_nhwc_f32(T[hb + 1], blob, h1, hc, 0, head_in, hc, h2, hc, 0, n, 6, 6, true, s))) return rc;
-  if ((rc = conv_nhwc_f32(T[hb + 2], blob, h2, hc, 0, nullptr, 0, h1, hc, 0, n, 6, 6, true, s))) return rc;
-  if ((rc = conv_nhwc_f32(T[hb + 3], blob, h1, hc, 0, h2, hc, head_in, hc, 0, n, 6, 6, true, s))) return rc;
-  if ((rc = conv_nhwc_f32(T[hb + 4], blob, head_in, hc, 0, nullptr, 0, ho, 64, 0, n, 6, 6, false, s))) return rc;
+  if ((rc = conv_nhwc_tf32x3(T[hb + 0], blob, head_in, hc, 0, nullptr, 0, h1, hc, 0, n, 6, 6, true, s))) return rc;
+  if ((rc = conv_nhwc_tf32x3(T[hb + 1], blob, h1, hc, 0, head_in, hc, h2, hc, 0, n, 6, 6, true, s))) return rc;
+  if ((rc = conv_nhwc_tf32x3(T[hb + 2], blob, h2, hc, 0, nullptr, 0, h1, hc, 0, n, 6, 6, true, s))) return rc;
+  if ((rc = conv_nhwc_tf32x3(T[hb + 3], blob, h1, hc, 0, h2, hc, head_in, hc, 0, n, 6, 6, true, s))) return rc;
+  if ((rc = conv_nhwc_tf32x3(T[hb + 4], blob, head_in, hc, 0, nullptr, 0, ho, 64, 0, n, 6, 6, false, s))) return rc;
   DecodeArgs da;
   da.head_out = ho; da.ld = 64; da.n_out = known ? 62 : 63;
   da.extrinsics = in->extrinsics; da.sample_range = in->sample_range; da.hand_idx = in->hand_idx;

@@ -7,6 +7,8 @@
 // Layout: the 17 skinning frames (3x4 each) of every hand in the block live in shared memory,
 // element-major ([204][kBlock]) so that lanes never conflict; landmarks are staged through the
 // same shared memory for fully coalesced 128-bit-friendly stores.
+#include <algorithm>
+
 #include "at_common.cuh"
 
 namespace {
@@ -149,6 +151,208 @@ __global__ void __launch_bounds__(kBlock) fk_skin_kernel(const float* __restrict
   for (int i = threadIdx.x; i < total; i += kBlock) dst[i] = smem[i];
 }
 
+
+// ------------------------------------------------------------------------------------------
+// Shared-hand-model fast path (eval scripts, frame-stream tracker): the model is uniform across the
+// CTA, so per joint the constant parts of the Rodrigues formula are computed once per CTA:
+//   R = I + s1*K + s2*K^2,  t = p - R p = -(s1*K p + s2*K^2 p),  K = skew(axis),
+//   s1 = angle*sin(th)/th,  s2 = angle^2*(1-cos(th))/th^2,  th = sqrt(max(|axis|^2 angle^2, 1e-4))
+// (identical to so3_exp_map(axis*angle) of hand_skinning.py:46).  The 17 frames never leave
+// registers: landmarks are visited frame by frame through a CSR table built once per CTA
+// (bone index -> landmarks) and accumulated in shared memory, which doubles as the staging buffer
+// for coalesced input loads and output stores.  252 B of shared memory per hand -> 3 CTAs x 256
+// threads per SM.
+constexpr int kFast = 256;             // hands per CTA
+constexpr int kOutLd = kFast + 1;      // conflict-free both for per-thread rows and the transposed copy
+constexpr int kJaLd = 23, kWxLd = 17;  // padded input rows
+
+struct JointConst {  // 24 floats, 16-byte aligned: K (3), K^2 (6 sym), K p (3), K^2 p (3), |axis|^2
+  float4 v[6];
+};
+
+struct FastTables {
+  JointConst jc[20];
+  float lm_p[63];          // landmark rest positions
+  int fs[kNumFrames + 1];  // CSR row starts
+  int ent_l[64];           // landmark of entry
+  float ent_w[64];         // weight of entry
+  int ent_first[64];       // 1: first contribution to that landmark (store), 0: accumulate
+  int lm_has[21];
+};
+
+// every landmark attached to frame b: out[l] (+)= w * (F [p,1])   (hand_skinning._lbs :56-67)
+__device__ __forceinline__ void emit_frame(const FastTables& tb, float* __restrict__ s_out, int b, const Xf& F) {
+  const int tid = threadIdx.x;
+  for (int e = tb.fs[b]; e < tb.fs[b + 1]; ++e) {
+    const int l = tb.ent_l[e];
+    const float w = tb.ent_w[e];
+    const float qx = tb.lm_p[3 * l] * w, qy = tb.lm_p[3 * l + 1] * w, qz = tb.lm_p[3 * l + 2] * w;
+    const float ox = F.r[0] * qx + F.r[1] * qy + F.r[2] * qz + F.t[0] * w;
+    const float oy = F.r[3] * qx + F.r[4] * qy + F.r[5] * qz + F.t[1] * w;
+    const float oz = F.r[6] * qx + F.r[7] * qy + F.r[8] * qz + F.t[2] * w;
+    float* o = s_out + (3 * l) * kOutLd + tid;
+    if (tb.ent_first[e]) {
+      o[0] = ox; o[kOutLd] = oy; o[2 * kOutLd] = oz;
+    } else {
+      o[0] += ox; o[kOutLd] += oy; o[2 * kOutLd] += oz;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kFast, 3) fk_skin_shared_kernel(const float* __restrict__ joint_angles,
+                                                                  const float* __restrict__ wrist,
+                                                                  const int64_t* __restrict__ hand_idx, AtHandModel m,
+                                                                  int64_t n, float* __restrict__ landmarks) {
+  extern __shared__ __align__(16) float smem[];
+  __shared__ FastTables tb;
+  __shared__ int s_b[64];
+  __shared__ int s_valid[64];
+  const int tid = threadIdx.x;
+  const int K = m.n_weights;
+  const int npairs = 21 * K;  // <= 63 for K <= 3 (host checks)
+
+  // ---- per-CTA tables
+  if (tid < 20) {
+    const float ax = m.joint_rotation_axes[3 * tid], ay = m.joint_rotation_axes[3 * tid + 1], az = m.joint_rotation_axes[3 * tid + 2];
+    const float px = m.joint_rest_positions[3 * tid], py = m.joint_rest_positions[3 * tid + 1], pz = m.joint_rest_positions[3 * tid + 2];
+    const float a2 = ax * ax + ay * ay + az * az;
+    // K^2 = a a^T - |a|^2 I (symmetric): xx, yy, zz, xy, xz, yz
+    const float kxx = -(ay * ay + az * az), kyy = -(ax * ax + az * az), kzz = -(ax * ax + ay * ay);
+    const float kxy = ax * ay, kxz = ax * az, kyz = ay * az;
+    const float kpx = ay * pz - az * py, kpy = az * px - ax * pz, kpz = ax * py - ay * px;  // K p = a x p
+    const float k2x = kxx * px + kxy * py + kxz * pz, k2y = kxy * px + kyy * py + kyz * pz, k2z = kxz * px + kyz * py + kzz * pz;
+    JointConst& J = tb.jc[tid];
+    J.v[0] = make_float4(ax, ay, az, a2);
+    J.v[1] = make_float4(kxx, kyy, kzz, 0.f);
+    J.v[2] = make_float4(kxy, kxz, kyz, 0.f);
+    J.v[3] = make_float4(kpx, kpy, kpz, 0.f);
+    J.v[4] = make_float4(k2x, k2y, k2z, 0.f);
+    J.v[5] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  if (tid >= 32 && tid < 32 + 63) tb.lm_p[tid - 32] = m.landmark_rest_positions[tid - 32];
+  if (tid >= 128 && tid < 128 + 64) {
+    const int e = tid - 128;
+    int valid = 0, b = 0;
+    if (e < npairs) {
+      valid = m.landmark_rest_bone_weights[e] != 0.0f;   // zero weights dropped (hand_skinning.py:92-94)
+      b = min(max(m.landmark_rest_bone_indices[e], 0), kNumFrames - 1);
+    }
+    s_b[e] = b;
+    s_valid[e] = valid;
+  }
+  __syncthreads();
+  if (tid >= 128 && tid < 128 + 64) {
+    const int e = tid - 128;
+    if (e < npairs && s_valid[e]) {
+      const int b = s_b[e], l = e / K;
+      int pos = 0, first = 1;
+      for (int j = 0; j < npairs; ++j) {
+        if (!s_valid[j]) continue;
+        const bool before = s_b[j] < b || (s_b[j] == b && j < e);
+        pos += before;
+        if (before && j / K == l) first = 0;
+      }
+      tb.ent_l[pos] = l;
+      tb.ent_w[pos] = m.landmark_rest_bone_weights[e];
+      tb.ent_first[pos] = first;
+    }
+    if (e <= kNumFrames) {
+      int cnt = 0;
+      for (int j = 0; j < npairs; ++j) cnt += s_valid[j] && s_b[j] < e;
+      tb.fs[e] = cnt;
+    }
+    if (e < 21) {
+      int any = 0;
+      for (int k = 0; k < K; ++k) any |= s_valid[e * K + k];
+      tb.lm_has[e] = any;
+    }
+  }
+  // ---- persistent loop over tiles of kFast hands (the tables above are built once per CTA)
+  const int64_t n_tiles = (n + kFast - 1) / kFast;
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+  const int64_t base = tile * kFast;
+  const int n_here = (int)min((int64_t)kFast, n - base);
+  // coalesced input staging: joint angles [n_here,22] -> rows of 23, wrist [n_here,16] -> rows of 17
+  float* s_ja = smem;
+  float* s_wx = smem + kFast * kJaLd;
+  {
+    const float* gja = joint_angles + base * 22;
+    for (int i = tid; i < n_here * 22; i += kFast) {
+      const int h = i / 22, j = i - h * 22;
+      s_ja[h * kJaLd + j] = __ldg(gja + i);
+    }
+    const float* gwx = wrist + base * 16;
+    for (int i = tid; i < n_here * 16; i += kFast) s_wx[(i >> 4) * kWxLd + (i & 15)] = __ldg(gwx + i);
+  }
+  __syncthreads();
+  const bool active = tid < n_here;
+  float ang[20];
+  Xf W;
+  if (active) {
+#pragma unroll
+    for (int j = 0; j < 20; ++j) ang[j] = s_ja[tid * kJaLd + j];
+    const float sgn = (hand_idx != nullptr && hand_idx[base + tid] == 1) ? -1.0f : 1.0f;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      W.r[i * 3 + 0] = sgn * s_wx[tid * kWxLd + i * 4 + 0];
+      W.r[i * 3 + 1] = s_wx[tid * kWxLd + i * 4 + 1];
+      W.r[i * 3 + 2] = s_wx[tid * kWxLd + i * 4 + 2];
+      W.t[i] = s_wx[tid * kWxLd + i * 4 + 3];
+    }
+  }
+  __syncthreads();  // inputs are in registers: the buffer becomes the [63][kOutLd] landmark accumulator
+  float* s_out = smem;
+  if (active) {
+    for (int l = 0; l < 21; ++l)
+      if (!tb.lm_has[l]) {
+        s_out[(3 * l) * kOutLd + tid] = 0.f; s_out[(3 * l + 1) * kOutLd + tid] = 0.f; s_out[(3 * l + 2) * kOutLd + tid] = 0.f;
+      }
+    emit_frame(tb, s_out, 0, W);
+    emit_frame(tb, s_out, 1, W);
+#pragma unroll 1
+    for (int f = 0; f < 5; ++f) {
+      Xf cur = W;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const JointConst& J = tb.jc[4 * f + i];
+        const float4 c0 = J.v[0], c1 = J.v[1], c2 = J.v[2], c3 = J.v[3], c4 = J.v[4];
+        const float a = ang[i];  // the angles of the current finger are rotated into ang[0..3]
+        // th = sqrt(max(|w|^2, 1e-4)) in [0.01, ~5]: MUFU rsqrt / sin / cos are accurate to ~4e-7
+        // absolute there, far inside the 1e-3 mm landmark tolerance (tests/test_gpu_kernels.py)
+        const float th2 = fmaxf(c0.w * a * a, 1e-4f);
+        const float inv = rsqrtf(th2);
+        const float th = th2 * inv;
+        float sn, cs;
+        __sincosf(th, &sn, &cs);
+        const float s1 = a * (inv * sn);
+        const float s2 = (a * a) * (inv * inv * (1.0f - cs));
+        Xf T, nxt;
+        T.r[0] = 1.0f + s2 * c1.x;        T.r[1] = s2 * c2.x - s1 * c0.z;  T.r[2] = s2 * c2.y + s1 * c0.y;
+        T.r[3] = s2 * c2.x + s1 * c0.z;   T.r[4] = 1.0f + s2 * c1.y;       T.r[5] = s2 * c2.z - s1 * c0.x;
+        T.r[6] = s2 * c2.y - s1 * c0.y;   T.r[7] = s2 * c2.z + s1 * c0.x;  T.r[8] = 1.0f + s2 * c1.z;
+        T.t[0] = -(s1 * c3.x + s2 * c4.x);
+        T.t[1] = -(s1 * c3.y + s2 * c4.y);
+        T.t[2] = -(s1 * c3.z + s2 * c4.z);
+        compose(cur, T, nxt);
+        cur = nxt;
+        if (i >= 1) emit_frame(tb, s_out, 2 + 3 * f + (i - 1), cur);
+      }
+#pragma unroll
+      for (int q = 0; q < 16; ++q) ang[q] = ang[q + 4];
+    }
+  }
+  __syncthreads();
+  // transposed, fully coalesced store: element idx = hand*63 + comp <- s_out[comp][hand]
+  float* dst = landmarks + base * 63;
+  const int total = n_here * 63;
+  for (int i = tid; i < total; i += kFast) {
+    const int h = i / 63, c = i - h * 63;
+    dst[i] = s_out[c * kOutLd + h];
+  }
+  __syncthreads();  // the buffer is reused as the input stage of the next tile
+  }
+}
+
 }  // namespace
 
 extern "C" int at_fk_skin_f32(const float* joint_angles, const float* wrist_xforms, const int64_t* hand_idx,
@@ -166,6 +370,20 @@ extern "C" int at_fk_skin_f32(const float* joint_angles, const float* wrist_xfor
   if (!attr_set) {
     cudaFuncSetAttribute(fk_skin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
     attr_set = true;
+  }
+  if (!model->per_sample && model->n_weights <= 3) {
+    constexpr int fast_smem = 63 * kOutLd * (int)sizeof(float);
+    static_assert(kFast * (kJaLd + kWxLd) <= 63 * kOutLd, "input staging must fit the output buffer");
+    static bool fast_attr = false;
+    if (!fast_attr) {
+      cudaFuncSetAttribute(fk_skin_shared_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fast_smem);
+      cudaFuncSetAttribute(fk_skin_shared_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+      fast_attr = true;
+    }
+    const int64_t fb = std::min<int64_t>((n + kFast - 1) / kFast, 3 * at::kNumSMs);  // persistent: 3 CTAs per SM
+    fk_skin_shared_kernel<<<(unsigned)fb, kFast, fast_smem, (cudaStream_t)stream>>>(joint_angles, wrist_xforms, hand_idx,
+                                                                                     *model, n, landmarks);
+    return at::check_launch("fk_skin_shared_kernel");
   }
   const int64_t blocks = (n + kBlock - 1) / kBlock;
   AT_REQUIRE(blocks <= 0x7fffffffLL, "at_fk_skin_f32: n too large");

@@ -1,2 +1,5 @@
-timeout 600 python -m pytest tests/test_gpu_kernels.py -m gpu -x -q -k crop 2>&1 | tail -5
-timeout 300 python scripts/kernel_roofline.py 2>&1 | grep crop_res | tee gpurun_out/kernel_roofline.log
+timeout 200 python scripts/tc_probe.py fp16 > gpurun_out/probe.log 2>&1; grep -E "layers ok|bad=[1-9]|rc=|c=2048" gpurun_out/probe.log
+AT_TC_DBG=32 timeout 100 python scripts/tc_time.py fp16 2048
+timeout 100 python scripts/tc_time.py fp16 2048
+AT_TC_DBG=32 timeout 100 python scripts/tc_time.py bf16 2048
+timeout 100 python scripts/tc_time.py bf16 2048

@@ -84,6 +84,12 @@ class BatchedHandTracker:
         self._hm_dev = HandModel(*[
             (v.to(self._device) if isinstance(v, torch.Tensor) else v) for v in hand_model_mm
         ])
+        # host->device ingest: a copy stream and two device staging slots, so that the H2D copy of
+        # step i+1 overlaps the kernels of step i (frames are 1.22 MB each: ingest is the e2e bound)
+        self._copy_stream = torch.cuda.Stream(device=self._device)
+        self._stage = [None, None]
+        self._stage_free = [None, None]
+        self._slot = 0
 
     @property
     def device(self):
@@ -108,8 +114,30 @@ class BatchedHandTracker:
         return BatchResult(out.joint_angles, wrist_mm, lm)
 
     def step(self, host_batch: FrameBatch, out_host: Optional[dict] = None) -> dict:
-        """Host buffers in, host buffers out (H2D + kernels + D2H on the current stream)."""
-        r = self.step_device(host_batch.to(self._device))
+        """Host buffers in, host buffers out: H2D on the copy stream into one of two staging slots
+        (overlaps the previous call's kernels), kernels + D2H on the current stream.  Nothing here
+        synchronises the host; results in `out_host` are valid after a stream synchronize."""
+        slot, self._slot = self._slot, self._slot ^ 1
+        cur = torch.cuda.current_stream(self._device)
+        cs = self._copy_stream
+        st = self._stage[slot]
+        fields = list(host_batch.__dataclass_fields__)
+        if st is None or any(getattr(st, f).shape != getattr(host_batch, f).shape for f in fields):
+            st = FrameBatch(*[torch.empty_like(getattr(host_batch, f), device=self._device) for f in fields])
+            self._stage[slot] = st
+            self._stage_free[slot] = None
+        if self._stage_free[slot] is not None:
+            cs.wait_event(self._stage_free[slot])  # the kernels that last read this slot are done
+        with torch.cuda.stream(cs):
+            for f in fields:
+                getattr(st, f).copy_(getattr(host_batch, f), non_blocking=True)
+            ready = torch.cuda.Event()
+            ready.record(cs)
+        cur.wait_event(ready)
+        r = self.step_device(st)
+        free = torch.cuda.Event()
+        free.record(cur)
+        self._stage_free[slot] = free
         if out_host is None:
             out_host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True) for k, v in vars(r).items()}
         for k, v in vars(r).items():

@@ -1,5 +1,3 @@
-timeout 200 python scripts/tc_probe.py fp16 > gpurun_out/probe.log 2>&1; grep -E "layers ok|bad=[1-9]|rc=|c=2048" gpurun_out/probe.log
-AT_TC_DBG=32 timeout 100 python scripts/tc_time.py fp16 2048
-timeout 100 python scripts/tc_time.py fp16 2048
-AT_TC_DBG=32 timeout 100 python scripts/tc_time.py bf16 2048
-timeout 100 python scripts/tc_time.py bf16 2048
+timeout 600 python -m pytest tests/test_gpu_model.py -m gpu -x -q 2>&1 | tail -2
+timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/bench_iter.json 2>gpurun_out/bench_iter.err; tail -3 gpurun_out/bench_iter.err; python -c "
+import json; d=json.load(open('gpurun_out/bench_iter.json')); print(d['value'], d['ms_per_step'], d['stages'], d['roofline']['achieved'], 'e2e', d['e2e']['value'])"

@@ -7,6 +7,8 @@
 // One CTA handles a quarter of one crop (24 rows), threads walk dst pixels in raster order so
 // output stores are fully coalesced and the gathered source taps of a warp are neighbours
 // (they hit the same few 128B lines through L1).
+#include <stdlib.h>
+
 #include "at_common.cuh"
 
 namespace {
@@ -239,6 +241,169 @@ crop_resample_fast_kernel(const uint8_t* __restrict__ src, int64_t frame_stride,
   }
 }
 
+
+// ------------------------------------------------------------------------------------------
+// Shared-memory-staged resampler (default for AT_MAP_FP32): one CTA per crop.
+//  1. the fast map is evaluated on the crop's BOUNDARY pixels; their min/max (the map is
+//     continuous, so the image of the boundary bounds the image of the crop) give the source
+//     bounding box, clipped to the image and widened by the bilinear footprint;
+//  2. the box is loaded row by row with coalesced 4-byte loads into shared memory - every source
+//     byte crosses the memory system ONCE.  `src` may be device memory or PINNED HOST memory
+//     (zero-copy ingest: only the ~30 KB box of each crop crosses PCIe instead of the 305 KB view);
+//  3. the fixed-point bilinear gather reads its 4 taps from shared memory.
+// Crops whose box does not fit (very wide crops), that look behind the camera, or whose source
+// layout is not 4-byte aligned take the direct global-memory gather instead.
+constexpr int kStageBytes = 72 * 1024;
+
+__device__ __forceinline__ int remap_fixed_u8_smem(const uint8_t* __restrict__ tile, int pitch, int x0a, int y0, int bw,
+                                                   int bh, int W, int H, float wx, float wy) {
+  const int sx = __float2int_rn(wx * 32.0f);
+  const int sy = __float2int_rn(wy * 32.0f);
+  const int ix = min(max(sx >> 5, -32768), 32767);
+  const int iy = min(max(sy >> 5, -32768), 32767);
+  const int fx = sx & 31, fy = sy & 31;
+  const bool x0 = (unsigned)ix < (unsigned)W, x1 = (unsigned)(ix + 1) < (unsigned)W;
+  const bool y0v = (unsigned)iy < (unsigned)H, y1v = (unsigned)(iy + 1) < (unsigned)H;
+  // box-relative tap coordinates, each clamped into the tile: taps outside the image are masked by
+  // the border tests above, and a (never observed) map excursion cannot read outside the tile
+  const int cx0 = min(max(ix - x0a, 0), bw - 1), cx1 = min(max(ix + 1 - x0a, 0), bw - 1);
+  const int cy0 = min(max(iy - y0, 0), bh - 1) * pitch, cy1 = min(max(iy + 1 - y0, 0), bh - 1) * pitch;
+  const int t00 = (y0v && x0) ? tile[cy0 + cx0] : 0;
+  const int t01 = (y0v && x1) ? tile[cy0 + cx1] : 0;
+  const int t10 = (y1v && x0) ? tile[cy1 + cx0] : 0;
+  const int t11 = (y1v && x1) ? tile[cy1 + cx1] : 0;
+  const int acc = ((32 - fy) * (32 - fx) * t00 + (32 - fy) * fx * t01 + fy * (32 - fx) * t10 + fy * fx * t11) * 32;
+  return (acc + 16384) >> 15;
+}
+
+__global__ void __launch_bounds__(kThreads)
+crop_resample_staged_kernel(const uint8_t* __restrict__ src, int64_t frame_stride, int64_t view_stride, int64_t row_stride,
+                            const AtCropParams* __restrict__ params, int dst_w, int dst_h, void* __restrict__ out,
+                            int out_dtype, unsigned long long* __restrict__ staged_bytes) {
+  extern __shared__ __align__(16) uint8_t tile[];
+  __shared__ FastParams P;
+  __shared__ int s_meta[4];
+  __shared__ float s_red[kThreads / 32][4];
+  __shared__ int s_behind;
+  __shared__ int s_box[6];  // x0a, y0, box width (bytes, multiple of 4), box height, direct flag
+  const int crop = blockIdx.x;
+  const AtCropParams& g = params[crop];
+  if (threadIdx.x < 9) P.M[threadIdx.x] = (float)g.M[threadIdx.x];
+  if (threadIdx.x < 3) P.d[threadIdx.x] = (float)g.d[threadIdx.x];
+  if (threadIdx.x == 32) {
+    P.ifdx = 1.0f / (float)g.f_dst[0]; P.ifdy = 1.0f / (float)g.f_dst[1];
+    P.qx0 = -(float)g.c_dst[0] * P.ifdx; P.qy0 = -(float)g.c_dst[1] * P.ifdy;
+    P.fsx = (float)g.f_src[0]; P.fsy = (float)g.f_src[1]; P.csx = (float)g.c_src[0]; P.csy = (float)g.c_src[1];
+    P.k1 = (float)g.k[0]; P.k2 = (float)g.k[1]; P.k3 = (float)g.k[2]; P.k4 = (float)g.k[3];
+    P.p1 = (float)g.k[4]; P.p2 = (float)g.k[5]; P.k5 = (float)g.k[6]; P.k6 = (float)g.k[7];
+    s_meta[0] = g.frame; s_meta[1] = g.view; s_meta[2] = g.src_w; s_meta[3] = g.src_h;
+    s_behind = 0;
+  }
+  __syncthreads();
+  const int W = s_meta[2], H = s_meta[3];
+  const uint8_t* img = src + (int64_t)s_meta[0] * frame_stride + (int64_t)s_meta[1] * view_stride;
+
+  // ---- 1. source bounding box from the boundary pixels
+  float mnx = 3.0e38f, mny = 3.0e38f, mxx = -3.0e38f, mxy = -3.0e38f;
+  const int nb = 2 * (dst_w + dst_h);
+  for (int i = threadIdx.x; i < nb; i += kThreads) {
+    int x, y;
+    if (i < dst_w) { x = i; y = 0; }
+    else if (i < 2 * dst_w) { x = i - dst_w; y = dst_h - 1; }
+    else if (i < 2 * dst_w + dst_h) { x = 0; y = i - 2 * dst_w; }
+    else { x = dst_w - 1; y = i - 2 * dst_w - dst_h; }
+    float wx, wy;
+    map_pixel_fast(P, fmaf((float)x, P.ifdx, P.qx0), fmaf((float)y, P.ifdy, P.qy0), wx, wy);
+    if (wx == -1.0f && wy == -1.0f) s_behind = 1;  // ez < 0 somewhere on the boundary (or exactly (-1,-1))
+    mnx = fminf(mnx, wx); mxx = fmaxf(mxx, wx);
+    mny = fminf(mny, wy); mxy = fmaxf(mxy, wy);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    mnx = fminf(mnx, __shfl_xor_sync(0xffffffffu, mnx, o)); mxx = fmaxf(mxx, __shfl_xor_sync(0xffffffffu, mxx, o));
+    mny = fminf(mny, __shfl_xor_sync(0xffffffffu, mny, o)); mxy = fmaxf(mxy, __shfl_xor_sync(0xffffffffu, mxy, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    float* r = s_red[threadIdx.x >> 5];
+    r[0] = mnx; r[1] = mxx; r[2] = mny; r[3] = mxy;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < kThreads / 32; ++w) {
+      mnx = fminf(mnx, s_red[w][0]); mxx = fmaxf(mxx, s_red[w][1]);
+      mny = fminf(mny, s_red[w][2]); mxy = fmaxf(mxy, s_red[w][3]);
+    }
+    // taps: ix = round(32 wx) >> 5 in [floor(wx - 1/64), floor(wx + 1/64)], and ix + 1; 1 px of slack
+    const float lim = 1.0e6f;
+    mnx = fminf(fmaxf(mnx, -lim), lim); mxx = fminf(fmaxf(mxx, -lim), lim);
+    mny = fminf(fmaxf(mny, -lim), lim); mxy = fminf(fmaxf(mxy, -lim), lim);
+    int x0 = max(0, (int)floorf(mnx) - 2), x1 = min(W - 1, (int)floorf(mxx) + 3);
+    int y0 = max(0, (int)floorf(mny) - 2), y1 = min(H - 1, (int)floorf(mxy) + 3);
+    int direct = s_behind;
+    int x0a = x0 & ~3, bw = 0, bh = 0;
+    if (x1 < x0 || y1 < y0) {
+      x0a = 0; y0 = 0; bw = 4; bh = 2;   // box outside the image: every tap is the constant border
+      x0 = 0;
+    } else {
+      bw = ((x1 + 1 - x0a) + 3) & ~3;
+      bh = y1 - y0 + 1;
+      if (bh < 2) { if (y0 > 0) --y0; bh = 2; }
+      if (bw < 4) bw = 4;
+    }
+    const bool aligned = ((W | (int)(view_stride & 3) | (int)(row_stride & 3) | (int)(frame_stride & 3)) & 3) == 0 &&
+                         (((uintptr_t)src) & 3) == 0;
+    if (!aligned || (long long)bw * bh > kStageBytes || x0a + bw > ((W + 3) & ~3) || y0 + bh > H) direct = 1;
+    s_box[0] = x0a; s_box[1] = y0; s_box[2] = bw; s_box[3] = bh; s_box[4] = direct;
+    if (staged_bytes != nullptr) atomicAdd(staged_bytes, direct ? (unsigned long long)(4ll * dst_w * dst_h) : (unsigned long long)((long long)bw * bh));
+  }
+  __syncthreads();
+  const int x0a = s_box[0], y0 = s_box[1], bw = s_box[2], bh = s_box[3];
+  const bool direct = s_box[4] != 0;
+
+  // ---- 2. stage the box (coalesced 32-bit loads; rows are 4-byte aligned by construction)
+  if (!direct) {
+    const int wpr = bw >> 2;
+    const int total = wpr * bh;
+    uint32_t* t32 = reinterpret_cast<uint32_t*>(tile);
+    for (int i = threadIdx.x; i < total; i += kThreads) {
+      const int r = i / wpr, c = i - r * wpr;
+      const int yy = y0 + r;
+      uint32_t v = 0u;
+      if (yy < H) v = __ldg(reinterpret_cast<const uint32_t*>(img + (int64_t)yy * row_stride + x0a) + c);
+      t32[i] = v;
+    }
+  }
+  __syncthreads();
+
+  // ---- 3. map + gather, 4 consecutive dst pixels per thread
+  const int groups_per_row = dst_w / kFastPx;
+  const int ngroups = groups_per_row * dst_h;
+  const int64_t obase = (int64_t)crop * dst_w * dst_h;
+  for (int gi = threadIdx.x; gi < ngroups; gi += kThreads) {
+    const int y = gi / groups_per_row, xg = (gi - y * groups_per_row) * kFastPx;
+    const float qy = fmaf((float)y, P.ifdy, P.qy0);
+    int v[kFastPx];
+#pragma unroll
+    for (int i = 0; i < kFastPx; ++i) {
+      float wx, wy;
+      map_pixel_fast(P, fmaf((float)(xg + i), P.ifdx, P.qx0), qy, wx, wy);
+      v[i] = direct ? remap_fixed_u8(img, row_stride, W, H, wx, wy)
+                    : remap_fixed_u8_smem(tile, bw, x0a, y0, bw, bh, W, H, wx, wy);
+    }
+    const int64_t o = obase + (int64_t)y * dst_w + xg;
+    if (out_dtype == AT_U8) {
+      *reinterpret_cast<uchar4*>((uint8_t*)out + o) = make_uchar4((uint8_t)v[0], (uint8_t)v[1], (uint8_t)v[2], (uint8_t)v[3]);
+    } else if (out_dtype == AT_F32) {
+      *reinterpret_cast<float4*>((float*)out + o) = make_float4(__fdiv_rn((float)v[0], 255.0f), __fdiv_rn((float)v[1], 255.0f),
+                                                                 __fdiv_rn((float)v[2], 255.0f), __fdiv_rn((float)v[3], 255.0f));
+    } else {
+      __nv_bfloat16* ob = (__nv_bfloat16*)out + o;
+#pragma unroll
+      for (int i = 0; i < kFastPx; ++i) ob[i] = __float2bfloat16_rn(__fdiv_rn((float)v[i], 255.0f));
+    }
+  }
+}
+
 // data_transform.py:78-144, float64 map (numpy promotes float32 x int32 -> float64 at :99).
 __global__ void __launch_bounds__(kThreads)
 resample_homography_kernel(const float* __restrict__ images, int H, int W, const float* __restrict__ xfs, int oh,
@@ -278,6 +443,14 @@ extern "C" int at_crop_resample_fisheye62_u8(const uint8_t* src, int64_t frame_s
                                              int64_t row_stride, const AtCropParams* params, int n_crops,
                                              int dst_w, int dst_h, void* out, int out_dtype, int map_mode,
                                              void* stream) {
+  return at_crop_resample_fisheye62_u8_ex(src, frame_stride, view_stride, row_stride, params, n_crops, dst_w, dst_h, out,
+                                          out_dtype, map_mode, nullptr, stream);
+}
+
+extern "C" int at_crop_resample_fisheye62_u8_ex(const uint8_t* src, int64_t frame_stride, int64_t view_stride,
+                                                int64_t row_stride, const AtCropParams* params, int n_crops,
+                                                int dst_w, int dst_h, void* out, int out_dtype, int map_mode,
+                                                unsigned long long* staged_bytes, void* stream) {
   AT_REQUIRE(n_crops >= 0, "at_crop_resample_fisheye62_u8: n_crops < 0");
   if (n_crops == 0) return AT_OK;
   AT_REQUIRE(src && params && out, "at_crop_resample_fisheye62_u8: NULL pointer");
@@ -286,11 +459,29 @@ extern "C" int at_crop_resample_fisheye62_u8(const uint8_t* src, int64_t frame_s
              "at_crop_resample_fisheye62_u8: bad out_dtype %d", out_dtype);
   AT_REQUIRE(map_mode == AT_MAP_FP32 || map_mode == AT_MAP_FP64, "at_crop_resample_fisheye62_u8: bad map_mode %d",
              map_mode);
+  // pinned host source (zero-copy ingest) -> the staged kernel: every source byte crosses PCIe once
+  bool src_on_host = false;
+  {
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, src) == cudaSuccess) src_on_host = attr.type == cudaMemoryTypeHost;
+    else cudaGetLastError();
+  }
+  AT_REQUIRE(!src_on_host || (map_mode == AT_MAP_FP32 && dst_w % 4 == 0),
+             "at_crop_resample_fisheye62_u8: a host (pinned) source needs AT_MAP_FP32 and dst_w % 4 == 0");
   dim3 grid((unsigned)n_crops, kSplit);
   if (map_mode == AT_MAP_FP64)
     crop_resample_kernel<double><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
         src, frame_stride, view_stride, row_stride, params, dst_w, dst_h, out, out_dtype);
-  else if (dst_w % kFastPx == 0)
+  else if (dst_w % kFastPx == 0 && (src_on_host || staged_bytes != nullptr || getenv("AT_CROP_STAGED") != nullptr)) {
+    static bool attr = false;
+    if (!attr) {
+      cudaFuncSetAttribute(crop_resample_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStageBytes);
+      cudaFuncSetAttribute(crop_resample_staged_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+      attr = true;
+    }
+    crop_resample_staged_kernel<<<(unsigned)n_crops, kThreads, kStageBytes, (cudaStream_t)stream>>>(
+        src, frame_stride, view_stride, row_stride, params, dst_w, dst_h, out, out_dtype, staged_bytes);
+  } else if (dst_w % kFastPx == 0)
     crop_resample_fast_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(src, frame_stride, view_stride, row_stride,
                                                                            params, dst_w, dst_h, out, out_dtype);
   else

@@ -66,7 +66,11 @@ class BatchResult:
 
 class BatchedHandTracker:
     def __init__(self, model, hand_model_mm: HandModel, max_slots: int, map_mode: str = "fp32",
-                 crop_dtype: torch.dtype = torch.uint8) -> None:
+                 crop_dtype: torch.dtype = torch.uint8, ingest: str = "zero_copy") -> None:
+        """ingest: how step() brings HOST frames to the GPU.  "zero_copy" (needs pinned frames and
+        map_mode "fp32"): the resampler reads the pinned frames in place and pulls only each crop's
+        source bounding box over PCIe (~30 KB per crop instead of the 305 KB view); "copy": the
+        whole frame tensor is copied on a side stream, overlapped with the previous step."""
         if not torch.cuda.is_available():
             raise _cabi.AbsoluteTrackError("BatchedHandTracker needs a CUDA device (no CPU fallback)")
         self._device = torch.device("cuda", torch.cuda.current_device())
@@ -86,6 +90,10 @@ class BatchedHandTracker:
         ])
         # host->device ingest: a copy stream and two device staging slots, so that the H2D copy of
         # step i+1 overlaps the kernels of step i (frames are 1.22 MB each: ingest is the e2e bound)
+        if ingest not in ("zero_copy", "copy"):
+            raise ValueError("ingest must be 'zero_copy' or 'copy'")
+        self._ingest = ingest
+        self.pulled_bytes = torch.zeros(1, dtype=torch.int64, device=self._device)  # bytes the resampler pulled from host frames
         self._copy_stream = torch.cuda.Stream(device=self._device)
         self._stage = [None, None]
         self._stage_free = [None, None]
@@ -99,7 +107,8 @@ class BatchedHandTracker:
         """All inputs already on the device."""
         S, H, V, W = b.frames.shape
         crops = crop_resample_cuda(
-            b.frames, H * V * W, W, V * W, b.crop_params, (96, 96), self._crop_dtype, self._map_mode
+            b.frames, H * V * W, W, V * W, b.crop_params, (96, 96), self._crop_dtype, self._map_mode,
+            staged_bytes=None if b.frames.is_cuda else self.pulled_bytes,
         )
         out = self._model.regress_pose_use_skeleton(
             InputFrameData(crops, b.intrinsics, b.extrinsics),
@@ -121,11 +130,16 @@ class BatchedHandTracker:
         cur = torch.cuda.current_stream(self._device)
         cs = self._copy_stream
         st = self._stage[slot]
-        fields = list(host_batch.__dataclass_fields__)
+        zero_copy = self._ingest == "zero_copy" and self._map_mode == "fp32" and host_batch.frames.is_pinned()
+        fields = [f for f in host_batch.__dataclass_fields__ if not (zero_copy and f == "frames")]
         if st is None or any(getattr(st, f).shape != getattr(host_batch, f).shape for f in fields):
-            st = FrameBatch(*[torch.empty_like(getattr(host_batch, f), device=self._device) for f in fields])
+            st = FrameBatch(*[
+                (torch.empty_like(getattr(host_batch, f), device=self._device) if f in fields else None)
+                for f in host_batch.__dataclass_fields__])
             self._stage[slot] = st
             self._stage_free[slot] = None
+        if zero_copy:
+            st.frames = host_batch.frames  # read in place by the resampler; the caller keeps it alive and unchanged
         if self._stage_free[slot] is not None:
             cs.wait_event(self._stage_free[slot])  # the kernels that last read this slot are done
         with torch.cuda.stream(cs):

@@ -83,19 +83,24 @@ def crop_resample_cuda(
     out_dtype: torch.dtype = torch.float32,
     map_mode: str = "fp64",
     out: Optional[torch.Tensor] = None,
+    staged_bytes: Optional[torch.Tensor] = None,
 ) -> torch.Tensor:
-    """Launch at_crop_resample_fisheye62_u8.  `src` uint8 CUDA tensor, `params` uint8 CUDA [c,256]."""
+    """Launch at_crop_resample_fisheye62_u8.  `src` uint8 CUDA tensor - or, in map_mode "fp32", a
+    PINNED host tensor (zero-copy ingest: the kernel pulls each crop's source bounding box over
+    PCIe once, through shared memory); `params` uint8 CUDA [c,256]."""
     lib = _cabi.lib()
-    assert src.is_cuda and src.dtype == torch.uint8 and params.is_cuda and params.dtype == torch.uint8
+    assert src.dtype == torch.uint8 and params.is_cuda and params.dtype == torch.uint8
+    if not src.is_cuda and not (src.is_pinned() and map_mode == "fp32"):
+        raise _cabi.AbsoluteTrackError("crop source must be a CUDA tensor (or a pinned host tensor with map_mode='fp32')")
     c = params.shape[0]
     W, H = int(dst_wh[0]), int(dst_wh[1])
     code = {torch.uint8: _cabi.AT_U8, torch.float32: _cabi.AT_F32, torch.bfloat16: _cabi.AT_BF16}[out_dtype]
     if out is None:
-        out = torch.empty((c, H, W), dtype=out_dtype, device=src.device)
-    with torch.cuda.device(src.device):
-        rc = lib.at_crop_resample_fisheye62_u8(
+        out = torch.empty((c, H, W), dtype=out_dtype, device=params.device)
+    with torch.cuda.device(params.device):
+        rc = lib.at_crop_resample_fisheye62_u8_ex(
             src.data_ptr(), frame_stride, view_stride, row_stride, params.contiguous().data_ptr(), c, W, H,
-            out.data_ptr(), code, MAP_MODES[map_mode], _cabi.stream_ptr(src.device),
+            out.data_ptr(), code, MAP_MODES[map_mode], _cabi.ptr(staged_bytes), _cabi.stream_ptr(params.device),
         )
     _cabi.check(rc, "at_crop_resample_fisheye62_u8")
     return out

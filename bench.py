@@ -185,6 +185,7 @@ def main():
                     help="encoder operand format; fp16 and bf16 run the same tcgen05 kind::f16 kernels with fp32 accumulation "
                          "(fp16 meets the 0.1 mm end-to-end tolerance, bf16 does not: DESIGN.md)")
     ap.add_argument("--map-mode", default="fp32", choices=["fp32", "fp64"])
+    ap.add_argument("--ingest", default="zero_copy", choices=["zero_copy", "copy"], help="e2e arm: how host frames reach the GPU")
     ap.add_argument("--ref-frames", type=int, default=24, help="frames per step of the CPU reference arm")
     ap.add_argument("--cpu-frames", type=int, default=96, help="bounded CPU-baseline sample (frames)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -219,7 +220,7 @@ def main():
     S = args.frames
     model = model_from_state_dict(make_random_state_dict(0), precision=args.precision)
     hm = synthetic.hand_model()
-    tracker = BatchedHandTracker(model, hm, max_slots=2 * S, map_mode=args.map_mode)
+    tracker = BatchedHandTracker(model, hm, max_slots=2 * S, map_mode=args.map_mode, ingest=args.ingest)
 
     # sequences are sharded by rank (r::world, the reference Sampler's rule, async_dataset.py:558-559)
     seq_ids = np.arange(S) * world + rank
@@ -293,7 +294,14 @@ def main():
 
     ms_e2e, _ = timed(step_host, args.steps, args.warmup)
     e2e_value = world * n / (ms_e2e / args.steps * 1e-3)
-    h2d = host[0].nbytes()
+    small = host[0].nbytes() - host[0].frames.numel()
+    pulled0 = int(tracker.pulled_bytes.item())
+    for i in range(2):
+        step_host(i)
+    torch.cuda.synchronize()
+    pulled = (int(tracker.pulled_bytes.item()) - pulled0) // 2   # bytes the resampler pulled from the pinned frames per step
+    ingest = "zero_copy (source boxes pulled from pinned frames by the resampler)" if pulled > 0 else "copy (whole frames, side stream)"
+    h2d = small + (pulled if pulled > 0 else host[0].frames.numel())
     d2h = sum(v.numel() * v.element_size() for v in out_host[0].values())
 
     # ---- per-stage timings (device resident) for the roofline
@@ -355,7 +363,8 @@ def main():
                        "crops_per_step_per_gpu": c, "map_mode": args.map_mode, "l2": flush_note,
                        "weights": "seeded random state dict (252 keys), BN folded", "sharding": "sequences r::world"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "api": "BatchedHandTracker.step (pinned host buffers)"},
+                    "api": "BatchedHandTracker.step (pinned host buffers)", "ingest": ingest,
+                    "host_frame_bytes_per_step": int(host[0].frames.numel())},
             "gpu_launches": int(launches),
             "roofline": {"bound": "tensor", "kernel": "per-view encoder (all conv launches of at_encoder_forward)",
                          "achieved": enc_tflops, "peak": tf_peak, "unit": "TFLOP/s", "frac": enc_tflops / tf_peak,

@@ -80,6 +80,14 @@ int at_crop_resample_fisheye62_u8(const uint8_t* src, int64_t frame_stride, int6
                                   int64_t row_stride, const AtCropParams* params, int n_crops,
                                   int dst_w, int dst_h, void* out, int out_dtype, int map_mode,
                                   void* stream);
+/* Same, plus an optional device counter.  In AT_MAP_FP32 mode each crop's source bounding box is
+ * staged once through shared memory, so `src` may also be PINNED HOST memory (zero-copy ingest:
+ * only the boxes cross PCIe).  *staged_bytes (device, may be NULL) is incremented by the bytes each
+ * crop pulled from `src`. */
+int at_crop_resample_fisheye62_u8_ex(const uint8_t* src, int64_t frame_stride, int64_t view_stride,
+                                     int64_t row_stride, const AtCropParams* params, int n_crops,
+                                     int dst_w, int dst_h, void* out, int out_dtype, int map_mode,
+                                     unsigned long long* staged_bytes, void* stream);
 
 /* The torch_data pinhole->pinhole resampler.  Replaces data_transform._resample_images_batched
  * (lib/batched_dataset/data_transform.py:78-144): (u,v,1) -> xf[0:3,0:3]*(u,v,1)+xf[0:3,3],

@@ -185,6 +185,55 @@ def test_crop_edge_cases(cuda_lib):
     assert e.shape == (0, 96, 96)
 
 
+def test_crop_staged_path_equals_direct_gather_and_zero_copy(cuda_lib, gold):
+    """AT_MAP_FP32: the shared-memory-staged kernel (bounding box from the boundary pixels) must
+    reproduce the direct global-memory gather bit for bit - on real geometry, on a crop too wide
+    to stage, on a crop that looks away from the camera - and give the same crops when the source
+    frames stay in PINNED HOST memory (zero-copy ingest)."""
+    from absolutetrack_b200.lib.common import camera as C
+    from absolutetrack_b200.lib.tracker.tracker import crop_resample_cuda, pack_crop_params
+
+    G = scenario.geometry()
+    frames = np.stack([scenario.synth_frame("noise", 21), scenario.synth_frame("smooth", 22)])
+    recs = []
+    for k in (0, 5, 40, 77, 120):
+        for h in range(2):
+            for s_ in range(2):
+                cam = int(G["crop_cam"][k, h, s_])
+                if cam < 0:
+                    continue
+                src = C.Fisheye62CameraModel(636, 480, G["cam_f"][cam], G["cam_c"][cam], G["cam_coeffs"][cam], G["camera_to_world"][k, cam])
+                dst = C.PinholePlaneCameraModel(96, 96, G["crop_f"][k, h, s_], G["crop_c"][k, h, s_], [], G["crop_c2w"][k, h, s_])
+                recs.append((k % 2, cam, C.crop_kernel_params(src, dst)))
+    k, h, s_ = 5, 0, 0
+    cam = int(G["crop_cam"][k, h, s_])
+    src = C.Fisheye62CameraModel(636, 480, G["cam_f"][cam], G["cam_c"][cam], G["cam_coeffs"][cam], G["camera_to_world"][k, cam])
+    c2w = G["crop_c2w"][k, h, s_]
+    back = c2w.copy()
+    back[:3, :3] = c2w[:3, :3] @ np.diag([1.0, -1.0, -1.0])
+    for dst in (C.PinholePlaneCameraModel(96, 96, (20.0, 20.0), G["crop_c"][k, h, s_], [], c2w),        # wider than the image
+                C.PinholePlaneCameraModel(96, 96, (45.0, 45.0), G["crop_c"][k, h, s_], [], c2w),        # box too big to stage
+                C.PinholePlaneCameraModel(96, 96, G["crop_f"][k, h, s_], G["crop_c"][k, h, s_], [], back),   # behind the camera
+                C.PinholePlaneCameraModel(96, 96, (300.0, 300.0), (4000.0, 48.0), [], c2w)):            # far outside the image
+        recs.append((0, cam, C.crop_kernel_params(src, dst)))
+    params = torch.from_numpy(pack_crop_params(recs)).cuda()
+    host = torch.from_numpy(frames).pin_memory()
+    dev = host.cuda()
+    args = (480 * 2544, 636, 2544, params, (96, 96), torch.uint8, "fp32")
+    counter = torch.zeros(1, dtype=torch.int64, device="cuda")
+    staged = crop_resample_cuda(dev, *args, staged_bytes=counter)   # a byte counter selects the staged kernel
+    zero_copy = crop_resample_cuda(host, *args)                      # so does a pinned host source
+    direct = crop_resample_cuda(dev, *args)                          # device source: direct gather
+    torch.cuda.synchronize()
+    assert torch.equal(staged, direct)
+    assert torch.equal(zero_copy, direct)
+    assert direct.float().std() > 1
+    per_crop = counter.item() / len(recs)
+    assert 8_000 < per_crop < 80_000, per_crop                     # ~30 KB boxes, not 305 KB views
+    with pytest.raises(Exception):
+        crop_resample_cuda(torch.from_numpy(frames), *args)          # pageable host memory is refused
+
+
 # ------------------------------------------------------------------ homography resampler (a12)
 def test_homography_resampler_matches_oracle(cuda_lib):
     from absolutetrack_b200 import _cabi

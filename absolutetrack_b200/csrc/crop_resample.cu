@@ -352,8 +352,20 @@ crop_resample_staged_kernel(const uint8_t* __restrict__ src, int64_t frame_strid
     }
     const bool aligned = ((W | (int)(view_stride & 3) | (int)(row_stride & 3) | (int)(frame_stride & 3)) & 3) == 0 &&
                          (((uintptr_t)src) & 3) == 0;
-    if (!aligned || (long long)bw * bh > kStageBytes || x0a + bw > ((W + 3) & ~3) || y0 + bh > H) direct = 1;
-    s_box[0] = x0a; s_box[1] = y0; s_box[2] = bw; s_box[3] = bh; s_box[4] = direct;
+    // 16-byte loads when every row of the box has the same 16-byte phase and the widened box stays
+    // inside the (multi-view) source row: 4x fewer, 4x larger requests (matters over PCIe)
+    int vec16 = 0;
+    if (aligned && (row_stride & 15) == 0 && (frame_stride & 15) == 0 && x1 >= x0 && y1 >= y0) {
+      const long long view_off = (long long)s_meta[1] * view_stride;       // offset of the view inside its row
+      const int phase = (int)(((uintptr_t)src + (uintptr_t)view_off + (uintptr_t)x0a) & 15);
+      const int nx0 = x0a - phase;
+      const int nbw = ((x0a + bw - nx0) + 15) & ~15;
+      if (view_off + nx0 >= 0 && view_off + nx0 + nbw <= row_stride && (long long)nbw * bh <= kStageBytes) {
+        x0a = nx0; bw = nbw; vec16 = 1;
+      }
+    }
+    if (!aligned || (long long)bw * bh > kStageBytes || (!vec16 && x0a + bw > ((W + 3) & ~3)) || y0 + bh > H) direct = 1;
+    s_box[0] = x0a; s_box[1] = y0; s_box[2] = bw; s_box[3] = bh; s_box[4] = direct; s_box[5] = vec16;
     if (staged_bytes != nullptr) atomicAdd(staged_bytes, direct ? (unsigned long long)(4ll * dst_w * dst_h) : (unsigned long long)((long long)bw * bh));
   }
   __syncthreads();
@@ -361,7 +373,15 @@ crop_resample_staged_kernel(const uint8_t* __restrict__ src, int64_t frame_strid
   const bool direct = s_box[4] != 0;
 
   // ---- 2. stage the box (coalesced 32-bit loads; rows are 4-byte aligned by construction)
-  if (!direct) {
+  if (!direct && s_box[5]) {
+    const int wpr = bw >> 4;
+    const int total = wpr * bh;
+    uint4* t128 = reinterpret_cast<uint4*>(tile);
+    for (int i = threadIdx.x; i < total; i += kThreads) {
+      const int r = i / wpr, c = i - r * wpr;
+      t128[i] = __ldg(reinterpret_cast<const uint4*>(img + (int64_t)(y0 + r) * row_stride + x0a) + c);
+    }
+  } else if (!direct) {
     const int wpr = bw >> 2;
     const int total = wpr * bh;
     uint32_t* t32 = reinterpret_cast<uint32_t*>(tile);

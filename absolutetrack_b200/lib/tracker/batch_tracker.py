@@ -138,6 +138,9 @@ class BatchedHandTracker:
                 for f in host_batch.__dataclass_fields__])
             self._stage[slot] = st
             self._stage_free[slot] = None
+            # the caching allocator may hand out blocks whose previous users are still running on
+            # the current stream: order the first copy-stream write after them
+            cs.wait_stream(cur)
         if zero_copy:
             st.frames = host_batch.frames  # read in place by the resampler; the caller keeps it alive and unchanged
         if self._stage_free[slot] is not None:

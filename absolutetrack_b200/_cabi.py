@@ -103,6 +103,7 @@ SIGNATURES = {
     "at_launch_count": (_I64, []),
     "at_crop_resample_fisheye62_u8": (_I, [_VP, _I64, _I64, _I64, _VP, _I, _I, _I, _VP, _I, _I, _VP]),
     "at_crop_resample_fisheye62_u8_ex": (_I, [_VP, _I64, _I64, _I64, _VP, _I, _I, _I, _VP, _I, _I, _VP, _VP]),
+    "at_crop_pull_source_boxes_u8": (_I, [_VP, _VP, _I64, _I64, _I64, _I64, _VP, _I, _I, _I, _I, _VP, _VP]),
     "at_resample_homography_f32": (_I, [_VP, _I, _I, _I, _VP, _I, _I, _VP, _F, _VP]),
     "at_fk_skin_f32": (_I, [_VP, _VP, _VP, C.POINTER(AtHandModel), _I64, _VP, _VP]),
     "at_model_layer_table": (_I, [C.POINTER(AtLayerInfo), _I]),

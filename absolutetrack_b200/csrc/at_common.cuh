@@ -32,6 +32,25 @@ inline int check_launch(const char* what) {
 
 constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
 
+// Kernels that must co-reside with a long-lived CTA of ANOTHER kernel (the encoder's conv launches
+// and the source-box pull of the next step) all ask for the SAME shared-memory carve-out (the
+// maximum).  The driver otherwise picks the smallest configuration that fits each launch, and an SM
+// can only switch configuration when it is empty: with a pull CTA resident, the first conv launch
+// that wants a different carve-out stalls until that CTA exits (measured: the encoder blocked for
+// the whole pull; scripts/overlap_probe.cu).  Kernels outside that window keep the default (more L1).
+template <typename K>
+inline void prefer_max_smem_carveout(K kernel) {
+  cudaFuncSetAttribute((const void*)kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+}
+#define AT_CARVEOUT_ONCE(kernel)                                   \
+  do {                                                             \
+    static const bool at_carve_done_ = [] {                        \
+      at::prefer_max_smem_carveout(kernel);                        \
+      return true;                                                 \
+    }();                                                           \
+    (void)at_carve_done_;                                          \
+  } while (0)
+
 __host__ __device__ inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
 
 }  // namespace at

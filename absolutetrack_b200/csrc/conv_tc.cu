@@ -38,6 +38,11 @@ namespace tc {
 
 constexpr int kTileM = 128;
 constexpr int kThreads = 384;
+// Register cap.  The register file is split per SM sub-partition (4 x 16384): 3 warps x 160 regs
+// leave 1024 registers per sub-partition -- room for one 32-register warp of another kernel (the
+// source-box pull of the next step, crop_resample.cu) to stay co-resident.  At 168 (what
+// __launch_bounds__(384, 1) allows) a resident side warp blocks the launch of the next conv CTA.
+constexpr int kMaxRegs = 160;
 constexpr int kMaxTaps = 9;
 constexpr int kSmemBudget = 220 * 1024;
 
@@ -98,7 +103,7 @@ struct EpiCoord {
 // MODE: 0 planar out, 1 planar out + residual, 2 phase-split out + residual, 3 fp32 NHWC out.
 // WRES: the layer's weights stay resident in shared memory (else they stream through a ring).
 template <int NTAPS, int KSTEPS, int MT, int WRES, int MODE>
-__global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
+__global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   using namespace ptx;
   const uint32_t sbase = smem_u32(smem);
@@ -895,6 +900,7 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
     std::lock_guard<std::mutex> lock(mu);
     if (std::find(configured.begin(), configured.end(), fn) == configured.end()) {
       cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget + 4096);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
       if (e != cudaSuccess) {
         set_error("cudaFuncSetAttribute(conv_tc_kernel): %s", cudaGetErrorString(e));
         return AT_ERR_CUDA;
@@ -1008,10 +1014,13 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
     {
       const Level& L0 = P.lv[0];
       const unsigned blocks = (unsigned)((L0.P + 255) / 256);
-      if (crop_dtype == AT_U8)
+      if (crop_dtype == AT_U8) {
+        AT_CARVEOUT_ONCE(stem_pack_kernel<uint8_t>);
         stem_pack_kernel<uint8_t><<<blocks, 256, 0, s>>>((const uint8_t*)crops + (size_t)c0 * 96 * 96, buf(0, 3), L0, fmt);
-      else
+      } else {
+        AT_CARVEOUT_ONCE(stem_pack_kernel<float>);
         stem_pack_kernel<float><<<blocks, 256, 0, s>>>((const float*)crops + (size_t)c0 * 96 * 96, buf(0, 3), L0, fmt);
+      }
       if ((rc = check_launch("stem_pack_kernel"))) return rc;
       ConvIo io;
       memset(&io, 0, sizeof(io));

@@ -424,6 +424,135 @@ crop_resample_staged_kernel(const uint8_t* __restrict__ src, int64_t frame_strid
   }
 }
 
+// ---- source-box pull (host -> device ingest without copying whole frames) -------------------------
+// For every crop: bound the source region its map touches (boundary pixels of the crop, as in the
+// staged kernel), then copy just those rows/columns from `src` (pinned host memory, read over PCIe)
+// into `dst`, a device buffer with the SAME layout.  The ordinary resampler then runs on `dst`: bytes
+// outside the boxes are never read.  Spans are widened to 16-byte address alignment -- harmless,
+// because source and destination share one layout.
+//
+// The kernel is built to hide behind the previous step's encoder: a 384-thread x 168-register
+// conv_tc CTA with ~220 KB of shared memory leaves 1024 registers, ~6 KB of shared memory and warp
+// slots free on its SM.  So: ONE warp per CTA, 32 registers, and the bytes in flight live in a small
+// shared-memory ring filled by cp.async.ca (LDGSTS; the .cg form reads PCIe at half the rate)
+// instead of in registers.  Each lane reads back only the 16-byte slots it filled itself, so
+// cp.async.wait_group is the only synchronisation in the copy loop.  The launch also asks for the
+// maximum shared-memory carve-out, like the conv kernels: see at_common.cuh.
+constexpr int kPullStages = 2;        // ring halves
+
+__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gptr) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gptr) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// word i of the box -> byte offset of its 16-byte word, or 0xFFFFFFFF when the word is past the row / buffer
+__device__ __forceinline__ uint32_t pull_word_offset(int i, int total, int wpr, uint32_t base, uint32_t row_stride,
+                                                     uint32_t bw, uint32_t tb) {
+  if (i >= total) return 0xFFFFFFFFu;
+  const int r = i / wpr, c = i - r * wpr;
+  const uint32_t row0 = base + (uint32_t)r * row_stride;
+  const uint32_t addr = (row0 & ~15u) + ((uint32_t)c << 4);
+  return (addr < row0 + bw && addr + 16u <= tb) ? addr : 0xFFFFFFFFu;
+}
+
+template <int kPullPerLane>  // 16-byte slots per lane per stage: ring = 2 x kPullPerLane x 512 B
+__global__ void __maxnreg__(32)
+crop_pull_boxes_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int64_t total_bytes,
+                       int64_t frame_stride, int64_t view_stride, int64_t row_stride,
+                       const AtCropParams* __restrict__ params, int n_crops, int dst_w, int dst_h,
+                       unsigned long long* __restrict__ pulled_bytes) {
+  __shared__ __align__(16) uint8_t ring[kPullStages * kPullPerLane * 32 * 16];
+  __shared__ FastParams P;
+  const int lane = threadIdx.x;
+  const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(ring) + (uint32_t)lane * 16u;
+  uint32_t my_words = 0u;
+  for (int crop = blockIdx.x; crop < n_crops; crop += gridDim.x) {
+    const AtCropParams& g = params[crop];
+    __syncwarp();
+    if (lane < 9) P.M[lane] = (float)g.M[lane];
+    if (lane < 3) P.d[lane] = (float)g.d[lane];
+    if (lane == 31) {
+      P.ifdx = 1.0f / (float)g.f_dst[0]; P.ifdy = 1.0f / (float)g.f_dst[1];
+      P.qx0 = -(float)g.c_dst[0] * P.ifdx; P.qy0 = -(float)g.c_dst[1] * P.ifdy;
+      P.fsx = (float)g.f_src[0]; P.fsy = (float)g.f_src[1]; P.csx = (float)g.c_src[0]; P.csy = (float)g.c_src[1];
+      P.k1 = (float)g.k[0]; P.k2 = (float)g.k[1]; P.k3 = (float)g.k[2]; P.k4 = (float)g.k[3];
+      P.p1 = (float)g.k[4]; P.p2 = (float)g.k[5]; P.k5 = (float)g.k[6]; P.k6 = (float)g.k[7];
+    }
+    __syncwarp();
+    const int W = g.src_w, H = g.src_h;
+    float mnx = 3.0e38f, mny = 3.0e38f, mxx = -3.0e38f, mxy = -3.0e38f;
+    bool behind = false;
+    const int nb = 2 * (dst_w + dst_h);
+    for (int i = lane; i < nb; i += 32) {
+      int x, y;
+      if (i < dst_w) { x = i; y = 0; }
+      else if (i < 2 * dst_w) { x = i - dst_w; y = dst_h - 1; }
+      else if (i < 2 * dst_w + dst_h) { x = 0; y = i - 2 * dst_w; }
+      else { x = dst_w - 1; y = i - 2 * dst_w - dst_h; }
+      float wx, wy;
+      map_pixel_fast(P, fmaf((float)x, P.ifdx, P.qx0), fmaf((float)y, P.ifdy, P.qy0), wx, wy);
+      behind |= (wx == -1.0f && wy == -1.0f);
+      mnx = fminf(mnx, wx); mxx = fmaxf(mxx, wx);
+      mny = fminf(mny, wy); mxy = fmaxf(mxy, wy);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      mnx = fminf(mnx, __shfl_xor_sync(0xffffffffu, mnx, o)); mxx = fmaxf(mxx, __shfl_xor_sync(0xffffffffu, mxx, o));
+      mny = fminf(mny, __shfl_xor_sync(0xffffffffu, mny, o)); mxy = fmaxf(mxy, __shfl_xor_sync(0xffffffffu, mxy, o));
+    }
+    behind = __any_sync(0xffffffffu, behind);
+    const float lim = 1.0e6f;
+    mnx = fminf(fmaxf(mnx, -lim), lim); mxx = fminf(fmaxf(mxx, -lim), lim);
+    mny = fminf(fmaxf(mny, -lim), lim); mxy = fminf(fmaxf(mxy, -lim), lim);
+    // taps: ix = round(32 wx) >> 5 and ix + 1 (see the staged kernel); 2 px of slack
+    int x0 = max(0, (int)floorf(mnx) - 2), x1 = min(W - 1, (int)floorf(mxx) + 3);
+    int y0 = max(0, (int)floorf(mny) - 2), y1 = min(H - 1, (int)floorf(mxy) + 3);
+    if (behind) { x0 = 0; y0 = 0; x1 = W - 1; y1 = H - 1; }  // part of the crop looks behind the camera: whole view
+    const int bw = x1 - x0 + 1, bh = y1 - y0 + 1;
+    if (bw <= 0 || bh <= 0) continue;                         // nothing inside the image (warp-uniform)
+    const uint32_t base = (uint32_t)((int64_t)g.frame * frame_stride + (int64_t)g.view * view_stride +
+                                     (int64_t)y0 * row_stride + x0);
+    const int wpr = (bw + 15 + 15) >> 4;  // 16-byte words per row, upper bound over row phases
+    const int total = wpr * bh;
+    const uint32_t tb = (uint32_t)total_bytes, rs = (uint32_t)row_stride;
+    constexpr int kStageWords = 32 * kPullPerLane;
+    const int nst = (total + kStageWords - 1) / kStageWords;
+    // prologue: fill kPullStages - 1 stages
+    for (int st = 0; st < nst + kPullStages - 1; ++st) {
+      if (st < nst) {
+        const uint32_t sbase = ring_s + (uint32_t)(st % kPullStages) * (kStageWords * 16);
+#pragma unroll
+        for (int u = 0; u < kPullPerLane; ++u) {
+          const uint32_t a = pull_word_offset(st * kStageWords + u * 32 + lane, total, wpr, base, rs, (uint32_t)bw, tb);
+          if (a != 0xFFFFFFFFu) cp_async16(sbase + u * 512, src + a);
+        }
+      }
+      cp_async_commit();
+      const int dr = st - (kPullStages - 1);  // stage to drain
+      if (dr >= 0) {
+        cp_async_wait<kPullStages - 1>();
+        const uint8_t* sb = ring + lane * 16 + (dr % kPullStages) * (kStageWords * 16);
+#pragma unroll
+        for (int u = 0; u < kPullPerLane; ++u) {
+          const uint32_t a = pull_word_offset(dr * kStageWords + u * 32 + lane, total, wpr, base, rs, (uint32_t)bw, tb);
+          if (a != 0xFFFFFFFFu) {
+            *reinterpret_cast<uint4*>(dst + a) = *reinterpret_cast<const uint4*>(sb + u * 512);
+            ++my_words;
+          }
+        }
+      }
+    }
+    cp_async_wait<0>();
+  }
+  if (pulled_bytes != nullptr) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) my_words += __shfl_xor_sync(0xffffffffu, my_words, o);
+    if (lane == 0 && my_words) atomicAdd(pulled_bytes, 16ull * my_words);
+  }
+}
+
 // data_transform.py:78-144, float64 map (numpy promotes float32 x int32 -> float64 at :99).
 __global__ void __launch_bounds__(kThreads)
 resample_homography_kernel(const float* __restrict__ images, int H, int W, const float* __restrict__ xfs, int oh,
@@ -489,10 +618,10 @@ extern "C" int at_crop_resample_fisheye62_u8_ex(const uint8_t* src, int64_t fram
   AT_REQUIRE(!src_on_host || (map_mode == AT_MAP_FP32 && dst_w % 4 == 0),
              "at_crop_resample_fisheye62_u8: a host (pinned) source needs AT_MAP_FP32 and dst_w % 4 == 0");
   dim3 grid((unsigned)n_crops, kSplit);
-  if (map_mode == AT_MAP_FP64)
+  if (map_mode == AT_MAP_FP64) {
     crop_resample_kernel<double><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
         src, frame_stride, view_stride, row_stride, params, dst_w, dst_h, out, out_dtype);
-  else if (dst_w % kFastPx == 0 && (src_on_host || staged_bytes != nullptr || getenv("AT_CROP_STAGED") != nullptr)) {
+  } else if (dst_w % kFastPx == 0 && (src_on_host || staged_bytes != nullptr || getenv("AT_CROP_STAGED") != nullptr)) {
     static bool attr = false;
     if (!attr) {
       cudaFuncSetAttribute(crop_resample_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStageBytes);
@@ -501,12 +630,13 @@ extern "C" int at_crop_resample_fisheye62_u8_ex(const uint8_t* src, int64_t fram
     }
     crop_resample_staged_kernel<<<(unsigned)n_crops, kThreads, kStageBytes, (cudaStream_t)stream>>>(
         src, frame_stride, view_stride, row_stride, params, dst_w, dst_h, out, out_dtype, staged_bytes);
-  } else if (dst_w % kFastPx == 0)
+  } else if (dst_w % kFastPx == 0) {
     crop_resample_fast_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(src, frame_stride, view_stride, row_stride,
                                                                            params, dst_w, dst_h, out, out_dtype);
-  else
+  } else {
     crop_resample_kernel<float><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
         src, frame_stride, view_stride, row_stride, params, dst_w, dst_h, out, out_dtype);
+  }
   return at::check_launch("crop_resample_kernel");
 }
 
@@ -520,4 +650,45 @@ extern "C" int at_resample_homography_f32(const float* images, int n, int H, int
   dim3 grid((unsigned)n, kSplit);
   resample_homography_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(images, H, W, xfs, oh, ow, out, out_divisor);
   return at::check_launch("resample_homography_kernel");
+}
+
+extern "C" int at_crop_pull_source_boxes_u8(const uint8_t* src, uint8_t* dst, int64_t n_frames, int64_t frame_stride,
+                                            int64_t view_stride, int64_t row_stride, const AtCropParams* params,
+                                            int n_crops, int dst_w, int dst_h, int max_ctas,
+                                            unsigned long long* pulled_bytes, void* stream) {
+  AT_REQUIRE(n_crops >= 0 && n_frames >= 0, "at_crop_pull_source_boxes_u8: negative count");
+  if (n_crops == 0 || n_frames == 0) return AT_OK;
+  AT_REQUIRE(src && dst && params, "at_crop_pull_source_boxes_u8: NULL pointer");
+  AT_REQUIRE(dst_w > 0 && dst_h > 0 && dst_w <= 4096 && dst_h <= 4096, "at_crop_pull_source_boxes_u8: bad crop size");
+  AT_REQUIRE((((uintptr_t)src | (uintptr_t)dst) & 15) == 0 && (frame_stride & 15) == 0 && frame_stride > 0,
+             "at_crop_pull_source_boxes_u8: source, destination and frame stride must be 16-byte aligned");
+  AT_REQUIRE(n_frames * frame_stride < (1ll << 32) - 16 && row_stride >= 0 && view_stride >= 0,
+             "at_crop_pull_source_boxes_u8: at most 4 GiB of frames per call, non-negative strides");
+  {
+    cudaPointerAttributes attr;
+    const bool ok = cudaPointerGetAttributes(&attr, src) == cudaSuccess &&
+                    (attr.type == cudaMemoryTypeHost || attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged);
+    if (!ok) cudaGetLastError();
+    AT_REQUIRE(ok, "at_crop_pull_source_boxes_u8: the source must be pinned host memory (or device memory)");
+  }
+  int grid = max_ctas > 0 ? max_ctas : at::kNumSMs;
+  if (grid > n_crops) grid = n_crops;
+  // Bytes in flight = grid x depth x 1 KB.  Measured on B200 (scripts/pull_time.py, bench.py): PCIe
+  // saturates (~36-39 GB/s on these short rows) from ~150 KB in flight; every SM-issued PCIe read
+  // also slows the co-running encoder a little (scripts/overlap_probe.cu), and more requests in
+  // flight only make that worse -> one warp per SM, 1 KB each.  AT_PULL_DEPTH (1, 2, 4, 8) to tune.
+  static const int depth = getenv("AT_PULL_DEPTH") ? atoi(getenv("AT_PULL_DEPTH")) : 1;
+#define AT_PULL_LAUNCH(D)                                                                                         \
+  do {                                                                                                            \
+    AT_CARVEOUT_ONCE(crop_pull_boxes_kernel<D>);                                                                  \
+    crop_pull_boxes_kernel<D><<<grid, 32, 0, (cudaStream_t)stream>>>(src, dst, n_frames * frame_stride,           \
+                                                                     frame_stride, view_stride, row_stride, params, \
+                                                                     n_crops, dst_w, dst_h, pulled_bytes);        \
+  } while (0)
+  if (depth == 1) AT_PULL_LAUNCH(1);
+  else if (depth == 2) AT_PULL_LAUNCH(2);
+  else if (depth == 8) AT_PULL_LAUNCH(8);
+  else AT_PULL_LAUNCH(4);
+#undef AT_PULL_LAUNCH
+  return at::check_launch("crop_pull_boxes_kernel");
 }

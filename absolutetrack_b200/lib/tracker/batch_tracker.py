@@ -14,6 +14,8 @@ Everything runs in libabsolutetrack_b200.so; there is no CPU path.
 from dataclasses import dataclass
 from typing import Optional
 
+import os
+
 import numpy as np
 import torch
 
@@ -21,7 +23,7 @@ from .. import _cabi
 from ..common.hand import HandModel
 from ..common.hand_skinning import skin_landmarks_cuda
 from ..models.umetrack_model import InputFrameData, InputFrameDesc, InputSkeletonData
-from .tracker import crop_resample_cuda
+from .tracker import crop_pull_source_boxes_cuda, crop_resample_cuda
 
 M_TO_MM = 1000.0
 
@@ -66,11 +68,15 @@ class BatchResult:
 
 class BatchedHandTracker:
     def __init__(self, model, hand_model_mm: HandModel, max_slots: int, map_mode: str = "fp32",
-                 crop_dtype: torch.dtype = torch.uint8, ingest: str = "zero_copy") -> None:
-        """ingest: how step() brings HOST frames to the GPU.  "zero_copy" (needs pinned frames and
-        map_mode "fp32"): the resampler reads the pinned frames in place and pulls only each crop's
-        source bounding box over PCIe (~30 KB per crop instead of the 305 KB view); "copy": the
-        whole frame tensor is copied on a side stream, overlapped with the previous step."""
+                 crop_dtype: torch.dtype = torch.uint8, ingest: str = "pull") -> None:
+        """ingest: how step() brings HOST frames to the GPU.
+        "pull" (needs pinned frames): a small side-stream kernel copies only each crop's source
+        bounding box (~37 KB per crop instead of the 305 KB view) from the pinned frames into a
+        device frame buffer of the same layout, overlapped with the previous step's kernels; the
+        resampler then runs on device memory, in any map mode.
+        "zero_copy" (pinned frames, map_mode "fp32"): the resampler itself reads the pinned frames
+        in place through shared memory - no side stream, the PCIe time is inside the step.
+        "copy": the whole frame tensor is copied on the side stream."""
         if not torch.cuda.is_available():
             raise _cabi.AbsoluteTrackError("BatchedHandTracker needs a CUDA device (no CPU fallback)")
         self._device = torch.device("cuda", torch.cuda.current_device())
@@ -90,14 +96,18 @@ class BatchedHandTracker:
         ])
         # host->device ingest: a copy stream and two device staging slots, so that the H2D copy of
         # step i+1 overlaps the kernels of step i (frames are 1.22 MB each: ingest is the e2e bound)
-        if ingest not in ("zero_copy", "copy"):
-            raise ValueError("ingest must be 'zero_copy' or 'copy'")
+        if ingest not in ("pull", "zero_copy", "copy"):
+            raise ValueError("ingest must be 'pull', 'zero_copy' or 'copy'")
         self._ingest = ingest
         self.pulled_bytes = torch.zeros(1, dtype=torch.int64, device=self._device)  # bytes the resampler pulled from host frames
-        self._copy_stream = torch.cuda.Stream(device=self._device)
+        self.pull_ctas = 0  # CTAs of the pull kernel (0 = one per SM)
+        self.trace = None   # debug: a list -> step() appends (ingest start, ingest end, compute start, compute end) events
+        # high priority: the ingest kernels are tiny and must not queue behind the encoder's CTAs
+        self._copy_stream = torch.cuda.Stream(device=self._device, priority=int(os.environ.get("AT_INGEST_PRIORITY", "-1")))
         self._stage = [None, None]
         self._stage_free = [None, None]
         self._slot = 0
+        self._crops_done = None
 
     @property
     def device(self):
@@ -110,6 +120,10 @@ class BatchedHandTracker:
             b.frames, H * V * W, W, V * W, b.crop_params, (96, 96), self._crop_dtype, self._map_mode,
             staged_bytes=None if b.frames.is_cuda else self.pulled_bytes,
         )
+        # the next step's ingest kernel is released after this point: the resampler runs with its own
+        # (L1-heavy) shared-memory configuration and must not meet resident ingest CTAs
+        self._crops_done = torch.cuda.Event()
+        self._crops_done.record()
         out = self._model.regress_pose_use_skeleton(
             InputFrameData(crops, b.intrinsics, b.extrinsics),
             InputFrameDesc(b.sample_range, b.memory_idx, b.use_memory, b.hand_idx),
@@ -130,9 +144,11 @@ class BatchedHandTracker:
         cur = torch.cuda.current_stream(self._device)
         cs = self._copy_stream
         st = self._stage[slot]
-        zero_copy = self._ingest == "zero_copy" and self._map_mode == "fp32" and host_batch.frames.is_pinned()
+        pinned = host_batch.frames.is_pinned()
+        zero_copy = self._ingest == "zero_copy" and self._map_mode == "fp32" and pinned
+        pull = self._ingest == "pull" and pinned
         fields = [f for f in host_batch.__dataclass_fields__ if not (zero_copy and f == "frames")]
-        if st is None or any(getattr(st, f).shape != getattr(host_batch, f).shape for f in fields):
+        if st is None or any(getattr(st, f) is None or getattr(st, f).shape != getattr(host_batch, f).shape for f in fields):
             st = FrameBatch(*[
                 (torch.empty_like(getattr(host_batch, f), device=self._device) if f in fields else None)
                 for f in host_batch.__dataclass_fields__])
@@ -145,15 +161,26 @@ class BatchedHandTracker:
             st.frames = host_batch.frames  # read in place by the resampler; the caller keeps it alive and unchanged
         if self._stage_free[slot] is not None:
             cs.wait_event(self._stage_free[slot])  # the kernels that last read this slot are done
+        if self._crops_done is not None:
+            cs.wait_event(self._crops_done)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)] if self.trace is not None else None
         with torch.cuda.stream(cs):
+            if ev: ev[0].record(cs)
             for f in fields:
-                getattr(st, f).copy_(getattr(host_batch, f), non_blocking=True)
-            ready = torch.cuda.Event()
+                if not (pull and f == "frames"):
+                    getattr(st, f).copy_(getattr(host_batch, f), non_blocking=True)
+            if pull:
+                S, H, V, W = host_batch.frames.shape
+                crop_pull_source_boxes_cuda(host_batch.frames, st.frames, H * V * W, W, V * W, st.crop_params,
+                                            (96, 96), self.pull_ctas, self.pulled_bytes)
+            ready = ev[1] if ev else torch.cuda.Event()
             ready.record(cs)
         cur.wait_event(ready)
+        if ev: ev[2].record(cur)
         r = self.step_device(st)
-        free = torch.cuda.Event()
+        free = ev[3] if ev else torch.cuda.Event()
         free.record(cur)
+        if ev: self.trace.append(ev)
         self._stage_free[slot] = free
         if out_host is None:
             out_host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True) for k, v in vars(r).items()}

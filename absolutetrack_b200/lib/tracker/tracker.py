@@ -106,6 +106,36 @@ def crop_resample_cuda(
     return out
 
 
+def crop_pull_source_boxes_cuda(
+    src: torch.Tensor,
+    dst: torch.Tensor,
+    frame_stride: int,
+    view_stride: int,
+    row_stride: int,
+    params: torch.Tensor,
+    dst_wh=(96, 96),
+    max_ctas: int = 0,
+    pulled_bytes: Optional[torch.Tensor] = None,
+) -> None:
+    """Launch at_crop_pull_source_boxes_u8 on the current stream: copy, for every crop in `params`,
+    the source box its map touches from the PINNED host frames `src` into the device buffer `dst`
+    of the same shape (bytes outside the boxes are left as they are and never read by the
+    resampler)."""
+    lib = _cabi.lib()
+    assert src.dtype == torch.uint8 and dst.dtype == torch.uint8 and dst.is_cuda and params.is_cuda
+    if src.shape != dst.shape or not src.is_contiguous() or not dst.is_contiguous():
+        raise _cabi.AbsoluteTrackError("pull source and destination must be contiguous and of one shape")
+    if not (src.is_cuda or src.is_pinned()):
+        raise _cabi.AbsoluteTrackError("the pull source must be pinned host memory (pageable memory is not GPU-readable)")
+    with torch.cuda.device(dst.device):
+        rc = lib.at_crop_pull_source_boxes_u8(
+            src.data_ptr(), dst.data_ptr(), src.numel() // frame_stride, frame_stride, view_stride, row_stride,
+            params.contiguous().data_ptr(), params.shape[0], int(dst_wh[0]), int(dst_wh[1]), int(max_ctas),
+            _cabi.ptr(pulled_bytes), _cabi.stream_ptr(dst.device),
+        )
+    _cabi.check(rc, "at_crop_pull_source_boxes_u8")
+
+
 def _warp_image(
     src_camera: camera.CameraModel,
     dst_camera: camera.CameraModel,

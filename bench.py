@@ -185,7 +185,8 @@ def main():
                     help="encoder operand format; fp16 and bf16 run the same tcgen05 kind::f16 kernels with fp32 accumulation "
                          "(fp16 meets the 0.1 mm end-to-end tolerance, bf16 does not: DESIGN.md)")
     ap.add_argument("--map-mode", default="fp32", choices=["fp32", "fp64"])
-    ap.add_argument("--ingest", default="zero_copy", choices=["zero_copy", "copy"], help="e2e arm: how host frames reach the GPU")
+    ap.add_argument("--ingest", default="pull", choices=["pull", "zero_copy", "copy"], help="e2e arm: how host frames reach the GPU")
+    ap.add_argument("--pull-ctas", type=int, default=0, help="CTAs of the source-box pull kernel (0 = 2 per SM)")
     ap.add_argument("--ref-frames", type=int, default=24, help="frames per step of the CPU reference arm")
     ap.add_argument("--cpu-frames", type=int, default=96, help="bounded CPU-baseline sample (frames)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -221,6 +222,7 @@ def main():
     model = model_from_state_dict(make_random_state_dict(0), precision=args.precision)
     hm = synthetic.hand_model()
     tracker = BatchedHandTracker(model, hm, max_slots=2 * S, map_mode=args.map_mode, ingest=args.ingest)
+    tracker.pull_ctas = args.pull_ctas
 
     # sequences are sharded by rank (r::world, the reference Sampler's rule, async_dataset.py:558-559)
     seq_ids = np.arange(S) * world + rank
@@ -289,10 +291,15 @@ def main():
     # ---- end to end from pinned host buffers
     out_host = [None]
 
+    issue = [0.0]
+
     def step_host(i):
+        t0 = time.perf_counter()
         out_host[0] = tracker.step(host[i % NB], out_host[0])
+        issue[0] += time.perf_counter() - t0
 
     ms_e2e, _ = timed(step_host, args.steps, args.warmup)
+    issue_ms = issue[0] / (args.steps + args.warmup) * 1e3  # host time to enqueue one step (must stay below the GPU time)
     e2e_value = world * n / (ms_e2e / args.steps * 1e-3)
     small = host[0].nbytes() - host[0].frames.numel()
     pulled0 = int(tracker.pulled_bytes.item())
@@ -300,7 +307,9 @@ def main():
         step_host(i)
     torch.cuda.synchronize()
     pulled = (int(tracker.pulled_bytes.item()) - pulled0) // 2   # bytes the resampler pulled from the pinned frames per step
-    ingest = "zero_copy (source boxes pulled from pinned frames by the resampler)" if pulled > 0 else "copy (whole frames, side stream)"
+    ingest = {"pull": "pull (side-stream kernel copies each crop's source box from the pinned frames, overlapped with the previous step)",
+              "zero_copy": "zero_copy (source boxes read from pinned frames by the resampler itself)",
+              "copy": "copy (whole frames, side stream)"}[args.ingest]
     h2d = small + (pulled if pulled > 0 else host[0].frames.numel())
     d2h = sum(v.numel() * v.element_size() for v in out_host[0].values())
 
@@ -363,7 +372,7 @@ def main():
                        "crops_per_step_per_gpu": c, "map_mode": args.map_mode, "l2": flush_note,
                        "weights": "seeded random state dict (252 keys), BN folded", "sharding": "sequences r::world"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "api": "BatchedHandTracker.step (pinned host buffers)", "ingest": ingest,
+                    "api": "BatchedHandTracker.step (pinned host buffers)", "ingest": ingest, "host_issue_ms_per_step": issue_ms,
                     "host_frame_bytes_per_step": int(host[0].frames.numel())},
             "gpu_launches": int(launches),
             "roofline": {"bound": "tensor", "kernel": "per-view encoder (all conv launches of at_encoder_forward)",

@@ -88,6 +88,19 @@ int at_crop_resample_fisheye62_u8_ex(const uint8_t* src, int64_t frame_stride, i
                                      int64_t row_stride, const AtCropParams* params, int n_crops,
                                      int dst_w, int dst_h, void* out, int out_dtype, int map_mode,
                                      unsigned long long* staged_bytes, void* stream);
+/* Host->device ingest without copying whole frames (the PCIe side of tracker._warp_image's source
+ * read, lib/tracker/tracker.py:61-89, for frames that live in pinned host memory).  For every crop
+ * the source region its map touches is bounded from the crop's boundary pixels (fp32 map) and
+ * copied from `src` into `dst`, a DEVICE buffer of the same layout ([n_frames] x frame_stride
+ * bytes); at_crop_resample_fisheye62_u8 then runs on `dst` and never reads outside the boxes.
+ * src, dst and frame_stride must be 16-byte aligned, n_frames * frame_stride < 4 GiB.  The launch
+ * is small on purpose (max_ctas one-warp CTAs, 0 = one per SM; 32 registers, <= 4 KB shared memory)
+ * so that it stays co-resident with the encoder kernels of the previous step on a side stream.
+ * *pulled_bytes (device, may be NULL) is incremented by the bytes read from `src`. */
+int at_crop_pull_source_boxes_u8(const uint8_t* src, uint8_t* dst, int64_t n_frames, int64_t frame_stride,
+                                 int64_t view_stride, int64_t row_stride, const AtCropParams* params,
+                                 int n_crops, int dst_w, int dst_h, int max_ctas,
+                                 unsigned long long* pulled_bytes, void* stream);
 
 /* The torch_data pinhole->pinhole resampler.  Replaces data_transform._resample_images_batched
  * (lib/batched_dataset/data_transform.py:78-144): (u,v,1) -> xf[0:3,0:3]*(u,v,1)+xf[0:3,3],

@@ -8,7 +8,7 @@ from absolutetrack_b200 import _cabi
 from absolutetrack_b200.lib.models.model_loader import make_random_state_dict, model_from_state_dict
 c = int(sys.argv[1]) if len(sys.argv) > 1 else 2048
 lib = _cabi.lib()
-model = model_from_state_dict(make_random_state_dict(0), precision="bf16").cuda()
+model = model_from_state_dict(make_random_state_dict(0), precision=(sys.argv[2] if len(sys.argv) > 2 else "fp16")).cuda()
 crops = (torch.rand(c, 96, 96) * 255).to(torch.uint8).cuda()
 for _ in range(20): model.encode(crops)
 torch.cuda.synchronize()

@@ -233,6 +233,22 @@ def test_crop_staged_path_equals_direct_gather_and_zero_copy(cuda_lib, gold):
     with pytest.raises(Exception):
         crop_resample_cuda(torch.from_numpy(frames), *args)          # pageable host memory is refused
 
+    # source-box pull: only the boxes are copied into a poisoned device buffer of the same layout;
+    # the ordinary resampler on that buffer must still give the same crops, in both map modes
+    from absolutetrack_b200.lib.tracker.tracker import crop_pull_source_boxes_cuda
+    for ctas in (0, 3):
+        pulled = torch.full_like(dev, 0xA5)
+        counter.zero_()
+        crop_pull_source_boxes_cuda(host, pulled, 480 * 2544, 636, 2544, params, (96, 96), ctas, counter)
+        assert torch.equal(crop_resample_cuda(pulled, *args), direct)
+        args64 = args[:-1] + ("fp64",)
+        assert torch.equal(crop_resample_cuda(pulled, *args64), crop_resample_cuda(dev, *args64))
+        per_crop = counter.item() / len(recs)
+        assert 8_000 < per_crop < 120_000, per_crop                 # two of the 24 crops pull a whole 305 KB view
+        assert (pulled != dev).float().mean() > 0.5                 # most of the frame was never copied
+    with pytest.raises(Exception):
+        crop_pull_source_boxes_cuda(torch.from_numpy(frames), pulled, 480 * 2544, 636, 2544, params)
+
 
 # ------------------------------------------------------------------ homography resampler (a12)
 def test_homography_resampler_matches_oracle(cuda_lib):

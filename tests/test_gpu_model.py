@@ -202,3 +202,64 @@ def test_gen_crop_cameras_matches_reference_golden(model, gold):
                 assert np.allclose(got.f, G["crop_f"][k, h, s], rtol=1e-5)
                 assert np.allclose(got.c, G["crop_c"][k, h, s])
                 assert np.allclose(got.camera_to_world_xf, G["crop_c2w"][k, h, s], atol=1e-4)
+
+
+def test_batched_tracker_ingest_modes_agree_and_match_oracle(cuda_lib, state_dict):
+    """BatchedHandTracker (the throughput entry bench.py times): S sequences in lock-step over 3
+    time steps.  (1) Host ingest by source-box pull, by zero-copy staging and by whole-frame copy
+    all give bit-identical results to device-resident frames; (2) with the bit-exact fp64 crop map
+    the poses/landmarks equal the CPU oracle run on the same crops with the same memory slots."""
+    from absolutetrack_b200 import synthetic
+    from absolutetrack_b200.lib.models.model_loader import model_from_state_dict
+    from absolutetrack_b200.lib.tracker.batch_tracker import BatchedHandTracker
+    from absolutetrack_b200.lib.tracker.tracker import crop_resample_cuda
+
+    S, T = 3, 3
+    seq = np.array([0, 7, 31])
+    hm = synthetic.hand_model()
+    g = torch.Generator().manual_seed(5)
+    batches = []
+    for t in range(T):
+        fr = torch.randint(0, 256, (S, synthetic.H, synthetic.V, synthetic.W), dtype=torch.uint8, generator=g)
+        batches.append(synthetic.make_batch(seq, t, frames=fr, first_step=(t == 0)).pin())
+
+    def run(ingest, map_mode):
+        tr = BatchedHandTracker(model_from_state_dict(state_dict).cuda(), hm, max_slots=2 * S, map_mode=map_mode,
+                                ingest=ingest if ingest != "device" else "pull")
+        outs = []
+        for hb in batches:
+            if ingest == "device":
+                r = tr.step_device(hb.to("cuda"))
+                o = {k: v.cpu() for k, v in vars(r).items()}
+            else:
+                o = tr.step(hb)
+            torch.cuda.synchronize()
+            outs.append({k: v.clone() for k, v in o.items()})
+        tr.check()
+        return outs, tr
+
+    base, _ = run("device", "fp32")
+    for ingest in ("pull", "zero_copy", "copy"):
+        outs, tr = run(ingest, "fp32")
+        for a, b in zip(outs, base):
+            for k in a:
+                assert torch.equal(a[k], b[k]), (ingest, k)
+        if ingest != "copy":
+            assert 0 < tr.pulled_bytes.item() < T * batches[0].frames.numel() / 4   # boxes, not frames
+
+    # oracle: same crops (fp64 map is bit-exact vs the reference warp), batched samples, slot = seq*2+hand
+    outs, _ = run("pull", "fp64")
+    hmn = scenario.hand_model()
+    st = MO.TemporalState()
+    for t, hb in enumerate(batches):
+        crops = crop_resample_cuda(hb.frames.cuda(), synthetic.H * synthetic.V * synthetic.W, synthetic.W,
+                                   synthetic.V * synthetic.W, hb.crop_params.cuda(), (96, 96), torch.float32, "fp64").cpu()
+        ref = MO.forward(state_dict, st, crops, hb.intrinsics, hb.extrinsics, hb.sample_range, hb.memory_idx,
+                         hb.use_memory, hb.hand_idx, _skel())
+        o = outs[t]
+        assert np.abs(o["joint_angles"].numpy() - ref["joint_angles"].numpy()).max() < TOL_ANGLE_RAD
+        for i in range(o["landmarks"].shape[0]):
+            w = ref["wrist_xfs"][i].numpy().copy()
+            w[:3, 3] *= 1000.0
+            lm_ref = O.landmarks_from_hand_pose(hmn, ref["joint_angles"][i].numpy(), w, int(hb.hand_idx[i]))[0]
+            assert np.abs(o["landmarks"][i].numpy() - lm_ref).max() < 0.05   # mm

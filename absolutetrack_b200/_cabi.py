@@ -124,6 +124,12 @@ SIGNATURES = {
         _I,
         [_VP, C.POINTER(AtTailInputs), C.POINTER(AtTemporalState), C.POINTER(AtTailOutputs), _VP, _I64, _VP],
     ),
+    "at_tail_f16_blob_bytes": (_I64, []),
+    "at_tail_prepack_f16": (_I, [_VP, _VP, _VP]),
+    "at_tail_forward_f16": (
+        _I,
+        [_VP, _VP, C.POINTER(AtTailInputs), C.POINTER(AtTemporalState), C.POINTER(AtTailOutputs), _VP, _I64, _VP],
+    ),
 }
 
 _lib = None

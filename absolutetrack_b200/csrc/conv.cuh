@@ -38,6 +38,13 @@ int conv_nhwc_f32(const ConvLayer& L, const float* blob, const float* in, int in
 int conv_nhwc_tf32x3(const ConvLayer& L, const float* blob, const float* in, int in_ld, int in_coff, const float* res,
                      int res_ld, float* out, int out_ld, int out_coff, int N, int H, int W, bool relu,
                      cudaStream_t stream);
+// fp16 x 3 (error-compensated, fp32-grade) variant: weights pre-split by conv_f16x3_split_weights into
+// conv_f16x3_weight_halves(L) halves at `wsplit`.
+int64_t conv_f16x3_weight_halves(const ConvLayer& L);
+int conv_f16x3_split_weights(const ConvLayer& L, const float* blob, void* wsplit, cudaStream_t stream);
+int conv_nhwc_f16x3(const ConvLayer& L, const float* blob, const void* wsplit, const float* in, int in_ld, int in_coff,
+                    const float* res, int res_ld, float* out, int out_ld, int out_coff, int N, int H, int W, bool relu,
+                    cudaStream_t stream);
 int stem_f32(const ConvLayer& L, const float* blob, const void* crops, int crop_dtype, float* out, int c,
              cudaStream_t stream);
 

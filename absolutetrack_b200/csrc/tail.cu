@@ -6,6 +6,8 @@
 // umetrack_model.py:77-97,123-242.  Features are NHWC: [sample, 36 pixels, channels].
 // The small 4x4 / 3x3 matrix algebra runs in double on one thread per hand (the reference uses
 // fp32 torch.inverse / svd; the differences are ~1e-7 relative); feature math is fp32.
+#include <stdlib.h>
+
 #include "conv.cuh"
 
 namespace at {
@@ -400,10 +402,45 @@ extern "C" int64_t at_tail_workspace_bytes(int n) {
   return (int64_t)sizeof(float) * at::kWsPerSample * (int64_t)n + 256;
 }
 
+namespace at {
+namespace {
+// byte offset of layer `id`'s pre-split fp16 weights inside the tail operand blob (layers L_FUSION.. in order)
+int64_t f16_blob_offset(int id) {
+  const ConvLayer* T = layer_table();
+  int64_t off = 0;
+  for (int i = L_FUSION; i < id; ++i)
+    if (i != L_SKEL) off += round_up(conv_f16x3_weight_halves(T[i]) * 2, 256);
+  return off;
+}
+}  // namespace
+}  // namespace at
+
+extern "C" int64_t at_tail_f16_blob_bytes(void) { return at::f16_blob_offset(at::L_COUNT); }
+
+extern "C" int at_tail_prepack_f16(const float* blob, void* f16_blob, void* stream) {
+  using namespace at;
+  AT_REQUIRE(blob && f16_blob, "at_tail_prepack_f16: NULL argument");
+  AT_REQUIRE((((uintptr_t)f16_blob) & 15) == 0, "at_tail_prepack_f16: the operand blob must be 16-byte aligned");
+  const ConvLayer* T = layer_table();
+  for (int i = L_FUSION; i < L_COUNT; ++i) {
+    if (i == L_SKEL) continue;
+    int rc = conv_f16x3_split_weights(T[i], blob, (uint8_t*)f16_blob + f16_blob_offset(i), (cudaStream_t)stream);
+    if (rc) return rc;
+  }
+  return AT_OK;
+}
+
 extern "C" int at_tail_forward(const float* blob, const AtTailInputs* in, AtTemporalState* state,
                                const AtTailOutputs* out, void* workspace, int64_t workspace_bytes, void* stream_) {
+  return at_tail_forward_f16(blob, nullptr, in, state, out, workspace, workspace_bytes, stream_);
+}
+
+extern "C" int at_tail_forward_f16(const float* blob, const void* f16_blob, const AtTailInputs* in,
+                                   AtTemporalState* state, const AtTailOutputs* out, void* workspace,
+                                   int64_t workspace_bytes, void* stream_) {
   using namespace at;
   AT_REQUIRE(blob && in && state && out, "at_tail_forward: NULL argument");
+  AT_REQUIRE((((uintptr_t)f16_blob) & 15) == 0, "at_tail_forward: the fp16 operand blob must be 16-byte aligned");
   const int n = in->n, c = in->c;
   AT_REQUIRE(n >= 0 && c >= 0, "at_tail_forward: negative size");
   if (n == 0) return AT_OK;
@@ -443,6 +480,17 @@ extern "C" int at_tail_forward(const float* blob, const AtTailInputs* in, AtTemp
   float* ho = w;       w += kWsHo * n;
   float* skel = w;
 
+  // every conv of the tail: error-compensated fp16 x 3 tensor-core GEMM when the pre-split operand
+  // blob is given, else the TF32 x 3 kernel on the fp32 blob (both fp32-grade; see conv_f32.cu)
+  static const bool force_tf32 = getenv("AT_TAIL_TF32") != nullptr && atoi(getenv("AT_TAIL_TF32")) != 0;
+  const bool use_f16 = f16_blob != nullptr && !force_tf32;
+  auto conv = [&](int id, const float* x, int x_ld, const float* res, int res_ld, float* y, int y_ld, bool relu) -> int {
+    if (use_f16)
+      return conv_nhwc_f16x3(T[id], blob, (const uint8_t*)f16_blob + f16_blob_offset(id), x, x_ld, 0, res, res_ld, y, y_ld,
+                             0, n, 6, 6, relu, s);
+    return conv_nhwc_tf32x3(T[id], blob, x, x_ld, 0, res, res_ld, y, y_ld, 0, n, 6, 6, relu, s);
+  };
+
   PrepArgs pa;
   pa.in = *in; pa.st = *state; pa.fuse_in = fuse_in; pa.temp_in = temp_in; pa.status = out->status;
   tail_prepare_kernel<<<n, 128, 0, s>>>(pa);
@@ -450,18 +498,18 @@ extern "C" int at_tail_forward(const float* blob, const AtTailInputs* in, AtTemp
   if (rc) return rc;
   // 2-view fusion (model_utils.py:141-163).  Rows of single-view samples are computed on
   // whatever the workspace holds and ignored afterwards.
-  if ((rc = conv_nhwc_tf32x3(T[L_FUSION + 0], blob, fuse_in, 144, 0, nullptr, 0, f1, 108, 0, n, 6, 6, true, s))) return rc;
-  if ((rc = conv_nhwc_tf32x3(T[L_FUSION + 1], blob, f1, 108, 0, nullptr, 0, f2, 72, 0, n, 6, 6, true, s))) return rc;
-  if ((rc = conv_nhwc_tf32x3(T[L_FUSION + 2], blob, f2, 72, 0, nullptr, 0, f3, 72, 0, n, 6, 6, false, s))) return rc;
+  if ((rc = conv(L_FUSION + 0, fuse_in, 144, nullptr, 0, f1, 108, true))) return rc;
+  if ((rc = conv(L_FUSION + 1, f1, 108, nullptr, 0, f2, 72, true))) return rc;
+  if ((rc = conv(L_FUSION + 2, f2, 72, nullptr, 0, f3, 72, false))) return rc;
   {
     const int64_t tot = (int64_t)n * kPix * kFeat;
     post_fusion_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(f3, in->intrinsics, in->sample_range, n, c, temp_in);
     if ((rc = check_launch("post_fusion_kernel"))) return rc;
   }
   // SimpleConvRNN step (temporal.py:76-91): 3x conv1x1(90->90), ReLU after the first two
-  if ((rc = conv_nhwc_tf32x3(T[L_TEMPORAL + 0], blob, temp_in, 90, 0, nullptr, 0, t1, 90, 0, n, 6, 6, true, s))) return rc;
-  if ((rc = conv_nhwc_tf32x3(T[L_TEMPORAL + 1], blob, t1, 90, 0, nullptr, 0, t2, 90, 0, n, 6, 6, true, s))) return rc;
-  if ((rc = conv_nhwc_tf32x3(T[L_TEMPORAL + 2], blob, t2, 90, 0, nullptr, 0, t3, 90, 0, n, 6, 6, false, s))) return rc;
+  if ((rc = conv(L_TEMPORAL + 0, temp_in, 90, nullptr, 0, t1, 90, true))) return rc;
+  if ((rc = conv(L_TEMPORAL + 1, t1, 90, nullptr, 0, t2, 90, true))) return rc;
+  if ((rc = conv(L_TEMPORAL + 2, t2, 90, nullptr, 0, t3, 90, false))) return rc;
   const int hc = known ? 76 : 72;
   if (known) {
     const ConvLayer& L = T[L_SKEL];
@@ -477,11 +525,11 @@ extern "C" int at_tail_forward(const float* blob, const AtTailInputs* in, AtTemp
   }
   // pose head (model_utils.py:195-208): 2 BasicBlocks + conv1x1 + global average pool
   const int hb = known ? L_HEAD_K : L_HEAD_U;
-  if ((rc = conv_nhwc_tf32x3(T[hb + 0], blob, head_in, hc, 0, nullptr, 0, h1, hc, 0, n, 6, 6, true, s))) return rc;
-  if ((rc = conv_nhwc_tf32x3(T[hb + 1], blob, h1, hc, 0, head_in, hc, h2, hc, 0, n, 6, 6, true, s))) return rc;
-  if ((rc = conv_nhwc_tf32x3(T[hb + 2], blob, h2, hc, 0, nullptr, 0, h1, hc, 0, n, 6, 6, true, s))) return rc;
-  if ((rc = conv_nhwc_tf32x3(T[hb + 3], blob, h1, hc, 0, h2, hc, head_in, hc, 0, n, 6, 6, true, s))) return rc;
-  if ((rc = conv_nhwc_tf32x3(T[hb + 4], blob, head_in, hc, 0, nullptr, 0, ho, 64, 0, n, 6, 6, false, s))) return rc;
+  if ((rc = conv(hb + 0, head_in, hc, nullptr, 0, h1, hc, true))) return rc;
+  if ((rc = conv(hb + 1, h1, hc, head_in, hc, h2, hc, true))) return rc;
+  if ((rc = conv(hb + 2, h2, hc, nullptr, 0, h1, hc, true))) return rc;
+  if ((rc = conv(hb + 3, h1, hc, h2, hc, head_in, hc, true))) return rc;
+  if ((rc = conv(hb + 4, head_in, hc, nullptr, 0, ho, 64, false))) return rc;
   DecodeArgs da;
   da.head_out = ho; da.ld = 64; da.n_out = known ? 62 : 63;
   da.extrinsics = in->extrinsics; da.sample_range = in->sample_range; da.hand_idx = in->hand_idx;

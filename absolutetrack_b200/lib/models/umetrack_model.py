@@ -72,6 +72,8 @@ class UmeTrackModel(nn.Module):
         self.precision = precision
         self._bf16_blob: Optional[torch.Tensor] = None
         self._bf16_prec = -1
+        self.tail_mode = "f16x3"  # or "tf32x3": which fp32-grade tensor-core kernel the tail convs use
+        self._tail_f16_blob: Optional[torch.Tensor] = None
         # recurrent state (plain attributes, like the reference: not buffers, not moved by .to())
         self._mem_features = torch.empty(0)      # [cap, 6, 6, 18]  (NHWC)
         self._prev_extrinsics = torch.empty(0)   # [cap, 4, 4]
@@ -138,6 +140,21 @@ class UmeTrackModel(nn.Module):
                 )
             self._bf16_blob, self._bf16_prec = buf, prec
         return self._bf16_blob
+
+    def _tail_f16_weights(self, device):
+        """Pre-split fp16 hi/lo operand blob of the tail convolutions (at_tail_prepack_f16)."""
+        if self.tail_mode == "tf32x3":
+            return None
+        if self.tail_mode != "f16x3":
+            raise ValueError("tail_mode must be 'f16x3' or 'tf32x3'")
+        if self._tail_f16_blob is None or self._tail_f16_blob.device != device:
+            lib = _cabi.lib()
+            buf = torch.zeros(lib.at_tail_f16_blob_bytes(), dtype=torch.uint8, device=device)
+            with torch.cuda.device(device):
+                _cabi.check(lib.at_tail_prepack_f16(self._blob.data_ptr(), buf.data_ptr(), _cabi.stream_ptr(device)),
+                            "at_tail_prepack_f16")
+            self._tail_f16_blob = buf
+        return self._tail_f16_blob
 
     def encode(self, crops: torch.Tensor) -> torch.Tensor:
         """Per-view encoder: crops [c,96,96] (uint8 grey levels or float32 in [0,1]) on the GPU ->
@@ -220,9 +237,10 @@ class UmeTrackModel(nn.Module):
             self._status.data_ptr(),
         )
         ws = self._ws_tail.get(lib.at_tail_workspace_bytes(n), dev)
+        f16 = self._tail_f16_weights(dev)
         with torch.cuda.device(dev):
-            rc = lib.at_tail_forward(
-                self._blob.data_ptr(), tin, st, tout, ws.data_ptr(), ws.numel(), _cabi.stream_ptr(dev)
+            rc = lib.at_tail_forward_f16(
+                self._blob.data_ptr(), _cabi.ptr(f16), tin, st, tout, ws.data_ptr(), ws.numel(), _cabi.stream_ptr(dev)
             )
         _cabi.check(rc, "at_tail_forward")
         if self.strict:

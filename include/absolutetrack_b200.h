@@ -230,6 +230,17 @@ int64_t at_tail_workspace_bytes(int n);
 int at_tail_forward(const float* blob, const AtTailInputs* in, AtTemporalState* state,
                     const AtTailOutputs* out, void* workspace, int64_t workspace_bytes,
                     void* stream);
+/* Same arithmetic contract (fp32-grade: every product carries 22 significant bits), twice the
+ * tensor throughput: the 11 convolutions of the tail run as error-compensated fp16 x 3 GEMMs
+ * (x = hi + lo in fp16; hi*hi + lo*hi + hi*lo accumulated in fp32, mma.m16n8k16) instead of
+ * TF32 x 3.  f16_blob = at_tail_f16_blob_bytes() bytes filled once per weight blob by
+ * at_tail_prepack_f16 (pre-split, pre-transposed weights); NULL selects the TF32 x 3 kernels,
+ * i.e. at_tail_forward. */
+int64_t at_tail_f16_blob_bytes(void);
+int at_tail_prepack_f16(const float* blob, void* f16_blob, void* stream);
+int at_tail_forward_f16(const float* blob, const void* f16_blob, const AtTailInputs* in,
+                        AtTemporalState* state, const AtTailOutputs* out, void* workspace,
+                        int64_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

@@ -59,11 +59,14 @@ def test_encoder_features_match_reference(model, gold, state_dict):
 
 
 @pytest.mark.parametrize("head", ["k", "u"])
-def test_model_sequence_matches_reference_golden(model, gold, head):
+@pytest.mark.parametrize("tail_mode", ["f16x3", "tf32x3"])
+def test_model_sequence_matches_reference_golden(model, gold, head, tail_mode):
     """4-frame known-skeleton sequence (frame 2 has a single-view sample, temporal memory carried
-    across frames) and 3-frame scale-head sequence vs the reference's outputs."""
+    across frames) and 3-frame scale-head sequence vs the reference's outputs - with both
+    fp32-grade tensor-core kernels of the tail (error-compensated fp16 x 3, the default, and TF32 x 3)."""
     from absolutetrack_b200.lib.models.umetrack_model import InputSkeletonData
 
+    model.tail_mode = tail_mode
     M = gold["model"]
     n_frames, start, sv = (int(v) for v in M[f"{head}_case"])
     seq = scenario.model_sequence(n_frames=n_frames, start=start, single_view_frame=None if sv < 0 else sv)

@@ -94,6 +94,70 @@ class AtTailOutputs(C.Structure):
     ]
 
 
+class AtRigCamera(C.Structure):
+    _fields_ = [
+        ("f", C.c_double * 2),
+        ("c", C.c_double * 2),
+        ("k", C.c_double * 8),
+        ("angle_deg", C.c_double),
+        ("width", C.c_int32),
+        ("height", C.c_int32),
+    ]
+
+
+RIG_CAMERA_BYTES = 112
+assert C.sizeof(AtRigCamera) == RIG_CAMERA_BYTES
+
+
+class AtCropCameraOpts(C.Structure):
+    _fields_ = [
+        ("num_crop_points", C.c_int32),
+        ("min_required_vis_landmarks", C.c_int32),
+        ("max_view_num", C.c_int32),
+        ("min_num_crops", C.c_int32),
+        ("sort_camera_index", C.c_int32),
+        ("mirror_right_hand", C.c_int32),
+        ("crop_w", C.c_int32),
+        ("crop_h", C.c_int32),
+        ("focal_multiplier", C.c_double),
+        ("min_focal", C.c_double),
+    ]
+
+
+class AtCropCameraInputs(C.Structure):
+    _fields_ = [
+        ("joint_angles", C.c_void_p),
+        ("wrist_xforms", C.c_void_p),
+        ("pose_frame", C.c_void_p),
+        ("pose_hand", C.c_void_p),
+        ("pose_valid", C.c_void_p),
+        ("neutral_joint_angles", C.c_void_p),
+        ("camera_to_world", C.c_void_p),
+        ("cameras", C.c_void_p),
+        ("n_poses", C.c_int32),
+        ("n_frames", C.c_int32),
+        ("n_cams", C.c_int32),
+        ("reserved", C.c_int32),
+    ]
+
+
+class AtCropCameraOutputs(C.Structure):
+    _fields_ = [
+        ("crop_params", C.c_void_p),
+        ("intrinsics", C.c_void_p),
+        ("extrinsics", C.c_void_p),
+        ("crop_camera_to_world", C.c_void_p),
+        ("crop_camera_index", C.c_void_p),
+        ("sample_range", C.c_void_p),
+        ("hand_idx", C.c_void_p),
+        ("memory_idx", C.c_void_p),
+        ("use_memory", C.c_void_p),
+        ("pose_index", C.c_void_p),
+        ("tracking_history", C.c_void_p),
+        ("counts", C.c_void_p),
+    ]
+
+
 # every symbol include/absolutetrack_b200.h declares: name -> (restype, argtypes)
 _VP, _I, _I64, _F = C.c_void_p, C.c_int, C.c_int64, C.c_float
 SIGNATURES = {
@@ -106,6 +170,12 @@ SIGNATURES = {
     "at_crop_pull_source_boxes_u8": (_I, [_VP, _VP, _I64, _I64, _I64, _I64, _VP, _I, _I, _I, _I, _VP, _VP]),
     "at_resample_homography_f32": (_I, [_VP, _I, _I, _I, _VP, _I, _I, _VP, _F, _VP]),
     "at_fk_skin_f32": (_I, [_VP, _VP, _VP, C.POINTER(AtHandModel), _I64, _VP, _VP]),
+    "at_crop_cameras_workspace_bytes": (_I64, [_I, _I]),
+    "at_gen_crop_cameras": (
+        _I,
+        [C.POINTER(AtCropCameraInputs), C.POINTER(AtHandModel), C.POINTER(AtCropCameraOpts),
+         C.POINTER(AtCropCameraOutputs), _VP, _I64, _VP],
+    ),
     "at_model_layer_table": (_I, [C.POINTER(AtLayerInfo), _I]),
     "at_model_blob_floats": (_I64, []),
     "at_model_bf16_blob_bytes": (_I64, []),

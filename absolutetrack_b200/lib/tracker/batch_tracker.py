@@ -23,6 +23,7 @@ from .. import _cabi
 from ..common.hand import HandModel
 from ..common.hand_skinning import skin_landmarks_cuda
 from ..models.umetrack_model import InputFrameData, InputFrameDesc, InputSkeletonData
+from .crop_cameras import CropCameraOpts, DeviceRig, alloc_crop_inputs, gen_crop_inputs_cuda
 from .tracker import crop_pull_source_boxes_cuda, crop_resample_cuda
 
 M_TO_MM = 1000.0
@@ -60,10 +61,38 @@ class FrameBatch:
 
 
 @dataclass
+class PoseBatch:
+    """One time step of S sequences BEFORE crop-camera generation: what a recording provides per
+    frame (video_pose_data.py:98-150: images, camera_to_world_transforms, and the pose the crop
+    is centred on - the labelled pose in the eval scripts, run_eval_known_skeleton.py:74-82).
+
+    frames          uint8 [S,H,V,W]   (pinned host memory for step_poses)
+    joint_angles    f32 [P,22], wrist_xforms f32 [P,4,4] (mm; right hands NOT mirrored)
+    pose_frame      i32 [P] sequence slot, pose_hand i32 [P], pose_valid uint8 [P] (confidence >= 0.5)
+    camera_to_world f64 [S,V,4,4]
+    """
+
+    frames: torch.Tensor
+    joint_angles: torch.Tensor
+    wrist_xforms: torch.Tensor
+    pose_frame: torch.Tensor
+    pose_hand: torch.Tensor
+    pose_valid: torch.Tensor
+    camera_to_world: torch.Tensor
+
+    def pin(self) -> "PoseBatch":
+        return PoseBatch(*[getattr(self, f).pin_memory() for f in self.__dataclass_fields__])
+
+    def small_nbytes(self) -> int:
+        return sum(getattr(self, f).numel() * getattr(self, f).element_size() for f in self.__dataclass_fields__ if f != "frames")
+
+
+@dataclass
 class BatchResult:
     joint_angles: torch.Tensor   # [n,22]
     wrist_xforms: torch.Tensor   # [n,4,4] wrist->world, millimetres, right hands mirrored
     landmarks: torch.Tensor      # [n,21,3] world, millimetres
+    memory_idx: Optional[torch.Tensor] = None  # [n] (sequence slot*2 + hand) - set by step_poses, where n is data dependent
 
 
 class BatchedHandTracker:
@@ -178,15 +207,109 @@ class BatchedHandTracker:
         cur.wait_event(ready)
         if ev: ev[2].record(cur)
         r = self.step_device(st)
+        return self._finish(slot, r, ev, out_host)
+
+    def _finish(self, slot, r: BatchResult, ev, out_host):
+        cur = torch.cuda.current_stream(self._device)
         free = ev[3] if ev else torch.cuda.Event()
         free.record(cur)
         if ev: self.trace.append(ev)
         self._stage_free[slot] = free
+        res = {k: v for k, v in vars(r).items() if v is not None}
         if out_host is None:
-            out_host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True) for k, v in vars(r).items()}
-        for k, v in vars(r).items():
-            out_host[k].copy_(v, non_blocking=True)
+            out_host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True) for k, v in res.items()}
+        for k, v in res.items():
+            out_host[k][: v.shape[0]].copy_(v, non_blocking=True)
         return out_host
+
+    # ------------------------------------------------------------------ poses in, poses out
+    def attach_rig(self, cameras, camera_angles, opts: Optional[CropCameraOpts] = None) -> None:
+        """Enable step_poses: the rig's cameras (constant per recording) go to the device once."""
+        self._rig = DeviceRig(cameras, camera_angles, self._hm, self._device)
+        self._cc_opts = opts or CropCameraOpts()
+        self._history = None
+        self._pstage = [None, None]
+
+    def reset_history(self) -> None:
+        if getattr(self, "_history", None) is not None:
+            self._history.zero_()
+
+    def step_poses(self, pb: PoseBatch, out_host: Optional[dict] = None) -> dict:
+        """One time step from what a recording provides (frames, camera poses, the pose each crop is
+        centred on): crop cameras + every model input are generated ON THE DEVICE
+        (at_gen_crop_cameras: the reference's HandTracker.gen_crop_cameras + _make_inputs,
+        tracker.py:222-260,315-368), then source-box pull -> resampler -> network -> FK as in step().
+        The host waits once per call for the two output counts (n hands, c crops) of the generator,
+        which ran on the side stream ahead of the previous step's kernels.
+        Returns pinned host buffers at capacity size plus out["n"]: the first n rows are valid after
+        a stream synchronize (rows follow out["memory_idx"] = sequence slot*2 + hand)."""
+        if getattr(self, "_rig", None) is None:
+            raise _cabi.AbsoluteTrackError("step_poses: call attach_rig(cameras, camera_angles) first")
+        if not pb.frames.is_pinned():
+            raise _cabi.AbsoluteTrackError("step_poses reads the frames in place: they must be pinned host memory")
+        slot, self._slot = self._slot, self._slot ^ 1
+        cur = torch.cuda.current_stream(self._device)
+        cs = self._copy_stream
+        S, H, V, W = pb.frames.shape
+        P = int(pb.joint_angles.shape[0])
+        small = [f for f in pb.__dataclass_fields__ if f != "frames"]
+        st = self._pstage[slot]
+        if st is None or st["frames"].shape != pb.frames.shape or st["joint_angles"].shape[0] != P:
+            dev = self._device
+            st = {f: torch.empty_like(getattr(pb, f), device=dev) for f in small}
+            st["frames"] = torch.empty(pb.frames.shape, dtype=torch.uint8, device=dev)
+            st["out"] = alloc_crop_inputs(P, self._cc_opts.max_view_num, dev)
+            st["ws"] = torch.empty((int(_cabi.lib().at_crop_cameras_workspace_bytes(P, self._cc_opts.max_view_num)),),
+                                   dtype=torch.uint8, device=dev)
+            st["counts_host"] = torch.zeros((4,), dtype=torch.int32).pin_memory()
+            self._pstage[slot] = st
+            self._stage_free[slot] = None
+            cs.wait_stream(cur)  # allocator reuse: see step()
+        if self._history is None or self._history.numel() != 2 * S:
+            self._history = torch.zeros((2 * S,), dtype=torch.bool, device=self._device)
+            cs.wait_stream(cur)
+        if self._stage_free[slot] is not None:
+            cs.wait_event(self._stage_free[slot])
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)] if self.trace is not None else None
+        with torch.cuda.stream(cs):
+            if ev: ev[0].record(cs)
+            for f in small:
+                st[f].copy_(getattr(pb, f), non_blocking=True)
+            gen_crop_inputs_cuda(self._rig, st["joint_angles"], st["wrist_xforms"], st["pose_frame"], st["pose_hand"],
+                                 st["camera_to_world"], self._cc_opts, pose_valid=st["pose_valid"],
+                                 tracking_history=self._history, out=st["out"], workspace=st["ws"])
+            st["counts_host"].copy_(st["out"].counts, non_blocking=True)
+            counted = torch.cuda.Event()
+            counted.record(cs)
+        counted.synchronize()  # the only host wait: (n, c) size the launches below
+        ci = st["out"].resolve(st["counts_host"])
+        if ci.n == 0:
+            self._stage_free[slot] = None
+            if out_host is not None:
+                out_host["n"] = 0
+            return out_host if out_host is not None else {"n": 0}
+        if self._crops_done is not None:
+            cs.wait_event(self._crops_done)
+        with torch.cuda.stream(cs):
+            crop_pull_source_boxes_cuda(pb.frames, st["frames"], H * V * W, W, V * W, ci.crop_params, (96, 96),
+                                        self.pull_ctas, self.pulled_bytes)
+            ready = ev[1] if ev else torch.cuda.Event()
+            ready.record(cs)
+        cur.wait_event(ready)
+        if ev: ev[2].record(cur)
+        r = self.step_device(FrameBatch(st["frames"], ci.crop_params, ci.intrinsics, ci.extrinsics, ci.sample_range,
+                                        ci.hand_idx, ci.memory_idx, ci.use_memory))
+        r.memory_idx = ci.memory_idx
+        if out_host is None:
+            out_host = {
+                "joint_angles": torch.empty((P, 22), dtype=torch.float32, pin_memory=True),
+                "wrist_xforms": torch.empty((P, 4, 4), dtype=torch.float32, pin_memory=True),
+                "landmarks": torch.empty((P, 21, 3), dtype=torch.float32, pin_memory=True),
+                "memory_idx": torch.empty((P,), dtype=torch.int64, pin_memory=True),
+            }
+        out_host["n"] = ci.n
+        out_host["c"] = ci.c
+        return self._finish(slot, r, ev, out_host)
 
     def check(self) -> None:
         self._model.check_status()

@@ -55,6 +55,9 @@ class HandTrackerOpts:
     # B200 extension: "fp64" reproduces the reference's float64 map bit for bit, "fp32" is the
     # HBM-roofline mode (<= 1.2e-4 px map error)
     map_mode: str = "fp64"
+    # B200 extension: "device" builds the crop cameras with csrc/crop_cameras.cu (one launch set per
+    # frame), "host" with the numpy mirror of perspective_crop.py / crop.py (FK still on the GPU)
+    crop_cameras: str = "device"
 
 
 def pack_crop_params(records) -> np.ndarray:
@@ -172,6 +175,38 @@ class HandTracker:
         self._min_required_vis_landmarks: int = opts.min_required_vis_landmarks
         self._map_mode = getattr(opts, "map_mode", "fp64")
         self._valid_tracking_history = np.zeros(2, dtype=bool)
+        self._crop_cameras_mode = getattr(opts, "crop_cameras", "device")
+        if self._crop_cameras_mode not in ("device", "host"):
+            raise ValueError("HandTrackerOpts.crop_cameras must be 'device' or 'host'")
+        self._rig_cache = {}
+
+    def _gen_crop_cameras_device(self, cameras, camera_angles, hand_model, gt_tracking, min_num_crops):
+        """tracker.py:222-260 in one at_gen_crop_cameras call for all hands of the frame."""
+        from .crop_cameras import CropCameraOpts, DeviceRig, crop_cameras_to_dict, gen_crop_inputs_cuda
+
+        key = (id(hand_model), tuple(float(a) for a in camera_angles),
+               tuple((c.width, c.height, tuple(c.f), tuple(c.c), tuple(c.distort)) for c in cameras))
+        rig = self._rig_cache.get(key)
+        if rig is None:
+            self._rig_cache.clear()
+            rig = self._rig_cache[key] = DeviceRig(cameras, camera_angles, hand_model, self._device)
+            rig._hand_model_ref = hand_model  # keeps id(hand_model) unique while cached
+        hands = list(gt_tracking.keys())
+        dev = self._device
+        ja = torch.from_numpy(np.stack([np.asarray(gt_tracking[h].joint_angles, np.float64) for h in hands])).float().to(dev)
+        wx = torch.from_numpy(np.stack([np.asarray(gt_tracking[h].wrist_xform, np.float64) for h in hands])).float().to(dev)
+        valid = torch.tensor([gt_tracking[h].hand_confidence >= CONFIDENCE_THRESHOLD for h in hands], dtype=torch.bool).to(dev)
+        c2w = torch.from_numpy(np.stack([np.asarray(c.camera_to_world_xf, np.float64) for c in cameras])[None]).contiguous().to(dev)
+        opts = CropCameraOpts(
+            num_crop_points=self._num_crop_points, min_required_vis_landmarks=self._min_required_vis_landmarks,
+            max_view_num=MAX_VIEW_NUM, min_num_crops=min_num_crops, sort_camera_index=True, mirror_right_hand=True,
+            crop_size=tuple(int(s) for s in self._input_size), focal_multiplier=self._hand_ratio_in_crop,
+        )
+        res = gen_crop_inputs_cuda(
+            rig, ja, wx, torch.zeros(len(hands), dtype=torch.int32, device=dev),
+            torch.tensor(hands, dtype=torch.int32).to(dev), c2w, opts, pose_valid=valid,
+        )
+        return crop_cameras_to_dict(res.resolve(), opts.crop_size)
 
     def reset_history(self) -> None:
         self._valid_tracking_history[:] = False
@@ -187,6 +222,8 @@ class HandTracker:
         crop_cameras: Dict[int, Dict[int, camera.PinholePlaneCameraModel]] = {}
         if not gt_tracking:
             return crop_cameras
+        if self._crop_cameras_mode == "device":
+            return self._gen_crop_cameras_device(cameras, camera_angles, hand_model, gt_tracking, min_num_crops)
         for hand_idx, pose in gt_tracking.items():
             if pose.hand_confidence < CONFIDENCE_THRESHOLD:
                 continue

@@ -313,6 +313,47 @@ def main():
     h2d = small + (pulled if pulled > 0 else host[0].frames.numel())
     d2h = sum(v.numel() * v.element_size() for v in out_host[0].values())
 
+    # ---- end to end from what a recording provides: frames + camera poses + the pose each crop is centred on.
+    # Crop cameras and every model input are generated on the device inside the timed region
+    # (at_gen_crop_cameras = the reference's HandTracker.gen_crop_cameras + _make_inputs).
+    e2e_poses = None
+    if args.ingest == "pull":
+        from absolutetrack_b200.lib.tracker.crop_cameras import gen_crop_inputs_cuda
+
+        tracker.attach_rig(*synthetic.rig_cameras())
+        pbs = [synthetic.make_pose_batch(seq_ids, i, frames=host[i].frames).pin() for i in range(NB)]
+        out_p = [None]
+        issue_p = [0.0]
+
+        def step_poses(i):
+            t0 = time.perf_counter()
+            out_p[0] = tracker.step_poses(pbs[i % NB], out_p[0])
+            issue_p[0] += time.perf_counter() - t0
+
+        ms_p, launches_p = timed(step_poses, args.steps, args.warmup)
+        tracker.check()
+        assert out_p[0]["n"] == n and out_p[0]["c"] == c, "device crop cameras selected other views than the reference"
+        pulled0 = int(tracker.pulled_bytes.item())
+        step_poses(0); step_poses(1)
+        torch.cuda.synchronize()
+        pulled_p = (int(tracker.pulled_bytes.item()) - pulled0) // 2
+        pdev = [getattr(pbs[0], f).to(dev) for f in ("joint_angles", "wrist_xforms", "pose_frame", "pose_hand", "camera_to_world")]
+        pvalid = pbs[0].pose_valid.to(dev)
+        gen_out = [None]
+
+        def st_gen(i):
+            gen_out[0] = gen_crop_inputs_cuda(tracker._rig, *pdev, tracker._cc_opts, pose_valid=pvalid, out=gen_out[0],
+                                              workspace=getattr(gen_out[0], "_workspace", None))
+
+        ms_gen, _ = timed(st_gen, args.steps, 3)
+        e2e_poses = {"value": world * n / (ms_p / args.steps * 1e-3), "unit": UNIT,
+                     "h2d_bytes_per_step": pbs[0].small_nbytes() + pulled_p,
+                     "d2h_bytes_per_step": sum(v.numel() * v.element_size() for k, v in out_p[0].items() if hasattr(v, "numel")) + 16,
+                     "api": "BatchedHandTracker.step_poses (pinned frames + poses + camera poses in; crop cameras and model inputs "
+                            "generated on the device inside the timed region)",
+                     "host_issue_ms_per_step": issue_p[0] / (args.steps + args.warmup + 2) * 1e3,
+                     "crop_cameras_ms": ms_gen / args.steps, "gpu_launches": int(launches_p)}
+
     # ---- per-stage timings (device resident) for the roofline
     b0 = devb[0]
     crops = [None]
@@ -374,6 +415,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "api": "BatchedHandTracker.step (pinned host buffers)", "ingest": ingest, "host_issue_ms_per_step": issue_ms,
                     "host_frame_bytes_per_step": int(host[0].frames.numel())},
+            "e2e_from_poses": e2e_poses,
             "gpu_launches": int(launches),
             "roofline": {"bound": "tensor", "kernel": "per-view encoder (all conv launches of at_encoder_forward)",
                          "achieved": enc_tflops, "peak": tf_peak, "unit": "TFLOP/s", "frac": enc_tflops / tf_peak,

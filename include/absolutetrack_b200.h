@@ -134,6 +134,77 @@ int at_fk_skin_f32(const float* joint_angles, const float* wrist_xforms, const i
                    const AtHandModel* model, int64_t n, float* landmarks, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * (5) Crop-camera generation + model-input assembly on the device.  Replaces
+ * HandTracker.gen_crop_cameras (lib/tracker/tracker.py:222-260) with everything below it -
+ * perspective_crop.gen_crop_cameras_from_pose (:136-180), _get_crop_points_from_hand_pose
+ * (:89-133: landmarks of the given pose, the neutral pose and the open pose under one wrist
+ * transform, float32 FK), rank_hand_visibility_in_cameras (:54-86: Fisheye62 projection of the 21
+ * landmarks into every camera, float64), crop.gen_crop_parameters_from_points (crop.py:31-82:
+ * bounding-box centre, affine.make_look_at_matrix affine.py:47-76 with from_two_vectors :34-44 and
+ * the camera roll, x mirror for right hands, gen_intrinsics_from_bounding_pts crop.py:15-28) - and
+ * the per-crop half of HandTracker._make_inputs (tracker.py:315-368: intrinsics matrix,
+ * world->crop-eye extrinsics in metres, sample_range, hand_idx, memory_idx, use_memory from the
+ * tracking history of tracker.py:105,409-410) plus the AtCropParams record of every crop.
+ * Camera math in float64 like the reference's numpy; rigid transforms are inverted as rigid
+ * transforms (R^T, -R^T t) instead of LAPACK's general inverse (difference: fp64 round-off).
+ * Output order is the reference's: poses in input order, per pose the selected cameras (by camera
+ * index when sort_camera_index, else most visible landmarks first, stable), poses with fewer than
+ * min_num_crops views dropped.
+ * ---------------------------------------------------------------------------------------- */
+typedef struct AtRigCamera { /* one physical Fisheye62 camera of the headset (constant per recording) */
+  double f[2];
+  double c[2];
+  double k[8];       /* k1 k2 k3 k4 p1 p2 k5 k6 */
+  double angle_deg;  /* camera_angles[cam]: physical roll of the camera (affine.py:73) */
+  int32_t width, height;
+} AtRigCamera; /* 112 bytes */
+
+typedef struct AtCropCameraOpts {
+  int32_t num_crop_points;            /* 21, 42 or 63 (HandTrackerOpts.num_crop_points, tracker.py:51) */
+  int32_t min_required_vis_landmarks; /* 19 (tracker.py:56) */
+  int32_t max_view_num;               /* 2 (tracker.py:37 MAX_VIEW_NUM); <= 4 */
+  int32_t min_num_crops;              /* gen_crop_cameras(min_num_crops) (tracker.py:228,257) */
+  int32_t sort_camera_index;          /* 1 (tracker.py:250) */
+  int32_t mirror_right_hand;          /* 1 (tracker.py:252) */
+  int32_t crop_w, crop_h;             /* model.getInputImageSizes(): 96 x 96 */
+  double focal_multiplier;            /* hand_ratio_in_crop 0.8 (tracker.py:55,251) */
+  double min_focal;                   /* 5 (crop.py:16) */
+} AtCropCameraOpts;
+
+typedef struct AtCropCameraInputs {
+  const float* joint_angles;         /* [n_poses,22] */
+  const float* wrist_xforms;         /* [n_poses,4,4] wrist->world (mm) as in SingleHandPose: right hands NOT mirrored */
+  const int32_t* pose_frame;         /* [n_poses] frame (sequence slot) of each pose */
+  const int32_t* pose_hand;          /* [n_poses] 0 = left, 1 = right */
+  const uint8_t* pose_valid;         /* [n_poses] hand_confidence >= 0.5 (tracker.py:236), NULL = all valid */
+  const float* neutral_joint_angles; /* [22] perspective_crop.neutral_joint_angles(hand_model) (:17-24) */
+  const double* camera_to_world;     /* [n_frames,n_cams,4,4] row-major */
+  const AtRigCamera* cameras;        /* [n_cams] (device) */
+  int32_t n_poses, n_frames, n_cams; /* n_cams <= 8 */
+  int32_t reserved;
+} AtCropCameraInputs;
+
+typedef struct AtCropCameraOutputs { /* capacity: n_poses samples, n_poses*max_view_num crops */
+  AtCropParams* crop_params;    /* [c] frame = pose_frame, view = camera index */
+  float* intrinsics;            /* [c,3,3] uv_to_window_matrix (camera.py:371-379) */
+  float* extrinsics;            /* [c,4,4] world->crop-eye, translation in metres (tracker.py:343-345) */
+  double* crop_camera_to_world; /* [c,4,4] of the PinholePlaneCameraModel (crop.py:81), mm; may be NULL */
+  int32_t* crop_camera_index;   /* [c] source camera of each crop; may be NULL */
+  int64_t* sample_range;        /* [n,2] */
+  int64_t* hand_idx;            /* [n] */
+  int64_t* memory_idx;          /* [n] = pose_frame*2 + hand */
+  uint8_t* use_memory;          /* [n] tracking_history[memory_idx] before this call */
+  int32_t* pose_index;          /* [n] input pose of each emitted sample; may be NULL */
+  uint8_t* tracking_history;    /* [n_frames*2] in/out: slot of every input pose := "emitted" (tracker.py:409-410); may be NULL */
+  int32_t* counts;              /* [4]: n samples, c crops, poses for which crop.py:25-26 would raise, 0 */
+} AtCropCameraOutputs;
+
+int64_t at_crop_cameras_workspace_bytes(int n_poses, int max_view_num);
+int at_gen_crop_cameras(const AtCropCameraInputs* in, const AtHandModel* hand_model /* shared, mm */,
+                        const AtCropCameraOpts* opts, const AtCropCameraOutputs* out, void* workspace,
+                        int64_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * (2)+(3) Network.  Replaces UmeTrackModel.regress_pose_use_skeleton / regress_pose_pred_skel_scale
  * (lib/models/umetrack_model.py:188-242) and everything below them: backbone
  * (model_utils.py:107-138, backbone_resnet.py:14-158), FTL (model_utils.py:57-104,166-192),

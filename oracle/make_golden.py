@@ -13,6 +13,11 @@ Fixtures
                   reference HandTracker.gen_crop_cameras (tracker.py:222-260) produced.
   warp.npz        reference tracker._warp_image (tracker.py:61-89, numpy fp64 + cv2.remap)
                   outputs for crops of that geometry on seeded synthetic images.
+  crop_cameras.npz  reference perspective_crop.gen_crop_cameras_from_pose (:136-180) on frames of
+                  all four sample recordings, default HandTracker options plus variants (rank
+                  by visibility instead of camera index, 21/42 crop points, thresholds, up to
+                  4 views, poses pushed towards the image borders) -> selected cameras + crop
+                  camera intrinsics / extrinsics.
   model.npz       reference UmeTrackModel outputs (umetrack_model.py:188-242) for the seeded
                   state dict of absolutetrack_b200 `make_random_state_dict(0)`.
 """
@@ -146,6 +151,63 @@ def make_geometry():
     print("geometry.npz", F, "frames", int((cc_cam >= 0).sum()), "crops")
 
 
+CROPCAM_VARIANTS = [
+    # (num_crop_points, min_vis, max_views, sort_camera_index, focal_multiplier, lateral shift mm)
+    (63, 19, 2, True, 0.8, 0.0),       # HandTrackerOpts defaults (tracker.py:49-58,222-260)
+    (63, 19, 4, False, 0.95, 0.0),     # gen_crop_cameras_from_pose defaults: ranked by visibility
+    (21, 12, 3, False, 0.8, 120.0),    # hands pushed sideways: fewer cameras see them
+    (42, 19, 2, True, 0.9, -150.0),
+    (63, 5, 4, False, 0.8, 250.0),
+]
+
+
+def make_cropcams():
+    from lib.tracker.perspective_crop import gen_crop_cameras_from_pose
+
+    recs = ["sample_data/recording_00.json"] + [f"sample_data/user05/recording_{r}.json" for r in ("00", "02", "11")]
+    rows = {k: [] for k in ("rec", "frame", "hand", "variant", "joint_angles", "wrist", "c2w", "n_sel", "sel_cam",
+                            "sel_f", "sel_c", "sel_c2w")}
+    out = {}
+    for ri, rec in enumerate(recs):
+        L = _load_hand_pose_labels(f"{REF}/{rec}")
+        out.update({f"r{ri}_cam_f": np.array([c.f for c in L.cameras]), f"r{ri}_cam_c": np.array([c.c for c in L.cameras]),
+                    f"r{ri}_cam_coeffs": np.array([tuple(c.distort) for c in L.cameras]),
+                    f"r{ri}_cam_wh": np.array([(c.width, c.height) for c in L.cameras], np.int64),
+                    f"r{ri}_camera_angles": np.array(L.camera_angles, np.float64)})
+        out.update(hand_model_arrays(L.hand_model, f"r{ri}_"))
+        for fi in range(ri, len(L), 23):
+            for vi, (ncp, minvis, maxv, sort_idx, fmul, shift) in enumerate(CROPCAM_VARIANTS):
+                for h in range(2):
+                    if L.hand_confidences[fi, h] <= 0:
+                        continue
+                    wrist = L.wrist_transforms[fi, h].astype(np.float64).copy()
+                    # shift along the x axis of camera 1 (world units: mm)
+                    wrist[:3, 3] += shift * L.camera_to_world_transforms[fi, 1][:3, 0]
+                    cams = [c.copy(camera_to_world_xf=L.camera_to_world_transforms[fi, i]) for i, c in enumerate(L.cameras)]
+                    pose = SingleHandPose(L.joint_angles[fi, h], wrist, 1.0)
+                    try:
+                        cc = gen_crop_cameras_from_pose(cams, L.camera_angles, L.hand_model, pose, h, ncp, (96, 96),
+                                                        max_view_num=maxv, sort_camera_index=sort_idx, focal_multiplier=fmul,
+                                                        mirror_right_hand=True, min_required_vis_landmarks=minvis)
+                        n_sel = len(cc)
+                    except ValueError:
+                        cc, n_sel = {}, -1  # "Unable to create crop camera" (crop.py:25-26)
+                    sel_cam = -np.ones(4, np.int64); sel_f = np.zeros((4, 2)); sel_c = np.zeros((4, 2)); sel_c2w = np.zeros((4, 4, 4))
+                    for s, (ci, cam) in enumerate(cc.items()):
+                        sel_cam[s], sel_f[s], sel_c[s], sel_c2w[s] = ci, cam.f, cam.c, cam.camera_to_world_xf
+                    for k, v in (("rec", ri), ("frame", fi), ("hand", h), ("variant", vi),
+                                 ("joint_angles", L.joint_angles[fi, h].astype(np.float64)), ("wrist", wrist),
+                                 ("c2w", L.camera_to_world_transforms[fi].astype(np.float64)), ("n_sel", n_sel),
+                                 ("sel_cam", sel_cam), ("sel_f", sel_f), ("sel_c", sel_c), ("sel_c2w", sel_c2w)):
+                        rows[k].append(v)
+    out.update({k: np.array(v) for k, v in rows.items()})
+    out["variants"] = np.array([[a, b, c, int(d), e, f] for a, b, c, d, e, f in CROPCAM_VARIANTS], np.float64)
+    np.savez_compressed(os.path.join(GOLD, "crop_cameras.npz"), **out)
+    import collections
+    print("crop_cameras.npz", len(out["rec"]), "poses; views per pose:", sorted(collections.Counter(out["n_sel"].tolist()).items()),
+          "; camera sets:", collections.Counter(tuple(int(c) for c in r if c >= 0) for r in out["sel_cam"]).most_common(12))
+
+
 def _load_generic():
     import json
 
@@ -186,11 +248,13 @@ def make_warp():
 
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
-    what = sys.argv[1:] or ["fk", "geometry", "warp", "model"]
+    what = sys.argv[1:] or ["fk", "geometry", "warp", "cropcams", "model"]
     if "fk" in what:
         make_fk()
     if "geometry" in what:
         make_geometry()
+    if "cropcams" in what:
+        make_cropcams()
     if "warp" in what:
         make_warp()
     if "model" in what:

@@ -220,6 +220,112 @@ def landmarks_from_hand_pose(model, joint_angles, wrist_xform, hand_idx):
 
 
 # --------------------------------------------------------------------------------------
+# crop-camera generation (lib/tracker/perspective_crop.py:54-180, lib/common/crop.py:15-82,
+# lib/common/affine.py:34-76, lib/tracker/tracker.py:222-260)
+# --------------------------------------------------------------------------------------
+
+
+def neutral_joint_angles(joint_limits, lower_factor=0.5):
+    """perspective_crop.py:17-24: midpoint of the joint limits (float32, like the torch tensor)."""
+    lim = np.asarray(joint_limits, np.float32)
+    return lim[..., 0] * np.float32(lower_factor) + lim[..., 1] * np.float32(1 - lower_factor)
+
+
+def crop_points_from_hand_pose(model, joint_angles, wrist_xform, hand_idx, num_crop_points):
+    """perspective_crop.py:89-133: landmarks of the pose, the neutral pose and the open (zero)
+    pose under the same wrist transform -> float32 [21 | 42 | 63, 3]."""
+    assert num_crop_points in (21, 42, 63)
+    sets = [np.asarray(joint_angles, np.float32)]
+    if num_crop_points > 21:
+        sets.append(neutral_joint_angles(model["joint_limits"]))
+    if num_crop_points > 42:
+        sets.append(np.zeros(22, np.float32))
+    ja = np.stack(sets)
+    xf = np.broadcast_to(np.asarray(wrist_xform, np.float64), (len(sets), 4, 4))
+    return landmarks_from_hand_pose(model, ja, xf, hand_idx).reshape(-1, 3)
+
+
+def rank_hand_visibility(cams, landmarks_world, min_required_vis_landmarks):
+    """perspective_crop.py:54-86: cameras (dicts with c2w,f,c,coeffs,width,height) that see at
+    least `min_required_vis_landmarks` landmarks, most first (stable sort)."""
+    counts, keep = [], []
+    for i, cam in enumerate(cams):
+        eye = world_to_eye(cam["c2w"], np.asarray(landmarks_world))
+        win = fisheye62_eye_to_window(eye, cam["f"], cam["c"], cam["coeffs"])
+        n_vis = int(((win[..., 0] >= 0) & (win[..., 0] <= cam["width"] - 1) & (win[..., 1] >= 0)
+                     & (win[..., 1] <= cam["height"] - 1) & (eye[..., 2] > 0)).sum())
+        counts.append(n_vis)
+        if n_vis >= min_required_vis_landmarks:
+            keep.append(i)
+    keep.sort(reverse=True, key=lambda i: counts[i])
+    return keep, counts
+
+
+def from_two_vectors(a_orig, b_orig):
+    """affine.py:34-44."""
+    a = a_orig / np.maximum(5.43e-20, np.sqrt((a_orig * a_orig).sum()))
+    b = b_orig / np.maximum(5.43e-20, np.sqrt((b_orig * b_orig).sum()))
+    v = np.cross(a, b)
+    s = np.linalg.norm(v)
+    c = np.dot(a, b)
+    K = np.array([[0, -v[2], v[1]], [v[2], 0, -v[0]], [-v[1], v[0], 0]], dtype=v.dtype)
+    return np.eye(3) + K + (K @ K) * (1 - c) / max(s * s, 1e-15)
+
+
+def make_look_at_matrix(orig_world_to_eye, center, camera_angle=0.0):
+    """affine.py:47-76 (scipy Rotation.from_euler('z', angle, degrees=True) written out)."""
+    local = center @ orig_world_to_eye[:3, :3].T + orig_world_to_eye[:3, 3]
+    z_dir = local / np.linalg.norm(local)
+    dR = from_two_vectors(np.array([0, 0, 1], dtype=np.asarray(center).dtype), z_dir)
+    e2w = np.linalg.inv(orig_world_to_eye)
+    out = e2w.copy()
+    out[:3, :3] = e2w[:3, :3] @ dR
+    t = np.deg2rad(camera_angle)
+    rz = np.array([[np.cos(t), -np.sin(t), 0.0], [np.sin(t), np.cos(t), 0.0], [0.0, 0.0, 1.0]])
+    out[:3, :3] = out[:3, :3] @ rz
+    return np.linalg.inv(out)
+
+
+def gen_crop_parameters_from_points(c2w_orig, pts_world, new_image_size, mirror_img_x, camera_angle, focal_multiplier,
+                                    min_focal=5):
+    """crop.py:31-82 + :15-28 -> (f [2], c [2], camera_to_world [4,4]) of the pinhole crop camera."""
+    pts_world = np.asarray(pts_world)
+    w2e = np.linalg.inv(np.asarray(c2w_orig, np.float64))
+    center = (pts_world.min(axis=0) + pts_world.max(axis=0)) / 2.0
+    new_w2e = make_look_at_matrix(w2e, center, camera_angle)
+    if mirror_img_x:
+        flip = np.eye(4, dtype=np.float32)
+        flip[0, 0] = -1
+        new_w2e = flip @ new_w2e
+    pts_eye = pts_world @ new_w2e[:3, :3].T + new_w2e[:3, 3]
+    ndc = pts_eye[..., :2] / pts_eye[..., 2:]
+    cx_cy = (np.array(new_image_size, dtype=pts_eye.dtype) - 1) / 2
+    fx_fy = cx_cy / np.abs(ndc).max()
+    if np.any(pts_eye[..., 2:] < 0.0001) or np.any(fx_fy < min_focal):
+        raise ValueError("Unable to create crop camera", fx_fy)
+    return focal_multiplier * fx_fy, cx_cy, np.linalg.inv(new_w2e)
+
+
+def gen_crop_cameras_from_pose(cams, camera_angles, model, joint_angles, wrist_xform, hand_idx, num_crop_points=63,
+                               new_image_size=(96, 96), max_view_num=2, sort_camera_index=True, focal_multiplier=0.8,
+                               mirror_right_hand=True, min_required_vis_landmarks=19):
+    """perspective_crop.py:136-180 -> ordered list of (cam_idx, f, c, camera_to_world)."""
+    pts = crop_points_from_hand_pose(model, joint_angles, wrist_xform, hand_idx, num_crop_points)
+    keep, _ = rank_hand_visibility(cams, pts[:21], min_required_vis_landmarks)
+    if sort_camera_index:
+        keep = sorted(keep)
+    out = []
+    for ci in keep:
+        f, c, c2w = gen_crop_parameters_from_points(cams[ci]["c2w"], pts, new_image_size,
+                                                    mirror_right_hand and hand_idx == 1, camera_angles[ci],
+                                                    focal_multiplier)
+        out.append((ci, f, c, c2w))
+        if len(out) == max_view_num:
+            break
+    return out
+
+
+# --------------------------------------------------------------------------------------
 # torch_data pinhole->pinhole resampler (lib/batched_dataset/data_transform.py:78-144)
 # --------------------------------------------------------------------------------------
 

@@ -136,6 +136,36 @@ def test_model_oracle_matches_reference_golden(gold, head):
         assert np.abs(out["sigmas"].numpy() - M[f"{head}{t}_sigmas"]).max() < 2e-5
 
 
+def cropcam_case(C, i):
+    """Inputs of golden row i of crop_cameras.npz for the oracle / the kernel."""
+    ri = int(C["rec"][i])
+    pre = f"r{ri}_"
+    cams = [dict(c2w=C["c2w"][i, v], f=C[pre + "cam_f"][v], c=C[pre + "cam_c"][v], coeffs=C[pre + "cam_coeffs"][v],
+                 width=int(C[pre + "cam_wh"][v, 0]), height=int(C[pre + "cam_wh"][v, 1])) for v in range(4)]
+    model = {k: C[pre + k] for k in ("joint_rotation_axes", "joint_rest_positions", "landmark_rest_positions",
+                                     "landmark_rest_bone_weights", "landmark_rest_bone_indices", "joint_limits")}
+    ncp, minvis, maxv, sort_idx, fmul, _ = C["variants"][int(C["variant"][i])]
+    opts = dict(num_crop_points=int(ncp), min_required_vis_landmarks=int(minvis), max_view_num=int(maxv),
+                sort_camera_index=bool(sort_idx), focal_multiplier=float(fmul))
+    return cams, C[pre + "camera_angles"], model, opts
+
+
+def test_oracle_crop_cameras_match_reference_golden(gold):
+    """gen_crop_cameras_from_pose restatement vs the reference's own outputs on 770 poses of the four
+    sample recordings x 5 option variants: selection exact; cameras to the round-off of the float32
+    FK landmarks they are fitted to (1e-4 mm on ~300 mm: 1e-6 relative)."""
+    C = gold["crop_cameras"]
+    for i in range(len(C["rec"])):
+        cams, angles, model, opts = cropcam_case(C, i)
+        got = O.gen_crop_cameras_from_pose(cams, angles, model, C["joint_angles"][i], C["wrist"][i], int(C["hand"][i]), **opts)
+        assert [g[0] for g in got] == [int(c) for c in C["sel_cam"][i] if c >= 0], i
+        for s, (_, f, c, c2w) in enumerate(got):
+            assert np.allclose(f, C["sel_f"][i, s], rtol=3e-6)
+            assert np.allclose(c, C["sel_c"][i, s])
+            assert np.abs(c2w[:3, :3] - C["sel_c2w"][i, s][:3, :3]).max() < 3e-6
+            assert np.abs(c2w[:3, 3] - C["sel_c2w"][i, s][:3, 3]).max() < 1e-9
+
+
 def test_oracle_metrics():
     rng = np.random.default_rng(0)
     gt = rng.normal(size=(2, 10, 21, 3))

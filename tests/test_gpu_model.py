@@ -233,7 +233,7 @@ def test_batched_tracker_ingest_modes_agree_and_match_oracle(cuda_lib, state_dic
         for hb in batches:
             if ingest == "device":
                 r = tr.step_device(hb.to("cuda"))
-                o = {k: v.cpu() for k, v in vars(r).items()}
+                o = {k: v.cpu() for k, v in vars(r).items() if v is not None}
             else:
                 o = tr.step(hb)
             torch.cuda.synchronize()

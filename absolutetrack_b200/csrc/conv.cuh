@@ -45,6 +45,12 @@ int conv_f16x3_split_weights(const ConvLayer& L, const float* blob, void* wsplit
 int conv_nhwc_f16x3(const ConvLayer& L, const float* blob, const void* wsplit, const float* in, int in_ld, int in_coff,
                     const float* res, int res_ld, float* out, int out_ld, int out_coff, int N, int H, int W, bool relu,
                     cudaStream_t stream);
+// Pose-head BasicBlocks (4 3x3 convs) as error-compensated fp16 x 3 shift-GEMMs on tcgen05 (conv_tc.cu).
+int64_t head_tc_weight_bytes();            // per conv
+int64_t head_tc_workspace_bytes(int n);
+int head_tc_prepack(const ConvLayer& L, const float* blob, void* dst, cudaStream_t stream);
+int head_tc_forward(const ConvLayer* L4, const float* blob, const void* const* wq, float* x, float* h2, float* y, int hc,
+                    int n, void* workspace, cudaStream_t stream);
 int stem_f32(const ConvLayer& L, const float* blob, const void* crops, int crop_dtype, float* out, int c,
              cudaStream_t stream);
 

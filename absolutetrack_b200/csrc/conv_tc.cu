@@ -63,6 +63,10 @@ struct ConvTcParams {
   uint4* out_ph[4];
   long long out_ph_plane_px;
   float* out_f32;
+  const float* res_f32;   // MODE 4: optional fp32 NHWC residual (channel stride f32_ld)
+  float out_scale;        // MODE 4: accumulator scale (undoes the 2^8 pre-scale of the split weights)
+  int split_planes;       // MODE 4: channel groups per part of the [hi | lo | hi] split output
+  int f32_ld;             // MODE 4: channel stride of out_f32 / res_f32
   int out_mode, relu, fmt;
   int n_src, n_taps, n_kchunks, kc;
   int n, cout;
@@ -100,7 +104,11 @@ struct EpiCoord {
   int ph;
 };
 
-// MODE: 0 planar out, 1 planar out + residual, 2 phase-split out + residual, 3 fp32 NHWC out.
+// MODE: 0 planar out, 1 planar out + residual, 2 phase-split out + residual, 3 fp32 NHWC out,
+// 4 error-compensated ("fp16 x 3") conv of the tail: the input planes are [hi | lo | hi] halves of
+// fp32 activations, the weights [hi | hi | lo] halves pre-scaled by 2^8; the epilogue rescales, adds
+// bias and an optional fp32 NHWC residual, applies ReLU, and writes fp32 NHWC and/or the split planes
+// of the next conv.
 // WRES: the layer's weights stay resident in shared memory (else they stream through a ring).
 template <int NTAPS, int KSTEPS, int MT, int WRES, int MODE>
 __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
@@ -291,7 +299,7 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
     const bool prof = p.prof != nullptr && (p.dbg & 16);
     const int ncg = (p.cout + 7) >> 3;
     constexpr bool has_res = MODE == 1 || MODE == 2;
-    constexpr int out_mode = MODE == 2 ? 1 : (MODE == 3 ? 2 : 0);
+    constexpr int out_mode = MODE == 2 ? 1 : (MODE == 3 ? 2 : (MODE == 4 ? 3 : 0));
     const int n_slabs = (p.n + 31) >> 5;  // 32-column slabs (the last one may hold 16)
     const int S = MT * n_slabs;           // slabs of one tile in flat order f = m * n_slabs + sl
     // Residual ring: 4 slots of one slab (4 channel groups x 16 B per lane).  Slot f & 3 holds flat
@@ -335,8 +343,8 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
           for (int k = 0; k < 4; ++k) {
             const int f = f0 + k;
             if (f >= S) break;
-            const int m = MT == 1 ? 0 : f >> p.slab_shift;
-            const int sl = MT == 1 ? f : f - (m << p.slab_shift);
+            const int m = MT == 1 ? 0 : (MODE == 4 ? (f >= n_slabs ? 1 : 0) : f >> p.slab_shift);
+            const int sl = MT == 1 ? f : (MODE == 4 ? f - m * n_slabs : f - (m << p.slab_shift));
             if (sl == 0) {  // new sub-tile: decode the pixel of this lane
               g = gbase + m * kTileM;
               const uint32_t img = fast_div(g, p.div_hw);
@@ -349,6 +357,8 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
                 o1 = (long long)img * (p.Hp2 * p.Wp2) + (y >> 1) * p.Wp2 + (x >> 1);
               } else if (out_mode == 2) {
                 o1 = ((long long)(img * p.H + y) * p.W + x) * p.cout;
+              } else if (out_mode == 3) {
+                o1 = ((long long)(img * p.H + y) * p.W + x) * p.f32_ld;
               }
             }
             const int c0 = sl << 5;
@@ -375,6 +385,46 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
               float o[8];
               const float4 b0 = *reinterpret_cast<const float4*>(bias_s + (cg < ncg ? cg : 0) * 8);
               const float4 b1 = *reinterpret_cast<const float4*>(bias_s + (cg < ncg ? cg : 0) * 8 + 4);
+              if (MODE == 4) {
+                const float sc = p.out_scale;
+                o[0] = fmaf(__uint_as_float(v[h * 8 + 0]), sc, b0.x); o[1] = fmaf(__uint_as_float(v[h * 8 + 1]), sc, b0.y);
+                o[2] = fmaf(__uint_as_float(v[h * 8 + 2]), sc, b0.z); o[3] = fmaf(__uint_as_float(v[h * 8 + 3]), sc, b0.w);
+                o[4] = fmaf(__uint_as_float(v[h * 8 + 4]), sc, b1.x); o[5] = fmaf(__uint_as_float(v[h * 8 + 5]), sc, b1.y);
+                o[6] = fmaf(__uint_as_float(v[h * 8 + 6]), sc, b1.z); o[7] = fmaf(__uint_as_float(v[h * 8 + 7]), sc, b1.w);
+                const bool live = valid && cg < ncg && (wide || h < 2);
+                const bool full = cg * 8 + 8 <= p.cout;  // the last group of a 76-channel tensor holds 4 channels
+                if (p.res_f32 != nullptr && live) {
+                  const float4 r0 = __ldg(reinterpret_cast<const float4*>(p.res_f32 + o1 + cg * 8));
+                  o[0] += r0.x; o[1] += r0.y; o[2] += r0.z; o[3] += r0.w;
+                  if (full) {
+                    const float4 r1 = __ldg(reinterpret_cast<const float4*>(p.res_f32 + o1 + cg * 8 + 4));
+                    o[4] += r1.x; o[5] += r1.y; o[6] += r1.z; o[7] += r1.w;
+                  }
+                }
+                if (p.relu) {
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) o[i] = fmaxf(o[i], 0.f);
+                }
+                if (p.out_f32 != nullptr && live) {
+                  float4* op = reinterpret_cast<float4*>(p.out_f32 + o1 + cg * 8);
+                  op[0] = make_float4(o[0], o[1], o[2], o[3]);
+                  if (full) op[1] = make_float4(o[4], o[5], o[6], o[7]);
+                }
+                if (p.out != nullptr && cg < p.split_planes && (wide || h < 2)) {
+                  uint4 hi = make_uint4(0u, 0u, 0u, 0u), lo = hi;
+                  if (valid) {  // x = hi + lo with 2 x 11 significant bits; pads stay zero
+                    float a, b;
+                    hi.x = pack2(o[0], o[1], 0); unpack2(hi.x, 0, a, b); lo.x = pack2(o[0] - a, o[1] - b, 0);
+                    hi.y = pack2(o[2], o[3], 0); unpack2(hi.y, 0, a, b); lo.y = pack2(o[2] - a, o[3] - b, 0);
+                    hi.z = pack2(o[4], o[5], 0); unpack2(hi.z, 0, a, b); lo.z = pack2(o[4] - a, o[5] - b, 0);
+                    hi.w = pack2(o[6], o[7], 0); unpack2(hi.w, 0, a, b); lo.w = pack2(o[6] - a, o[7] - b, 0);
+                  }
+                  uint4* op = p.out + (long long)cg * p.out_plane_px + g;
+                  const long long part = (long long)p.split_planes * p.out_plane_px;
+                  op[0] = hi; op[part] = lo; op[2 * part] = hi;
+                }
+                continue;
+              }
               o[0] = __uint_as_float(v[h * 8 + 0]) + b0.x; o[1] = __uint_as_float(v[h * 8 + 1]) + b0.y;
               o[2] = __uint_as_float(v[h * 8 + 2]) + b0.z; o[3] = __uint_as_float(v[h * 8 + 3]) + b0.w;
               o[4] = __uint_as_float(v[h * 8 + 4]) + b1.x; o[5] = __uint_as_float(v[h * 8 + 5]) + b1.y;
@@ -411,7 +461,7 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
               if (f + 4 < S) res_load(rr[k], gbase, f + 4);
               else if (has_next) res_load(rr[k], gbase_next, S >= 4 ? f + 4 - S : f);
             }
-            if (out_mode != 2) {
+            if (out_mode != 2 && out_mode != 3) {
 #pragma unroll
               for (int h = 0; h < 4; ++h) {
                 const int cg = (c0 >> 3) + h;
@@ -727,8 +777,19 @@ struct ConvIo {
   long long out_plane_px;
   long long out_phase_units;
   float* out_f32;
-  int out_mode;
+  int out_mode;              // 0 planar, 1 phase-split, 2 fp32 NHWC, 3 tail "fp16 x 3" (kernel MODE 4)
   bool relu;
+  const float* res_f32;      // out_mode 3
+  float out_scale;
+  int split_planes, f32_ld;
+};
+
+// A convolution that is not a row of the backbone layer table (the pose-head convs of the tail).
+struct TcConvDesc {
+  const char* name;
+  int ksize, stride, cout, n_pad, kc, nk;
+  const void* w;       // packed blocks [kchunk][tap][kc/8][n_pad][8]
+  const float* bias;
 };
 
 int g_mt_override = 0;
@@ -749,12 +810,20 @@ int g_prof_seq = -1;  // >= 0: launch k writes its counters at g_prof + k * 148 
 // `out_level`: geometry of the OUTPUT (= geometry of the input for stride 1, = geometry of each
 // input phase image for stride 2).  `next`: geometry of the phase images written in mode 1.
 int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const Level& OL, const Level* next,
-                   const ConvIo& io, int fmt, cudaStream_t stream) {
-  const ConvLayer& L = layer_table()[layer_id];
-  const TcLayer& T = tc_table()[layer_id];
+                   const ConvIo& io, int fmt, cudaStream_t stream, const TcConvDesc* desc = nullptr) {
+  ConvLayer L;
+  TcLayer T;
+  if (desc != nullptr) {
+    L.name = desc->name; L.cin = desc->kc * desc->nk; L.cout = desc->cout; L.ksize = desc->ksize; L.stride = desc->stride;
+    L.weight_offset = 0; L.bias_offset = 0; L.bf16_offset = -1;
+    T.offset = 0; T.n_pad = desc->n_pad; T.kc = desc->kc; T.nk = desc->nk;
+  } else {
+    L = layer_table()[layer_id];
+    T = tc_table()[layer_id];
+  }
   ConvTcParams p;
   memset(&p, 0, sizeof(p));
-  const bool is_stem = layer_id == L_STEM;
+  const bool is_stem = desc == nullptr && layer_id == L_STEM;
   const int taps = is_stem ? 8 : L.ksize * L.ksize;
   p.n_taps = taps;
   p.kc = T.kc; p.n_kchunks = T.nk; p.n = T.n_pad; p.cout = L.cout;
@@ -790,8 +859,10 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   }
   for (int s = 0; s < p.n_src; ++s) p.a_src[s] = io.a_base + s * io.a_phase_units;
   p.a_plane_px = io.a_plane_px;
-  p.w = reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(tc_blob) + T.offset);
-  p.bias = blob + L.bias_offset;
+  p.w = desc != nullptr ? reinterpret_cast<const uint4*>(desc->w)
+                        : reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(tc_blob) + T.offset);
+  p.bias = desc != nullptr ? desc->bias : blob + L.bias_offset;
+  p.res_f32 = io.res_f32; p.out_scale = io.out_scale; p.split_planes = io.split_planes; p.f32_ld = io.f32_ld;
   p.res = io.res; p.res_plane_px = io.res_plane_px;
   p.out = io.out; p.out_plane_px = io.out_plane_px;
   p.out_mode = io.out_mode; p.relu = io.relu ? 1 : 0; p.fmt = fmt;
@@ -807,6 +878,7 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   // tile / ring configuration
   // sub-tiles (128 pixels each) per tile: measured best per shape on B200 (scripts/tc_prof.py)
   int mt = p.n == 64 ? (io.res != nullptr ? 1 : 2) : (p.n <= 128 ? 2 : 1);
+  if (io.out_mode == 3) mt = 1;  // pose head: 2 tiles per CTA overlap epilogue and MMAs (measured: 0.31 vs 0.34 ms tail)
   {
     // experiment knobs: AT_TC_MT<N> = sub-tiles per tile for layers with padded Cout == N
     char name[32];
@@ -868,12 +940,12 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
     const int n_slabs = (p.n + 31) / 32;
     p.slab_shift = 0;
     while ((1 << p.slab_shift) < n_slabs) ++p.slab_shift;
-    if ((1 << p.slab_shift) != n_slabs && (mt > 1 || io.res != nullptr)) {
+    if ((1 << p.slab_shift) != n_slabs && io.out_mode != 3 && (mt > 1 || io.res != nullptr)) {
       set_error("conv_tc: layer %s: %d slabs per accumulator need mt == 1 and no residual", L.name, n_slabs);
       return AT_ERR_UNSUPPORTED;
     }
   }
-  const int mode = io.out_mode == 2 ? 3 : (io.res != nullptr ? (io.out_mode == 1 ? 2 : 1) : 0);
+  const int mode = io.out_mode == 3 ? 4 : io.out_mode == 2 ? 3 : (io.res != nullptr ? (io.out_mode == 1 ? 2 : 1) : 0);
   if (io.out_mode == 1 && io.res == nullptr) {
     set_error("conv_tc: phase-split output without a residual is not instantiated");
     return AT_ERR_UNSUPPORTED;
@@ -888,6 +960,7 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   AT_TC_CASE3(9, 4, 1, 1) AT_TC_CASE3(9, 4, 2, 1)
   AT_TC_CASE3(9, 4, 1, 0) AT_TC_CASE3(9, 4, 2, 0)
   AT_TC_CASE(1, 2, 1, 1, 0) AT_TC_CASE(1, 4, 1, 1, 0) AT_TC_CASE(1, 4, 1, 1, 3)
+  AT_TC_CASE(9, 5, 1, 0, 4) AT_TC_CASE(9, 5, 2, 0, 4)
 #undef AT_TC_CASE3
 #undef AT_TC_CASE
   if (fn == nullptr) {
@@ -1084,6 +1157,122 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
   }
   (void)workspace_bytes;
   return AT_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// Pose-head 3x3 convolutions (model_utils.py:195-208: two BasicBlocks at 76 / 72 channels on 6x6
+// maps) as error-compensated fp16 x 3 shift-GEMMs on tcgen05.  x = x_hi + x_lo and w = w_hi + w_lo
+// in fp16 (2 x 11 significant bits); the conv runs over 3 x 80 virtual input channels
+//   [x_hi | x_lo | x_hi] * [w_hi | w_hi | w_lo]  =  x_hi w_hi + x_lo w_hi + x_hi w_lo
+// accumulated in fp32 in TMEM: the same arithmetic contract as conv_nhwc_f16x3 (conv_f32.cu), at the
+// UMMA rate instead of the mma.sync rate.  Weights are pre-scaled by 2^8 (their lo halves would fall
+// into the fp16 denormals otherwise); the epilogue rescales.
+namespace tc {
+
+constexpr int kHeadCp = 80;             // channels per part (76 / 72 padded to a multiple of 16)
+constexpr int kHeadParts = 3;
+constexpr float kHeadWScale = 256.0f;
+
+__global__ void head_prepack_kernel(const float* __restrict__ w /*[9][cin][coutP]*/, uint16_t* __restrict__ out, int cin,
+                                    int cout, int coutP) {
+  const int total = kHeadParts * 9 * kHeadCp * kHeadCp;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  // i -> (part = k-chunk, tap, kk, nn, e): the block order prepack_kernel uses
+  const int e = i & 7;
+  int r = i >> 3;
+  const int nn = r % kHeadCp; r /= kHeadCp;
+  const int kk = r % (kHeadCp / 8); r /= (kHeadCp / 8);
+  const int t = r % 9;
+  const int part = r / 9;
+  const int ci = kk * 8 + e;
+  float v = 0.f;
+  if (ci < cin && nn < cout) v = w[((long long)t * cin + ci) * coutP + nn] * kHeadWScale;
+  const __half hi = __float2half_rn(v);
+  const __half lo = __float2half_rn(v - __half2float(hi));
+  const __half o = part == 2 ? lo : hi;
+  out[i] = *reinterpret_cast<const uint16_t*>(&o);
+}
+
+// fp32 NHWC [n,6,6,hc] -> split planes [hi | lo | hi] x 10 channel groups on the padded linear pixel
+// order; pad cells are written as zeros.
+__global__ void head_split_pack_kernel(const float* __restrict__ in, uint4* __restrict__ base /*plane0,px0*/, Level L,
+                                       int hc) {
+  const long long total = L.P * (kHeadCp / 8);
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int cg = (int)(i % (kHeadCp / 8));
+  const long long g = i / (kHeadCp / 8);
+  const int HWp = L.Hp * L.Wp;
+  const long long img = g / HWp;
+  const int rem = (int)(g - img * HWp);
+  const int y = rem / L.Wp, x = rem - y * L.Wp;
+  uint4 hi = make_uint4(0u, 0u, 0u, 0u), lo = hi;
+  if (y < L.H && x < L.W) {
+    const float* ip = in + ((img * L.H + y) * L.W + x) * hc + cg * 8;
+    float v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = cg * 8 + k < hc ? ip[k] : 0.f;
+    float a, b;
+    hi.x = ptx::pack2(v[0], v[1], 0); ptx::unpack2(hi.x, 0, a, b); lo.x = ptx::pack2(v[0] - a, v[1] - b, 0);
+    hi.y = ptx::pack2(v[2], v[3], 0); ptx::unpack2(hi.y, 0, a, b); lo.y = ptx::pack2(v[2] - a, v[3] - b, 0);
+    hi.z = ptx::pack2(v[4], v[5], 0); ptx::unpack2(hi.z, 0, a, b); lo.z = ptx::pack2(v[4] - a, v[5] - b, 0);
+    hi.w = ptx::pack2(v[6], v[7], 0); ptx::unpack2(hi.w, 0, a, b); lo.w = ptx::pack2(v[6] - a, v[7] - b, 0);
+  }
+  uint4* op = base + (long long)cg * L.plane_px + g;
+  const long long part = (long long)(kHeadCp / 8) * L.plane_px;
+  op[0] = hi; op[part] = lo; op[2 * part] = hi;
+}
+
+Level head_level(long long n) { return make_level(6, 6, kHeadParts * kHeadCp, n); }
+
+}  // namespace tc
+
+int64_t head_tc_weight_bytes() { return (int64_t)tc::kHeadParts * 9 * tc::kHeadCp * tc::kHeadCp * 2; }
+
+int64_t head_tc_workspace_bytes(int n) { return 2 * tc::head_level(n > 0 ? n : 1).buf_units() * 16 + 256; }
+
+int head_tc_prepack(const ConvLayer& L, const float* blob, void* dst, cudaStream_t s) {
+  AT_REQUIRE(L.ksize == 3 && L.cin <= tc::kHeadCp && L.cout <= tc::kHeadCp, "head_tc_prepack: not a pose-head 3x3 conv");
+  const int total = tc::kHeadParts * 9 * tc::kHeadCp * tc::kHeadCp;
+  tc::head_prepack_kernel<<<(total + 255) / 256, 256, 0, s>>>(blob + L.weight_offset, reinterpret_cast<uint16_t*>(dst), L.cin,
+                                                              L.cout, (int)round_up(L.cout, 4));
+  return check_launch("head_prepack_kernel");
+}
+
+// The two BasicBlocks of the pose head: x [n,6,6,hc] fp32 NHWC (also the first residual) -> y (same
+// shape; may alias x).  h2: fp32 scratch of the same shape.  wq[i]: head_tc_prepack output of conv i.
+int head_tc_forward(const ConvLayer* L4, const float* blob, const void* const* wq, float* x, float* h2, float* y, int hc,
+                    int n, void* workspace, cudaStream_t s) {
+  using namespace tc;
+  const Level HL = head_level(n);
+  uint4* ws = reinterpret_cast<uint4*>(round_up((int64_t)(uintptr_t)workspace, 128));
+  uint4* A = ws;
+  uint4* B = ws + HL.buf_units();
+  int rc;
+  // the guards in front of / behind the planes are read as halo and never written by the kernels
+  if ((rc = zero_halo(A, 2 * HL.planes(), HL, false, s))) return rc;
+  {
+    const long long total = HL.P * (kHeadCp / 8);
+    head_split_pack_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(x, A + HL.guard, HL, hc);
+    if ((rc = check_launch("head_split_pack_kernel"))) return rc;
+  }
+  auto conv = [&](int i, const uint4* in, const float* res, float* out_f32, uint4* out_split) -> int {
+    TcConvDesc d;
+    d.name = L4[i].name; d.ksize = 3; d.stride = 1; d.cout = L4[i].cout; d.n_pad = kHeadCp; d.kc = kHeadCp; d.nk = kHeadParts;
+    d.w = wq[i]; d.bias = blob + L4[i].bias_offset;
+    ConvIo io;
+    memset(&io, 0, sizeof(io));
+    io.a_base = in + HL.guard; io.a_plane_px = HL.plane_px;
+    io.out = out_split != nullptr ? out_split + HL.guard : nullptr; io.out_plane_px = HL.plane_px;
+    io.out_f32 = out_f32; io.res_f32 = res; io.out_mode = 3; io.relu = true;
+    io.out_scale = 1.0f / kHeadWScale; io.split_planes = kHeadCp / 8; io.f32_ld = hc;
+    return launch_conv_tc(-1, blob, nullptr, HL, nullptr, io, 0, s, &d);
+  };
+  if ((rc = conv(0, A, nullptr, nullptr, B))) return rc;   // block 0 conv1 + ReLU
+  if ((rc = conv(1, B, x, h2, A))) return rc;              // block 0 conv2 + x, ReLU
+  if ((rc = conv(2, A, nullptr, nullptr, B))) return rc;   // block 1 conv1 + ReLU
+  return conv(3, B, h2, y, nullptr);                       // block 1 conv2 + h2, ReLU
 }
 
 }  // namespace at

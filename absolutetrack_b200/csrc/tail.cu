@@ -399,7 +399,8 @@ constexpr int64_t kWsPerSample = kWsFuseIn + kWsF1 + kWsF2 + kWsF3 + 4 * kWsT + 
 
 extern "C" int64_t at_tail_workspace_bytes(int n) {
   if (n < 0) return AT_ERR_INVALID_ARGUMENT;
-  return (int64_t)sizeof(float) * at::kWsPerSample * (int64_t)n + 256;
+  // fp32 NHWC activations of the tail + the split fp16 planes of the tcgen05 pose head
+  return (int64_t)sizeof(float) * at::kWsPerSample * (int64_t)n + 256 + at::head_tc_workspace_bytes(n);
 }
 
 namespace at {
@@ -415,7 +416,17 @@ int64_t f16_blob_offset(int id) {
 }  // namespace
 }  // namespace at
 
-extern "C" int64_t at_tail_f16_blob_bytes(void) { return at::f16_blob_offset(at::L_COUNT); }
+namespace at {
+namespace {
+// the tcgen05 operands of the 8 pose-head 3x3 convs (4 per head) follow the mma.sync operands
+int64_t head_tc_blob_offset(int id) {
+  const int k = id >= L_HEAD_U ? 4 + (id - L_HEAD_U) : id - L_HEAD_K;
+  return round_up(f16_blob_offset(L_COUNT), 256) + (int64_t)k * round_up(head_tc_weight_bytes(), 256);
+}
+}  // namespace
+}  // namespace at
+
+extern "C" int64_t at_tail_f16_blob_bytes(void) { return at::head_tc_blob_offset(at::L_HEAD_U + 4); }
 
 extern "C" int at_tail_prepack_f16(const float* blob, void* f16_blob, void* stream) {
   using namespace at;
@@ -427,6 +438,11 @@ extern "C" int at_tail_prepack_f16(const float* blob, void* f16_blob, void* stre
     int rc = conv_f16x3_split_weights(T[i], blob, (uint8_t*)f16_blob + f16_blob_offset(i), (cudaStream_t)stream);
     if (rc) return rc;
   }
+  for (int hb : {(int)L_HEAD_K, (int)L_HEAD_U})
+    for (int i = 0; i < 4; ++i) {
+      int rc = head_tc_prepack(T[hb + i], blob, (uint8_t*)f16_blob + head_tc_blob_offset(hb + i), (cudaStream_t)stream);
+      if (rc) return rc;
+    }
   return AT_OK;
 }
 
@@ -479,6 +495,7 @@ extern "C" int at_tail_forward_f16(const float* blob, const void* f16_blob, cons
   float* h2 = w;       w += kWsH * n;
   float* ho = w;       w += kWsHo * n;
   float* skel = w;
+  void* head_ws = (uint8_t*)workspace + (int64_t)sizeof(float) * kWsPerSample * (int64_t)n + 256;
 
   // every conv of the tail: error-compensated fp16 x 3 tensor-core GEMM when the pre-split operand
   // blob is given, else the TF32 x 3 kernel on the fp32 blob (both fp32-grade; see conv_f32.cu)
@@ -525,10 +542,19 @@ extern "C" int at_tail_forward_f16(const float* blob, const void* f16_blob, cons
   }
   // pose head (model_utils.py:195-208): 2 BasicBlocks + conv1x1 + global average pool
   const int hb = known ? L_HEAD_K : L_HEAD_U;
-  if ((rc = conv(hb + 0, head_in, hc, nullptr, 0, h1, hc, true))) return rc;
-  if ((rc = conv(hb + 1, h1, hc, head_in, hc, h2, hc, true))) return rc;
-  if ((rc = conv(hb + 2, h2, hc, nullptr, 0, h1, hc, true))) return rc;
-  if ((rc = conv(hb + 3, h1, hc, h2, hc, head_in, hc, true))) return rc;
+  // the four 3x3 convs: tcgen05 shift-GEMMs on split fp16 planes (conv_tc.cu) unless AT_TAIL_HEAD_TC=0
+  const char* head_env = getenv("AT_TAIL_HEAD_TC");  // read per call: tests toggle it
+  const bool head_tc = head_env == nullptr || atoi(head_env) != 0;
+  if (use_f16 && head_tc) {
+    const void* wq[4];
+    for (int i = 0; i < 4; ++i) wq[i] = (const uint8_t*)f16_blob + head_tc_blob_offset(hb + i);
+    if ((rc = head_tc_forward(T + hb, blob, wq, head_in, h2, head_in, hc, n, head_ws, s))) return rc;
+  } else {
+    if ((rc = conv(hb + 0, head_in, hc, nullptr, 0, h1, hc, true))) return rc;
+    if ((rc = conv(hb + 1, h1, hc, head_in, hc, h2, hc, true))) return rc;
+    if ((rc = conv(hb + 2, h2, hc, nullptr, 0, h1, hc, true))) return rc;
+    if ((rc = conv(hb + 3, h1, hc, h2, hc, head_in, hc, true))) return rc;
+  }
   if ((rc = conv(hb + 4, head_in, hc, nullptr, 0, ho, 64, false))) return rc;
   DecodeArgs da;
   da.head_out = ho; da.ld = 64; da.n_out = known ? 62 : 63;

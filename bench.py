@@ -33,6 +33,9 @@ ENCODER_FLOP_PER_CROP = 969_228_288           # SURVEY.md 8(d), counted on the r
 TAIL_FLOP_PER_HAND = 19_150_000
 FK_BYTES_PER_HAND = 404                        # shared hand model
 CROP_SRC_BYTES = 32_160                        # mean source bounding box per crop
+# dram__bytes_read.sum + dram__bytes_write.sum over the conv launches of ONE encoder pass, per crop: 8,387 MB for 2048
+# crops in the ncu --set full capture profiles/r1_conv_tc_ncu_full_summary.csv (= the activations read + written once)
+ENCODER_DRAM_BYTES_PER_CROP = 8_387_313_920 / 2048
 
 
 def load_peaks():
@@ -99,10 +102,10 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------ CPU arm
-def cpu_reference_arm(n_frames, threads, warm=1):
+def cpu_reference_arm(n_frames, threads, warm=1, with_crop_cameras=False):
     """Oracle port of the reference CPU path, frame by frame like run_eval_known_skeleton.py:68-90:
-    4x _warp_image + regress_pose_use_skeleton (torch CPU fp32) + 2x landmarks_from_hand_pose.
-    Returns (hand_frames, seconds)."""
+    [gen_crop_cameras when with_crop_cameras] + 4x _warp_image + regress_pose_use_skeleton (torch CPU
+    fp32) + 2x landmarks_from_hand_pose.  Returns (hand_frames, seconds)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import numpy as np
     import torch
@@ -120,6 +123,8 @@ def cpu_reference_arm(n_frames, threads, warm=1):
     frames = [scenario.synth_frame("noise", i) for i in range(4)]
     hands = 0
     valid = np.zeros(2, bool)
+    G = scenario.geometry()
+    hm_cc = dict(hm, joint_limits=G["hm_joint_limits"])
     t0 = None
     for t in range(warm + n_frames):
         if t == warm:
@@ -129,6 +134,13 @@ def cpu_reference_arm(n_frames, threads, warm=1):
         if not fi["crops"]:
             continue
         frame = frames[t % 4]
+        if with_crop_cameras:  # tracker.gen_crop_cameras (tracker.py:222-260) on the labelled poses of the frame
+            cams = [dict(c2w=G["camera_to_world"][k, v], f=G["cam_f"][v], c=G["cam_c"][v], coeffs=G["cam_coeffs"][v],
+                         width=int(G["cam_wh"][v, 0]), height=int(G["cam_wh"][v, 1])) for v in range(4)]
+            for h in range(2):
+                if G["hand_confidences"][k, h] >= 0.5:
+                    O.gen_crop_cameras_from_pose(cams, G["camera_angles"], hm_cc, G["joint_angles"][k, h],
+                                                 G["wrist_transforms"][k, h], h)
         imgs = [O.warp_image(scenario.src_camera(k, cam), scenario.dst_camera(k, h, s), np.ascontiguousarray(frame[:, cam, :]))
                 for (h, s, cam) in fi["crops"]]
         images = torch.from_numpy(np.stack(imgs).astype(np.float32) / 255.0)
@@ -400,9 +412,11 @@ def main():
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
         hnd, sec = cpu_reference_arm(args.cpu_frames, cores)
-        cpu_baseline = {"value": hnd / sec, "unit": UNIT, "cores": cores, "kind": "port",
+        hnd_cc, sec_cc = cpu_reference_arm(args.cpu_frames, cores, with_crop_cameras=True)
+        cpu_baseline = {"value": hnd / sec, "value_with_crop_cameras": hnd_cc / sec_cc, "unit": UNIT, "cores": cores, "kind": "port",
                         "sample": f"{args.cpu_frames} consecutive 2-hand frames of the same stream, frame by frame "
-                                  f"(numpy fp64 warp + fixed-point remap, torch-CPU fp32 network with {cores} threads, numpy FK)"}
+                                  f"(numpy fp64 warp + fixed-point remap, torch-CPU fp32 network with {cores} threads, numpy FK); "
+                                  "value_with_crop_cameras adds the reference's per-frame gen_crop_cameras (the baseline of e2e_from_poses)"}
 
     if rank == 0:
         print(json.dumps({
@@ -419,7 +433,10 @@ def main():
             "gpu_launches": int(launches),
             "roofline": {"bound": "tensor", "kernel": "per-view encoder (all conv launches of at_encoder_forward)",
                          "achieved": enc_tflops, "peak": tf_peak, "unit": "TFLOP/s", "frac": enc_tflops / tf_peak,
-                         "traffic": None, "peak_source": peaks["src"] + " cuBLAS bf16 burst (MEASURED_PEAKS.json bf16_tflops)",
+                         "traffic": ENCODER_DRAM_BYTES_PER_CROP * c,
+                         "traffic_source": "bytes per encoder pass (all conv launches), scaled per crop from the ncu --set full "
+                                           "capture in profiles/r1_conv_tc_ncu_full_summary.csv",
+                         "peak_source": peaks["src"] + " cuBLAS bf16 burst (MEASURED_PEAKS.json bf16_tflops)",
                          "frac_of_sustained_peak": enc_tflops / peaks["tf_sust"],
                          "launches_per_step": enc_launches // max(1, args.steps)},
             "stages": {"crop_ms": ms_crop, "encoder_ms": ms_enc, "tail_ms": ms_tail, "fk_ms": ms_fk,

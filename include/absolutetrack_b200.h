@@ -304,9 +304,11 @@ int at_tail_forward(const float* blob, const AtTailInputs* in, AtTemporalState* 
 /* Same arithmetic contract (fp32-grade: every product carries 22 significant bits), twice the
  * tensor throughput: the 11 convolutions of the tail run as error-compensated fp16 x 3 GEMMs
  * (x = hi + lo in fp16; hi*hi + lo*hi + hi*lo accumulated in fp32, mma.m16n8k16) instead of
- * TF32 x 3.  f16_blob = at_tail_f16_blob_bytes() bytes filled once per weight blob by
- * at_tail_prepack_f16 (pre-split, pre-transposed weights); NULL selects the TF32 x 3 kernels,
- * i.e. at_tail_forward. */
+ * TF32 x 3.  The four 3x3 convolutions of the pose head (2/3 of the tail's FLOPs) run the same
+ * three-product scheme as tcgen05 shift-GEMMs over [hi | lo | hi] activation planes and
+ * [hi | hi | lo] weight planes (fp32 accumulation in TMEM).  f16_blob = at_tail_f16_blob_bytes()
+ * bytes filled once per weight blob by at_tail_prepack_f16 (pre-split, pre-transposed weights for
+ * both kernels); NULL selects the TF32 x 3 kernels, i.e. at_tail_forward. */
 int64_t at_tail_f16_blob_bytes(void);
 int at_tail_prepack_f16(const float* blob, void* f16_blob, void* stream);
 int at_tail_forward_f16(const float* blob, const void* f16_blob, const AtTailInputs* in,

@@ -63,6 +63,13 @@ struct ConvTcParams {
   uint4* out_ph[4];
   long long out_ph_plane_px;
   float* out_f32;
+  // folded 1x1 stride-2 shortcut (first block of layers 2-4): sc_nk extra K chunks read phase image
+  // (0,0) of the block input at shift 0 and accumulate W_sc x into the same accumulator
+  const uint4* sc_src;
+  long long sc_plane_px;
+  const float* bias2;     // second bias added to `bias` (the shortcut's BN shift)
+  int sc_nk, sc_planes, sc_ksteps;
+  uint32_t sc_a_bytes, sc_w_bytes;
   const float* res_f32;   // MODE 4: optional fp32 NHWC residual (channel stride f32_ld)
   float out_scale;        // MODE 4: accumulator scale (undoes the 2^8 pre-scale of the split weights)
   int split_planes;       // MODE 4: channel groups per part of the [hi | lo | hi] split output
@@ -137,7 +144,8 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
     tmem_alloc(tmem_slot, p.tmem_cols);
     tmem_relinquish();
   }
-  for (int i = threadIdx.x; i < p.n; i += kThreads) bias_s[i] = i < p.cout ? p.bias[i] : 0.f;
+  for (int i = threadIdx.x; i < p.n; i += kThreads)
+    bias_s[i] = i < p.cout ? p.bias[i] + (p.bias2 != nullptr ? p.bias2[i] : 0.f) : 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -156,22 +164,24 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
   if (warp == 0) {
     if (lane == 0) {  // ---------------- weight producer
       const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(p.w);
-      const int nblocks = nk * NTAPS;
+      const int nmain = nk * NTAPS;
+      const int nblocks = nmain + p.sc_nk;  // the shortcut blocks follow the main ones at the same stride
       if (WRES) {
         if (n_my > 0)
           for (int b = 0; b < nblocks; ++b) {
-            mbar_expect_tx(w_full + 8 * b, p.w_block_bytes);
-            bulk_g2s(sbase + p.smem_w_off + b * p.w_block_bytes, wsrc + (size_t)b * p.w_block_bytes, p.w_block_bytes,
-                     w_full + 8 * b);
+            const uint32_t bytes = b < nmain ? p.w_block_bytes : p.sc_w_bytes;
+            mbar_expect_tx(w_full + 8 * b, bytes);
+            bulk_g2s(sbase + p.smem_w_off + b * p.w_block_bytes, wsrc + (size_t)b * p.w_block_bytes, bytes, w_full + 8 * b);
           }
       } else {
         Ring r;
         for (int it = 0; it < n_my; ++it)
           for (int b = 0; b < nblocks; ++b) {
+            const uint32_t bytes = b < nmain ? p.w_block_bytes : p.sc_w_bytes;
             mbar_wait(w_empty + 8 * r.slot, r.phase ^ 1u);
-            mbar_expect_tx(w_full + 8 * r.slot, p.w_block_bytes);
-            bulk_g2s(sbase + p.smem_w_off + r.slot * p.w_block_bytes, wsrc + (size_t)b * p.w_block_bytes,
-                     p.w_block_bytes, w_full + 8 * r.slot);
+            mbar_expect_tx(w_full + 8 * r.slot, bytes);
+            bulk_g2s(sbase + p.smem_w_off + r.slot * p.w_block_bytes, wsrc + (size_t)b * p.w_block_bytes, bytes,
+                     w_full + 8 * r.slot);
             r.advance(p.ws);
           }
       }
@@ -261,6 +271,39 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
         }
         ra.advance(p.ra);
       }
+      // folded shortcut: one tap at shift 0 over the chunks of the block input's phase image (0,0)
+      for (int sc = 0; sc < p.sc_nk; ++sc) {
+        mbar_wait(a_full + 8 * ra.slot, ra.phase);
+        tc_fence_after();
+        const uint32_t a_lo = a_lo0 + ra.slot * a_slot16 + (uint32_t)(-p.min_shift);
+        uint32_t b_lo;
+        if (WRES) {
+          if (it == 0) {
+            mbar_wait(w_full + 8 * (nk * NTAPS + sc), 0);
+            tc_fence_after();
+          }
+          b_lo = b_lo0 + (nk * NTAPS + sc) * w_blk16;
+        } else {
+          mbar_wait(w_full + 8 * rw.slot, rw.phase);
+          tc_fence_after();
+          b_lo = b_lo0 + rw.slot * w_blk16;
+        }
+        if (elect_one()) {
+          for (int j = 0; j < p.sc_ksteps; ++j) {
+            const uint64_t bd = ((uint64_t)desc_hi << 32) | (b_lo + j * b_kstep16);
+#pragma unroll
+            for (int m = 0; m < MT; ++m) {
+              const uint64_t ad = ((uint64_t)desc_hi << 32) | (a_lo + j * a_kstep16 + m * kTileM);
+              umma_f16(d_base + m * p.n, ad, bd, idesc, 1u);
+            }
+          }
+          if (!WRES) umma_commit(w_empty + 8 * rw.slot);
+          umma_commit(a_empty + 8 * ra.slot);
+        }
+        __syncwarp();
+        if (!WRES) rw.advance(p.ws);
+        ra.advance(p.ra);
+      }
       if (elect_one()) umma_commit(acc_full + 8 * rc.slot);
       __syncwarp();
       rc.advance(p.as);
@@ -286,6 +329,15 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
             for (int pl = 0; pl < kPlanesPerChunk; ++pl, dst += p.a_plane_bytes, src += p.a_plane_px)
               bulk_g2s(dst, src, p.a_plane_bytes, a_full + 8 * ra.slot);
           }
+          ra.advance(p.ra);
+        }
+        for (int sc = 0; sc < p.sc_nk; ++sc) {
+          mbar_wait(a_empty + 8 * ra.slot, ra.phase ^ 1u);
+          mbar_expect_tx(a_full + 8 * ra.slot, p.sc_a_bytes);
+          uint32_t dst = sbase + p.smem_a_off + ra.slot * p.a_slot_bytes;
+          const uint4* src = p.sc_src + ((long long)(sc * p.sc_planes) * p.sc_plane_px + g0);
+          for (int pl = 0; pl < p.sc_planes; ++pl, dst += p.a_plane_bytes, src += p.sc_plane_px)
+            bulk_g2s(dst, src, p.a_plane_bytes, a_full + 8 * ra.slot);
           ra.advance(p.ra);
         }
       }
@@ -558,6 +610,9 @@ TcLayer g_tc[L_COUNT];
 int64_t g_tc_bytes = 0;
 std::once_flag g_tc_once;
 
+// conv2 of the first block of layers 2-4: the 1x1 stride-2 shortcut (the next table row) can be folded in
+bool is_fold_host(int i) { return i == L_LAYER2 + 1 || i == L_LAYER3 + 1 || i == L_LAYER4 + 1; }
+
 void build_tc_table() {
   const ConvLayer* T = layer_table();
   int64_t off = 0;
@@ -575,6 +630,7 @@ void build_tc_table() {
     g_tc[i].nk = T[i].cin / g_tc[i].kc;
     g_tc[i].offset = off;
     off += (int64_t)T[i].ksize * T[i].ksize * T[i].cin * g_tc[i].n_pad * 2;
+    if (is_fold_host(i)) off += (int64_t)T[i + 1].cin * g_tc[i].n_pad * 2;  // copy of the shortcut's blocks (layer i + 1)
     off = round_up(off, 128);
   }
   g_tc_bytes = off + 128;
@@ -782,6 +838,9 @@ struct ConvIo {
   const float* res_f32;      // out_mode 3
   float out_scale;
   int split_planes, f32_ld;
+  int sc_layer;              // > 0: fold this 1x1 stride-2 shortcut layer into the accumulator ...
+  const uint4* sc_src;       // ... reading phase image (0,0) of the block input (plane 0 / pixel 0)
+  long long sc_plane_px;
 };
 
 // A convolution that is not a row of the backbone layer table (the pose-head convs of the tail).
@@ -891,7 +950,19 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   if (mt > 2) mt = 2;
   if (taps == 1) mt = 1;
   while (mt > 1 && round_up(mt * p.n, 32) > 256) mt >>= 1;  // keep >= 2 accumulator stages
-  const int nblocks = p.n_kchunks * taps;
+  if (io.sc_layer > 0) {
+    const ConvLayer& S = layer_table()[io.sc_layer];
+    const int kc_sc = S.cin < 64 ? S.cin : 64;
+    if (desc != nullptr || S.ksize != 1 || S.cout != L.cout || kc_sc > p.kc || (S.cin / kc_sc > 1 && kc_sc != p.kc)) {
+      set_error("conv_tc: cannot fold shortcut layer %s into %s", S.name, L.name);
+      return AT_ERR_UNSUPPORTED;
+    }
+    p.sc_nk = S.cin / kc_sc; p.sc_planes = kc_sc / 8; p.sc_ksteps = kc_sc / 16;
+    p.sc_src = io.sc_src; p.sc_plane_px = io.sc_plane_px;
+    p.bias2 = blob + S.bias_offset;
+    p.sc_w_bytes = (uint32_t)(kc_sc * p.n * 2);
+  }
+  const int nblocks = p.n_kchunks * taps + p.sc_nk;
   const int64_t misc = 4096;
   int64_t w_bytes = 0, ra = 0;
   for (;; mt >>= 1) {
@@ -900,6 +971,7 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
     p.a_plane_bytes = (uint32_t)p.npix * 16u;
     p.a_slot_bytes = (uint32_t)(is_stem ? 1 : p.n_src * (p.kc / 8)) * p.a_plane_bytes;
     p.w_block_bytes = (uint32_t)(p.kc * p.n * 2);
+    p.sc_a_bytes = (uint32_t)p.sc_planes * p.a_plane_bytes;
     p.w_resident = (int64_t)nblocks * p.w_block_bytes <= 100 * 1024;
     p.ws = p.w_resident ? nblocks : 4;
     while (!p.w_resident && p.ws > 2 && (int64_t)p.ws * p.w_block_bytes > 128 * 1024) --p.ws;
@@ -1102,6 +1174,9 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
       if ((rc = launch_conv_tc(L_STEM, blob, tc_blob, L0, nullptr, io, fmt, s))) return rc;
     }
     const int nblocks[4] = {2, 3, 5, 2};
+    // fold the 1x1 stride-2 shortcut of the first block of layers 2-4 into that block's conv2
+    // (3 launches, their output writes and the residual reads go away); AT_TC_FOLD=0 keeps them apart
+    static const bool fold = getenv("AT_TC_FOLD") == nullptr || atoi(getenv("AT_TC_FOLD")) != 0;
     int id = L_LAYER1;
     int cur = 0;  // index (0 = X, 2 = Y) of the buffer holding the current activation of the level
     for (int l = 0; l < 4; ++l) {
@@ -1119,9 +1194,13 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
           io.a_base = src; io.a_plane_px = phl[l - 1].plane_px; io.a_phase_units = P.ps_units[l - 1];
           io.out = Tm; io.out_plane_px = LV.plane_px; io.out_mode = 0; io.relu = true;
           if ((rc = launch_conv_tc(id, blob, tc_blob, LV, nullptr, io, fmt, s))) return rc;
-          io.out = buf(l, 3); io.relu = false;
-          if ((rc = launch_conv_tc(id + 2, blob, tc_blob, LV, nullptr, io, fmt, s))) return rc;
-          resid = buf(l, 3);
+          if (fold) {
+            resid = nullptr;  // the shortcut conv is accumulated inside conv2 (below)
+          } else {
+            io.out = buf(l, 3); io.relu = false;
+            if ((rc = launch_conv_tc(id + 2, blob, tc_blob, LV, nullptr, io, fmt, s))) return rc;
+            resid = buf(l, 3);
+          }
           cur = 2;  // so that the block output goes to X
         } else {
           io.a_base = buf(l, cur); io.a_plane_px = LV.plane_px;
@@ -1132,6 +1211,11 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
         memset(&io, 0, sizeof(io));
         io.a_base = Tm; io.a_plane_px = LV.plane_px;
         io.res = resid; io.res_plane_px = LV.plane_px; io.relu = true;
+        if (first && fold) {
+          io.sc_layer = id + 2;
+          io.sc_src = ws + P.off_ps[l - 1] + phl[l - 1].guard;  // phase (0,0) of the previous level's output
+          io.sc_plane_px = phl[l - 1].plane_px;
+        }
         if (last) {
           io.out = ws + P.off_ps[l] + phl[l].guard; io.out_plane_px = phl[l].plane_px; io.out_phase_units = P.ps_units[l];
           io.out_mode = 1;
@@ -1303,6 +1387,15 @@ extern "C" int at_model_prepack_tc(const float* blob, void* tc_blob, int precisi
         T[i].cin, T[i].cout, (int)round_up(T[i].cout, 4), TT[i].n_pad, TT[i].kc, precision == AT_PREC_BF16 ? 1 : 0);
     int rc = check_launch("prepack_kernel");
     if (rc) return rc;
+    if (tc::is_fold_host(i)) {  // second copy of the block's 1x1 shortcut weights, behind conv2's own blocks
+      const ConvLayer& S = T[i + 1];
+      const int64_t main_bytes = (int64_t)taps * T[i].cin * TT[i].n_pad * 2;
+      const long long tot = (long long)S.cin * TT[i].n_pad;
+      tc::prepack_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+          blob + S.weight_offset, reinterpret_cast<uint16_t*>(reinterpret_cast<uint8_t*>(tc_blob) + TT[i].offset + main_bytes), 1,
+          S.cin, S.cout, (int)round_up(S.cout, 4), TT[i].n_pad, S.cin < 64 ? S.cin : 64, precision == AT_PREC_BF16 ? 1 : 0);
+      if ((rc = check_launch("prepack_kernel"))) return rc;
+    }
   }
   return AT_OK;
 }

@@ -33,9 +33,9 @@ ENCODER_FLOP_PER_CROP = 969_228_288           # SURVEY.md 8(d), counted on the r
 TAIL_FLOP_PER_HAND = 19_150_000
 FK_BYTES_PER_HAND = 404                        # shared hand model
 CROP_SRC_BYTES = 32_160                        # mean source bounding box per crop
-# dram__bytes_read.sum + dram__bytes_write.sum over the conv launches of ONE encoder pass, per crop: 8,387 MB for 2048
+# dram__bytes_read.sum + dram__bytes_write.sum over the 26 conv launches of ONE encoder pass, per crop: 7,939 MB for 2048
 # crops in the ncu --set full capture profiles/r1_conv_tc_ncu_full_summary.csv (= the activations read + written once)
-ENCODER_DRAM_BYTES_PER_CROP = 8_387_313_920 / 2048
+ENCODER_DRAM_BYTES_PER_CROP = 7_938_569_984 / 2048
 
 
 def load_peaks():

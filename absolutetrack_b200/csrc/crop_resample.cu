@@ -424,6 +424,260 @@ crop_resample_staged_kernel(const uint8_t* __restrict__ src, int64_t frame_strid
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Lattice-map resampler (default for AT_MAP_FP32 at the model's crop size): the staged kernel with
+// the per-pixel map replaced by a bicubic interpolation of the map itself.
+//  1. the fast fp32 map is evaluated only on a 4-pixel lattice ((W/4+3) x (H/4+3) points, one ring
+//     outside the crop) and stored pre-multiplied by 32 (the fixed-point scale of cv2.remap);
+//  2. the source box is bounded by the lattice points covering the crop and staged through shared
+//     memory exactly like the staged kernel (device or PINNED HOST source);
+//  3. a thread walks 12-pixel row segments: 6 lattice columns are interpolated down to its row
+//     (4-point Lagrange in y), then each pixel is a 4-point Lagrange blend in x - weights are
+//     compile-time constants - followed by the fixed-point bilinear gather from shared memory.
+// The pinhole->Fisheye62 map is smooth on the scale of the focal length: measured on the
+// recording's geometry the interpolation error at a 4-pixel lattice is 1.6e-4 px, the same class as
+// the fp32 map's own 1.2e-4 px.  ~20 instead of ~70 instructions per pixel for the
+// map.  Crops that look behind the camera keep the exact per-pixel map; boxes that do not fit the
+// staging buffer gather from global memory.
+constexpr int kLatStep = 4;
+constexpr int kLatMaxDim = 96 / kLatStep + 3;   // 27
+constexpr int kLatPitch = kLatMaxDim + 1;        // 28
+constexpr int kLatSeg = 12;                      // pixels per thread unit (3 lattice cells)
+constexpr int kLatStageBytes = 48 * 1024;        // 4 CTAs per SM
+constexpr float kLatMinFocal = 80.0f;            // narrower crops only (see the kernel)
+
+// Gather from the staged tile with pre-scaled coordinates (32 * w): rint -> 1/32-px fixed point.
+// The tile is stored with one pitch + 16 bytes of padding in front and one pitch behind, so the
+// address of tap (ix, iy) may be formed without per-coordinate clamps: taps outside the image get
+// zero weight (cv2's constant-0 border) and whatever byte their address holds is irrelevant; one
+// clamp of the linear address keeps every access inside the buffer.  koff = (1 - y0) * pitch - x0a + 16.
+__device__ __forceinline__ int remap_fixed_u8_smem_s(const uint8_t* __restrict__ tile, int pitch, int koff, int amax, int W,
+                                                     int H, float sxf, float syf) {
+  const int sx = __float2int_rn(sxf);
+  const int sy = __float2int_rn(syf);
+  const int ix = sx >> 5, iy = sy >> 5;
+  const int fx = sx & 31, fy = sy & 31;
+  const int wx1 = (unsigned)(ix + 1) < (unsigned)W ? fx : 0, wx0 = (unsigned)ix < (unsigned)W ? 32 - fx : 0;
+  const int wy1 = (unsigned)(iy + 1) < (unsigned)H ? fy : 0, wy0 = (unsigned)iy < (unsigned)H ? 32 - fy : 0;
+  const int a = min(max(iy * pitch + ix + koff, 0), amax);
+  const uint8_t* t0 = tile + a;
+  const uint8_t* t1 = t0 + pitch;
+  const int acc = wy0 * (wx0 * t0[0] + wx1 * t0[1]) + wy1 * (wx0 * t1[0] + wx1 * t1[1]);
+  return (acc + 512) >> 10;   // == ((acc * 32) + 16384) >> 15
+}
+
+__device__ __forceinline__ int remap_fixed_u8_s(const uint8_t* __restrict__ img, int64_t row_stride, int W, int H, float sxf,
+                                                float syf) {
+  const int sx = __float2int_rn(sxf);
+  const int sy = __float2int_rn(syf);
+  const int ix = min(max(sx >> 5, -32768), 32767);
+  const int iy = min(max(sy >> 5, -32768), 32767);
+  const int fx = sx & 31, fy = sy & 31;
+  const bool x0 = (unsigned)ix < (unsigned)W, x1 = (unsigned)(ix + 1) < (unsigned)W;
+  const bool y0 = (unsigned)iy < (unsigned)H, y1 = (unsigned)(iy + 1) < (unsigned)H;
+  const uint8_t* r0 = img + (int64_t)iy * row_stride + ix;
+  const uint8_t* r1 = r0 + row_stride;
+  const int t00 = (y0 && x0) ? __ldg(r0) : 0;
+  const int t01 = (y0 && x1) ? __ldg(r0 + 1) : 0;
+  const int t10 = (y1 && x0) ? __ldg(r1) : 0;
+  const int t11 = (y1 && x1) ? __ldg(r1 + 1) : 0;
+  const int acc = (32 - fy) * ((32 - fx) * t00 + fx * t01) + fy * ((32 - fx) * t10 + fx * t11);
+  return (acc + 512) >> 10;
+}
+
+// 4-point Lagrange weights for nodes (-1, 0, 1, 2) at t = k/4
+__device__ __forceinline__ float2 lag4(int k, const float2& a, const float2& b, const float2& c, const float2& d) {
+  float w0, w1, w2, w3;
+  if (k == 0) return b;
+  if (k == 1) { w0 = -0.0546875f; w1 = 0.8203125f; w2 = 0.2734375f; w3 = -0.0390625f; }
+  else if (k == 2) { w0 = -0.0625f; w1 = 0.5625f; w2 = 0.5625f; w3 = -0.0625f; }
+  else { w0 = -0.0390625f; w1 = 0.2734375f; w2 = 0.8203125f; w3 = -0.0546875f; }
+  return make_float2(fmaf(w0, a.x, fmaf(w1, b.x, fmaf(w2, c.x, w3 * d.x))), fmaf(w0, a.y, fmaf(w1, b.y, fmaf(w2, c.y, w3 * d.y))));
+}
+
+__global__ void __launch_bounds__(kThreads, 4)
+crop_resample_lattice_kernel(const uint8_t* __restrict__ src, int64_t frame_stride, int64_t view_stride, int64_t row_stride,
+                             const AtCropParams* __restrict__ params, int dst_w, int dst_h, void* __restrict__ out,
+                             int out_dtype, unsigned long long* __restrict__ staged_bytes) {
+  extern __shared__ __align__(16) uint8_t tile[];
+  __shared__ FastParams P;
+  __shared__ int s_meta[4];
+  __shared__ float s_red[kThreads / 32][4];
+  __shared__ int s_behind;
+  __shared__ int s_box[6];
+  __shared__ float2 s_lat[kLatMaxDim * kLatPitch];
+  const int crop = blockIdx.x;
+  const AtCropParams& g = params[crop];
+  if (threadIdx.x < 9) P.M[threadIdx.x] = (float)g.M[threadIdx.x];
+  if (threadIdx.x < 3) P.d[threadIdx.x] = (float)g.d[threadIdx.x];
+  if (threadIdx.x == 32) {
+    P.ifdx = 1.0f / (float)g.f_dst[0]; P.ifdy = 1.0f / (float)g.f_dst[1];
+    P.qx0 = -(float)g.c_dst[0] * P.ifdx; P.qy0 = -(float)g.c_dst[1] * P.ifdy;
+    P.fsx = (float)g.f_src[0]; P.fsy = (float)g.f_src[1]; P.csx = (float)g.c_src[0]; P.csy = (float)g.c_src[1];
+    P.k1 = (float)g.k[0]; P.k2 = (float)g.k[1]; P.k3 = (float)g.k[2]; P.k4 = (float)g.k[3];
+    P.p1 = (float)g.k[4]; P.p2 = (float)g.k[5]; P.k5 = (float)g.k[6]; P.k6 = (float)g.k[7];
+    s_meta[0] = g.frame; s_meta[1] = g.view; s_meta[2] = g.src_w; s_meta[3] = g.src_h;
+    // the interpolation error grows like (lattice step / focal length)^4: hand crops have f >= 90 px
+    // (1.6e-4 px); anything much wider keeps the exact per-pixel map, like crops that look behind the camera
+    s_behind = fminf((float)g.f_dst[0], (float)g.f_dst[1]) < kLatMinFocal ? 1 : 0;
+  }
+  __syncthreads();
+  const int W = s_meta[2], H = s_meta[3];
+  const uint8_t* img = src + (int64_t)s_meta[0] * frame_stride + (int64_t)s_meta[1] * view_stride;
+
+  // ---- 1. the map on the lattice (coordinates -4, 0, 4, ..., W + 4) and the source box of the crop
+  const int nlx = dst_w / kLatStep + 3, nly = dst_h / kLatStep + 3;
+  float mnx = 3.0e38f, mny = 3.0e38f, mxx = -3.0e38f, mxy = -3.0e38f;
+  for (int i = threadIdx.x; i < nlx * nly; i += kThreads) {
+    const int ly = i / nlx, lx = i - ly * nlx;
+    float wx, wy;
+    map_pixel_fast(P, fmaf((float)(kLatStep * (lx - 1)), P.ifdx, P.qx0), fmaf((float)(kLatStep * (ly - 1)), P.ifdy, P.qy0), wx, wy);
+    if (wx == -1.0f && wy == -1.0f) s_behind = 1;  // ez < 0 at a lattice point: the map is not smooth there
+    s_lat[ly * kLatPitch + lx] = make_float2(wx * 32.0f, wy * 32.0f);
+    if (lx >= 1 && lx <= nlx - 2 && ly >= 1 && ly <= nly - 2) {  // the points spanning [0, W] x [0, H]
+      mnx = fminf(mnx, wx); mxx = fmaxf(mxx, wx);
+      mny = fminf(mny, wy); mxy = fmaxf(mxy, wy);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    mnx = fminf(mnx, __shfl_xor_sync(0xffffffffu, mnx, o)); mxx = fmaxf(mxx, __shfl_xor_sync(0xffffffffu, mxx, o));
+    mny = fminf(mny, __shfl_xor_sync(0xffffffffu, mny, o)); mxy = fmaxf(mxy, __shfl_xor_sync(0xffffffffu, mxy, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    float* r = s_red[threadIdx.x >> 5];
+    r[0] = mnx; r[1] = mxx; r[2] = mny; r[3] = mxy;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < kThreads / 32; ++w) {
+      mnx = fminf(mnx, s_red[w][0]); mxx = fmaxf(mxx, s_red[w][1]);
+      mny = fminf(mny, s_red[w][2]); mxy = fmaxf(mxy, s_red[w][3]);
+    }
+    const float lim = 1.0e6f;
+    mnx = fminf(fmaxf(mnx, -lim), lim); mxx = fminf(fmaxf(mxx, -lim), lim);
+    mny = fminf(fmaxf(mny, -lim), lim); mxy = fminf(fmaxf(mxy, -lim), lim);
+    int x0 = max(0, (int)floorf(mnx) - 2), x1 = min(W - 1, (int)floorf(mxx) + 3);
+    int y0 = max(0, (int)floorf(mny) - 2), y1 = min(H - 1, (int)floorf(mxy) + 3);
+    int direct = 0;
+    int x0a = x0 & ~3, bw = 0, bh = 0;
+    if (x1 < x0 || y1 < y0) {
+      x0a = 0; y0 = 0; bw = 4; bh = 2;   // box outside the image: every tap is the constant border
+      x0 = 0;
+    } else {
+      bw = ((x1 + 1 - x0a) + 3) & ~3;
+      bh = y1 - y0 + 1;
+      if (bh < 2) { if (y0 > 0) --y0; bh = 2; }
+      if (bw < 4) bw = 4;
+    }
+    const bool aligned = ((W | (int)(view_stride & 3) | (int)(row_stride & 3) | (int)(frame_stride & 3)) & 3) == 0 &&
+                         (((uintptr_t)src) & 3) == 0;
+    int vec16 = 0;
+    if (aligned && (row_stride & 15) == 0 && (frame_stride & 15) == 0 && x1 >= x0 && y1 >= y0) {
+      const long long view_off = (long long)s_meta[1] * view_stride;
+      const int phase = (int)(((uintptr_t)src + (uintptr_t)view_off + (uintptr_t)x0a) & 15);
+      const int nx0 = x0a - phase;
+      const int nbw = ((x0a + bw - nx0) + 15) & ~15;
+      if (view_off + nx0 >= 0 && view_off + nx0 + nbw <= row_stride && (long long)nbw * (bh + 2) + 32 <= kLatStageBytes) {
+        x0a = nx0; bw = nbw; vec16 = 1;
+      }
+    }
+    if (!aligned || (long long)bw * (bh + 2) + 32 > kLatStageBytes || (!vec16 && x0a + bw > ((W + 3) & ~3)) || y0 + bh > H) direct = 1;
+    s_box[0] = x0a; s_box[1] = y0; s_box[2] = bw; s_box[3] = bh; s_box[4] = direct; s_box[5] = vec16;
+    if (staged_bytes != nullptr)
+      atomicAdd(staged_bytes, (direct || s_behind) ? (unsigned long long)(4ll * dst_w * dst_h) : (unsigned long long)((long long)bw * bh));
+  }
+  __syncthreads();
+  const int x0a = s_box[0], y0 = s_box[1], bw = s_box[2], bh = s_box[3];
+  const bool behind = s_behind != 0;
+  const bool direct = s_box[4] != 0 || behind;
+
+  // ---- 2. stage the box (data starts one pitch + 16 bytes into the buffer: see remap_fixed_u8_smem_s)
+  uint8_t* tdata = tile + bw + 16;
+  if (!direct && s_box[5]) {
+    const int wpr = bw >> 4;
+    const int total = wpr * bh;
+    uint4* t128 = reinterpret_cast<uint4*>(tdata);
+    for (int i = threadIdx.x; i < total; i += kThreads) {
+      const int r = i / wpr, c = i - r * wpr;
+      t128[i] = __ldg(reinterpret_cast<const uint4*>(img + (int64_t)(y0 + r) * row_stride + x0a) + c);
+    }
+  } else if (!direct) {
+    const int wpr = bw >> 2;
+    const int total = wpr * bh;
+    uint32_t* t32 = reinterpret_cast<uint32_t*>(tdata);
+    for (int i = threadIdx.x; i < total; i += kThreads) {
+      const int r = i / wpr, c = i - r * wpr;
+      const int yy = y0 + r;
+      uint32_t v = 0u;
+      if (yy < H) v = __ldg(reinterpret_cast<const uint32_t*>(img + (int64_t)yy * row_stride + x0a) + c);
+      t32[i] = v;
+    }
+  }
+  __syncthreads();
+
+  // ---- 3. interpolate the map and gather: units of 12 pixels in a row
+  const int segs = dst_w / kLatSeg;
+  const int nunits = segs * dst_h;
+  const int64_t obase = (int64_t)crop * dst_w * dst_h;
+  const int koff = (1 - y0) * bw - x0a + 16;       // tap address = iy * pitch + ix + koff (padded tile)
+  const int amax = (bh + 1) * bw + 16 - 2;          // last address whose 2x2 footprint is inside the buffer
+  for (int u = threadIdx.x; u < nunits; u += kThreads) {
+    const int y = segs == 8 ? u >> 3 : u / segs, seg = u - y * segs;   // 96-pixel rows: no division
+    const int xs = seg * kLatSeg;
+    int v[kLatSeg];
+    if (behind) {  // uniform per CTA
+      const float qy = fmaf((float)y, P.ifdy, P.qy0);
+#pragma unroll
+      for (int i = 0; i < kLatSeg; ++i) {
+        float wx, wy;
+        map_pixel_fast(P, fmaf((float)(xs + i), P.ifdx, P.qx0), qy, wx, wy);
+        v[i] = remap_fixed_u8_s(img, row_stride, W, H, wx * 32.0f, wy * 32.0f);
+      }
+    } else {
+      const int cy = y >> 2, ty = y & 3;
+      const float2* L = s_lat + cy * kLatPitch + 3 * seg;
+      float2 col[6];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) col[j] = lag4(ty, L[j], L[kLatPitch + j], L[2 * kLatPitch + j], L[3 * kLatPitch + j]);
+      if (!direct) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            const float2 m = lag4(t, col[c], col[c + 1], col[c + 2], col[c + 3]);
+            v[c * 4 + t] = remap_fixed_u8_smem_s(tile, bw, koff, amax, W, H, m.x, m.y);
+          }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            const float2 m = lag4(t, col[c], col[c + 1], col[c + 2], col[c + 3]);
+            v[c * 4 + t] = remap_fixed_u8_s(img, row_stride, W, H, m.x, m.y);
+          }
+      }
+    }
+    const int64_t o = obase + (int64_t)y * dst_w + xs;
+    if (out_dtype == AT_U8) {
+      uchar4* op = reinterpret_cast<uchar4*>((uint8_t*)out + o);
+#pragma unroll
+      for (int q = 0; q < 3; ++q)
+        op[q] = make_uchar4((uint8_t)v[4 * q], (uint8_t)v[4 * q + 1], (uint8_t)v[4 * q + 2], (uint8_t)v[4 * q + 3]);
+    } else if (out_dtype == AT_F32) {
+      float4* op = reinterpret_cast<float4*>((float*)out + o);
+#pragma unroll
+      for (int q = 0; q < 3; ++q)
+        op[q] = make_float4(__fdiv_rn((float)v[4 * q], 255.0f), __fdiv_rn((float)v[4 * q + 1], 255.0f),
+                            __fdiv_rn((float)v[4 * q + 2], 255.0f), __fdiv_rn((float)v[4 * q + 3], 255.0f));
+    } else {
+      __nv_bfloat16* ob = (__nv_bfloat16*)out + o;
+#pragma unroll
+      for (int i = 0; i < kLatSeg; ++i) ob[i] = __float2bfloat16_rn(__fdiv_rn((float)v[i], 255.0f));
+    }
+  }
+}
+
 // ---- source-box pull (host -> device ingest without copying whole frames) -------------------------
 // For every crop: bound the source region its map touches (boundary pixels of the crop, as in the
 // staged kernel), then copy just those rows/columns from `src` (pinned host memory, read over PCIe)
@@ -621,6 +875,17 @@ extern "C" int at_crop_resample_fisheye62_u8_ex(const uint8_t* src, int64_t fram
   if (map_mode == AT_MAP_FP64) {
     crop_resample_kernel<double><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
         src, frame_stride, view_stride, row_stride, params, dst_w, dst_h, out, out_dtype);
+  } else if (dst_w % kLatSeg == 0 && dst_h % kLatStep == 0 && dst_w <= 96 && dst_h <= 96 &&
+             (getenv("AT_CROP_LATTICE") == nullptr || atoi(getenv("AT_CROP_LATTICE")) != 0)) {
+    // the model's crop size: bicubic lattice map + staged gather, for device and pinned-host sources alike
+    static bool attr = false;
+    if (!attr) {
+      cudaFuncSetAttribute(crop_resample_lattice_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kLatStageBytes);
+      cudaFuncSetAttribute(crop_resample_lattice_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+      attr = true;
+    }
+    crop_resample_lattice_kernel<<<(unsigned)n_crops, kThreads, kLatStageBytes, (cudaStream_t)stream>>>(
+        src, frame_stride, view_stride, row_stride, params, dst_w, dst_h, out, out_dtype, staged_bytes);
   } else if (dst_w % kFastPx == 0 && (src_on_host || staged_bytes != nullptr || getenv("AT_CROP_STAGED") != nullptr)) {
     static bool attr = false;
     if (!attr) {

@@ -185,6 +185,27 @@ WORKLOAD = ("synthetic 4-view fisheye frame stream (4x 636x480 u8 per frame, rec
             "known-skeleton head (BASELINE.json configs[3])")
 
 
+def bind_to_gpu_numa_node(index):
+    """One process per GPU: run (and therefore allocate the pinned frame buffers) on the CPU cores next to
+    that GPU, so that the source-box pull crosses PCIe without also crossing the socket interconnect.
+    Returns a short description, or None when NVML / sched_setaffinity is unavailable."""
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        n = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (n + 63) // 64)
+        cpus = [64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1 and 64 * i + b < n]
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if not allowed:
+            return None
+        os.sched_setaffinity(0, allowed)
+        return f"{len(allowed)} cores near GPU {index} ({allowed[0]}-{allowed[-1]})"
+    except Exception:
+        return None
+
+
 # ------------------------------------------------------------------------------------ GPU arm
 def main():
     ap = argparse.ArgumentParser()
@@ -217,6 +238,11 @@ def main():
     import torch.distributed as dist
 
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback on the product arm)"
+    # stdout carries exactly ONE line (the JSON): libraries that print to fd 1 (NCCL's version banner) go to stderr
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+    numa = bind_to_gpu_numa_node(local_rank) if world > 1 else None
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
@@ -419,13 +445,16 @@ def main():
                                   "value_with_crop_cameras adds the reference's per-frame gen_crop_cameras (the baseline of e2e_from_poses)"}
 
     if rank == 0:
+        sys.stdout.flush()
+        os.dup2(json_fd, 1)
         print(json.dumps({
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": args.precision, "data": "synthetic",
             "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": S, "hand_frames_per_step_per_gpu": n,
                        "crops_per_step_per_gpu": c, "map_mode": args.map_mode, "l2": flush_note,
-                       "weights": "seeded random state dict (252 keys), BN folded", "sharding": "sequences r::world"},
+                       "weights": "seeded random state dict (252 keys), BN folded", "sharding": "sequences r::world",
+                       "host_numa_binding": numa},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "api": "BatchedHandTracker.step (pinned host buffers)", "ingest": ingest, "host_issue_ms_per_step": issue_ms,
                     "host_frame_bytes_per_step": int(host[0].frames.numel())},

@@ -315,7 +315,58 @@ __global__ void __launch_bounds__(kFast, 3) fk_skin_shared_kernel(const float* _
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Evaluation sums (run_eval_known_skeleton.py:92-93 / load_eval.py:26-44 bookkeeping): one warp per
+// hand, lanes = landmarks / joints; per-CTA partial sums, one fp64 atomic per CTA and quantity.
+constexpr int kEvalWarps = 8;
+__global__ void __launch_bounds__(kEvalWarps * 32)
+eval_accumulate_kernel(const float* __restrict__ lm, const float* __restrict__ gt, const float* __restrict__ ja,
+                       const float* __restrict__ gja, const uint8_t* __restrict__ valid, int64_t n, double* __restrict__ sums) {
+  __shared__ float s_part[kEvalWarps][3];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float e_sum = 0.f, a_sum = 0.f, cnt = 0.f;
+  for (int64_t h = (int64_t)blockIdx.x * kEvalWarps + warp; h < n; h += (int64_t)gridDim.x * kEvalWarps) {
+    if (valid != nullptr && valid[h] == 0) continue;
+    float d = 0.f, a = 0.f;
+    if (lane < 21) {
+      const float* p = lm + h * 63 + lane * 3;
+      const float* q = gt + h * 63 + lane * 3;
+      const float dx = p[0] - q[0], dy = p[1] - q[1], dz = p[2] - q[2];
+      d = sqrtf(dx * dx + dy * dy + dz * dz);
+    }
+    if (ja != nullptr && lane < 20) a = fabsf(ja[h * 22 + lane] - gja[h * 22 + lane]);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+      d += __shfl_xor_sync(0xffffffffu, d, o);
+      a += __shfl_xor_sync(0xffffffffu, a, o);
+    }
+    e_sum += d * (1.0f / 21.0f);
+    a_sum += a * (57.29577951308232f / 20.0f);
+    cnt += 1.0f;
+  }
+  if (lane == 0) { s_part[warp][0] = e_sum; s_part[warp][1] = a_sum; s_part[warp][2] = cnt; }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    double t = 0.0;
+    for (int w = 0; w < kEvalWarps; ++w) t += (double)s_part[w][threadIdx.x];
+    if (t != 0.0) atomicAdd(sums + threadIdx.x, t);
+  }
+}
+
 }  // namespace
+
+extern "C" int at_eval_accumulate_f32(const float* landmarks, const float* gt_landmarks, const float* joint_angles,
+                                      const float* gt_joint_angles, const uint8_t* valid, int64_t n, double* sums,
+                                      void* stream) {
+  AT_REQUIRE(n >= 0, "at_eval_accumulate_f32: n < 0");
+  if (n == 0) return AT_OK;
+  AT_REQUIRE(landmarks && gt_landmarks && sums, "at_eval_accumulate_f32: NULL pointer");
+  AT_REQUIRE((joint_angles == nullptr) == (gt_joint_angles == nullptr), "at_eval_accumulate_f32: give both joint-angle arrays or none");
+  const int64_t blocks = std::min<int64_t>((n + kEvalWarps - 1) / kEvalWarps, 4 * at::kNumSMs);
+  eval_accumulate_kernel<<<(unsigned)blocks, kEvalWarps * 32, 0, (cudaStream_t)stream>>>(landmarks, gt_landmarks, joint_angles,
+                                                                                        gt_joint_angles, valid, n, sums);
+  return at::check_launch("eval_accumulate_kernel");
+}
 
 extern "C" int at_fk_skin_f32(const float* joint_angles, const float* wrist_xforms, const int64_t* hand_idx,
                               const AtHandModel* model, int64_t n, float* landmarks, void* stream) {

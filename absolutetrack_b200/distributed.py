@@ -41,3 +41,26 @@ def mpjpe_accumulate(sums: torch.Tensor, tracked: torch.Tensor, gt: torch.Tensor
     v = valid.to(d.dtype)
     sums[0] += (d * v).sum()
     sums[1] += v.sum()
+
+
+def accumulate_metric_sums_cuda(landmarks, gt_landmarks, sums, valid=None, joint_angles=None, gt_joint_angles=None):
+    """sums (float64 [3], CUDA) += {sum of per-hand mean keypoint error, sum of per-hand mean |dtheta| in
+    degrees, number of valid hands} of one batch, in ONE launch of csrc/fk_skin.cu::eval_accumulate_kernel
+    (C-ABI at_eval_accumulate_f32; the bookkeeping of run_eval_known_skeleton.py:92-93 on the device).
+    Feed the result to all_reduce_metric_sums at the end of a sharded run."""
+    import torch
+
+    from . import _cabi
+
+    lib = _cabi.lib()
+    n = int(landmarks.shape[0])
+    if not (sums.is_cuda and sums.dtype == torch.float64 and sums.numel() >= 3):
+        raise TypeError("sums must be a CUDA float64 tensor with >= 3 elements")
+    f = lambda t: None if t is None else t.to(device=sums.device, dtype=torch.float32).contiguous()  # noqa: E731
+    lm, gt, ja, gja = f(landmarks), f(gt_landmarks), f(joint_angles), f(gt_joint_angles)
+    v = None if valid is None else valid.to(device=sums.device, dtype=torch.uint8).contiguous()
+    with torch.cuda.device(sums.device):
+        rc = lib.at_eval_accumulate_f32(lm.data_ptr(), gt.data_ptr(), _cabi.ptr(ja), _cabi.ptr(gja), _cabi.ptr(v), n,
+                                        sums.data_ptr(), _cabi.stream_ptr(sums.device))
+    _cabi.check(rc, "at_eval_accumulate_f32")
+    return sums

@@ -158,8 +158,11 @@ class BatchedHandTracker:
             InputFrameDesc(b.sample_range, b.memory_idx, b.use_memory, b.hand_idx),
             self._skel,
         )
-        wrist_mm = out.wrist_xfs.clone()
-        wrist_mm[:, :3, 3] *= M_TO_MM
+        if getattr(self, "_mm_scale", None) is None:  # metres -> millimetres on the translation column, one launch
+            sc = torch.ones(4, 4, device=self._device)
+            sc[:3, 3] = M_TO_MM
+            self._mm_scale = sc
+        wrist_mm = out.wrist_xfs * self._mm_scale
         # the model already mirrored right hands (umetrack_model.py:88-89); landmarks_from_hand_pose
         # mirrors them back before FK (perspective_crop.py:46-48) -> hand_idx does that in-kernel
         lm = skin_landmarks_cuda(self._hm_dev, out.joint_angles, wrist_mm, hand_idx=b.hand_idx)

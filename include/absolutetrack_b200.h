@@ -133,6 +133,18 @@ typedef struct AtHandModel {
 int at_fk_skin_f32(const float* joint_angles, const float* wrist_xforms, const int64_t* hand_idx,
                    const AtHandModel* model, int64_t n, float* landmarks, void* stream);
 
+/* Evaluation sums on the device.  Replaces the per-frame bookkeeping of
+ * run_eval_known_skeleton.py:92-93 (mean keypoint error of a hand-frame) for a batch:
+ *   sums[0] += sum over valid hands of mean_l |landmarks[h,l] - gt_landmarks[h,l]|   (input units, mm)
+ *   sums[1] += sum over valid hands of mean_j |joint_angles[h,j] - gt_joint_angles[h,j]| in degrees, j < 20
+ *              (skipped when both joint-angle pointers are NULL)
+ *   sums[2] += number of valid hands
+ * landmarks [n,21,3], joint_angles [n,22], valid [n] (NULL = all), sums: 3 float64 accumulators on the
+ * device - the per-shard numbers that the only collective of the path all-reduces. */
+int at_eval_accumulate_f32(const float* landmarks, const float* gt_landmarks, const float* joint_angles,
+                           const float* gt_joint_angles, const uint8_t* valid, int64_t n, double* sums,
+                           void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * (5) Crop-camera generation + model-input assembly on the device.  Replaces
  * HandTracker.gen_crop_cameras (lib/tracker/tracker.py:222-260) with everything below it -

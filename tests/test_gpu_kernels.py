@@ -271,3 +271,26 @@ def test_homography_resampler_matches_oracle(cuda_lib):
     _cabi.check(rc)
     assert np.abs(out.cpu().numpy() - ref).max() <= 1e-6
     assert (ref != 0).mean() > 0.5
+
+
+# ------------------------------------------------------------------ evaluation sums
+def test_eval_sums_match_oracle_mpjpe(cuda_lib):
+    from absolutetrack_b200.distributed import accumulate_metric_sums_cuda
+
+    g = torch.Generator().manual_seed(5)
+    n = 3000
+    lm = torch.randn(n, 21, 3, generator=g) * 50
+    gt = lm + torch.randn(n, 21, 3, generator=g)
+    ja = torch.randn(n, 22, generator=g)
+    gja = ja + 0.01 * torch.randn(n, 22, generator=g)
+    valid = torch.rand(n, generator=g) > 0.2
+    sums = torch.zeros(3, dtype=torch.float64, device="cuda")
+    for lo, hi in ((0, 1000), (1000, n)):   # accumulates across calls
+        accumulate_metric_sums_cuda(lm[lo:hi].cuda(), gt[lo:hi].cuda(), sums, valid[lo:hi].cuda(), ja[lo:hi].cuda(), gja[lo:hi].cuda())
+    s = sums.cpu().numpy()
+    assert s[2] == int(valid.sum())
+    assert abs(s[0] / s[2] - O.mpjpe(lm.numpy(), gt.numpy(), valid.numpy())) < 1e-4
+    dth = np.degrees(np.abs(ja.numpy()[:, :20] - gja.numpy()[:, :20])).mean(-1)[valid.numpy()].mean()
+    assert abs(s[1] / s[2] - dth) < 1e-4
+    accumulate_metric_sums_cuda(lm[:0].cuda(), gt[:0].cuda(), sums)   # empty batch
+    assert sums.cpu().numpy()[2] == s[2]

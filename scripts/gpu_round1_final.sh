@@ -17,7 +17,7 @@ timeout 900 ncu --set full --clock-control none -k regex:conv_tc -s 78 -c 26 -o 
 echo "full rc=$?"; cat gpurun_out/tc_time.log
 ncu -i /tmp/tc_full.ncu-rep --page raw --csv > gpurun_out/tc_full_raw.csv 2>/dev/null
 # the other kernels of one step: resampler, crop-camera generator, tail (incl. the tcgen05 head convs), FK
-timeout 900 ncu --set full --clock-control none -k regex:"crop_resample_fast|crop_cameras_|conv_nhwc_f16x3|conv_tc_kernel<9, 5|head_split|fk_skin_shared|tail_prepare|post_fusion|split_kernel|decode_kernel" -s 40 -c 24 -o /tmp/step_other_full -f $CMD > gpurun_out/ncu_other.log 2>&1
+timeout 900 ncu --set full --clock-control none -k regex:"crop_resample_lattice|crop_cameras_|eval_accumulate|conv_nhwc_f16x3|conv_tc_kernel<9, 5|head_split|fk_skin_shared|tail_prepare|post_fusion|split_kernel|decode_kernel" -s 40 -c 24 -o /tmp/step_other_full -f $CMD > gpurun_out/ncu_other.log 2>&1
 echo "other rc=$?"
 ncu -i /tmp/step_other_full.ncu-rep --page raw --csv > gpurun_out/step_other_raw.csv 2>/dev/null
 ls -la gpurun_out/

@@ -330,3 +330,26 @@ def test_shard_indices_validate_rank():
     assert D.shard(["a", "b", "c"], 0, 2) == ["a", "c"]
     with pytest.raises(TypeError):
         D.all_reduce_metric_sums(torch.zeros(2))
+
+
+def test_ctypes_structs_match_the_c_header(tmp_path):
+    """include/absolutetrack_b200.h compiled as plain C (gcc): every struct the Python binding mirrors has the
+    same size there as in ctypes, so by-value / by-pointer arguments cannot silently drift apart."""
+    import shutil
+    import subprocess
+
+    from absolutetrack_b200 import _cabi
+
+    gcc = shutil.which("gcc")
+    if gcc is None:
+        pytest.skip("no gcc")
+    names = ["AtCropParams", "AtHandModel", "AtLayerInfo", "AtTemporalState", "AtTailInputs", "AtTailOutputs",
+             "AtRigCamera", "AtCropCameraOpts", "AtCropCameraInputs", "AtCropCameraOutputs"]
+    src = tmp_path / "sizes.c"
+    src.write_text('#include <stdio.h>\n#include "absolutetrack_b200.h"\nint main(void){\n'
+                   + "".join(f'printf("{n} %zu\\n", sizeof({n}));\n' for n in names) + "return 0;}\n")
+    exe = tmp_path / "sizes"
+    subprocess.check_call([gcc, "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    out = dict(line.split() for line in subprocess.check_output([str(exe)], text=True).splitlines())
+    for n in names:
+        assert int(out[n]) == ctypes.sizeof(getattr(_cabi, n)), n

@@ -186,12 +186,15 @@ def test_hand_tracker_track_frame_matches_reference_golden(model, gold):
     assert res.hand_poses == {} and not tracker._valid_tracking_history.any()
 
 
-def test_gen_crop_cameras_matches_reference_golden(model, gold):
+@pytest.mark.parametrize("mode", ["device", "host"])
+def test_gen_crop_cameras_matches_reference_golden(model, gold, mode):
+    """HandTracker.gen_crop_cameras (tracker.py:222-260) through the device kernel (default) and through the
+    numpy mirror of perspective_crop.py / crop.py, against the reference's own crop cameras."""
     from absolutetrack_b200.lib.tracker.tracker import HandTracker, HandTrackerOpts
     from absolutetrack_b200.lib.tracker.tracking_result import SingleHandPose
 
     G = gold["geometry"]
-    tracker = HandTracker(model, HandTrackerOpts())
+    tracker = HandTracker(model, HandTrackerOpts(crop_cameras=mode))
     for k in range(0, G["crop_cam"].shape[0], 7):
         frame, _, hm = _tracker_objects(k)
         gt = {h: SingleHandPose(G["joint_angles"][k, h], G["wrist_transforms"][k, h], G["hand_confidences"][k, h])

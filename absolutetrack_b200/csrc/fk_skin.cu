@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(kBlock) fk_skin_kernel(const float* __restrict
     }
     store_frame(smem, 0, W);
     store_frame(smem, 1, W);
-#pragma unroll 1
+#pragma unroll 1  // (fully unrolled: 0.414 instead of 0.439 of HBM at 4M hands - instruction cache)
     for (int f = 0; f < 5; ++f) {
       Xf cur = W;
 #pragma unroll
@@ -122,11 +122,13 @@ __global__ void __launch_bounds__(kBlock) fk_skin_kernel(const float* __restrict
 // (identical to so3_exp_map(axis*angle) of hand_skinning.py:46).  The 17 frames never leave
 // registers: landmarks are visited frame by frame through a CSR table built once per CTA
 // (bone index -> landmarks) and accumulated in shared memory, which doubles as the staging buffer
-// for coalesced input loads and output stores.  252 B of shared memory per hand -> 3 CTAs x 256
+// for 16-byte input loads and output stores.  252 B of shared memory per hand -> 3 CTAs x 256
 // threads per SM.
-constexpr int kFast = 256;             // hands per CTA
-constexpr int kOutLd = kFast + 1;      // conflict-free both for per-thread rows and the transposed copy
-constexpr int kJaLd = 23, kWxLd = 17;  // padded input rows
+constexpr int kFast = 256;  // hands per CTA
+// shared buffer: first the flat [hands][22] joint-angle stage, then the flat [hands][63] landmark
+// accumulator = the exact global layout, so both copies are straight 16-byte moves; the per-thread
+// rows have odd (63) / 8-byte-friendly (22) strides -> conflict-free LDS.64 / STS.32
+constexpr int kOutFloats = kFast * 63;
 
 struct JointConst {  // 24 floats, 16-byte aligned: K (3), K^2 (6 sym), K p (3), K^2 p (3), |axis|^2
   float4 v[6];
@@ -134,29 +136,25 @@ struct JointConst {  // 24 floats, 16-byte aligned: K (3), K^2 (6 sym), K p (3),
 
 struct FastTables {
   JointConst jc[20];
-  float lm_p[63];          // landmark rest positions
+  float4 ent_q[64];        // (w p, w) of entry: out (+)= R (w p) + w t
+  int ent_off[64];         // 3 * landmark; bit 31 set: first contribution to that landmark (store)
   int fs[kNumFrames + 1];  // CSR row starts
-  int ent_l[64];           // landmark of entry
-  float ent_w[64];         // weight of entry
-  int ent_first[64];       // 1: first contribution to that landmark (store), 0: accumulate
   int lm_has[21];
 };
 
 // every landmark attached to frame b: out[l] (+)= w * (F [p,1])   (hand_skinning._lbs :56-67)
-__device__ __forceinline__ void emit_frame(const FastTables& tb, float* __restrict__ s_out, int b, const Xf& F) {
-  const int tid = threadIdx.x;
+__device__ __forceinline__ void emit_frame(const FastTables& tb, float* __restrict__ row, int b, const Xf& F) {
   for (int e = tb.fs[b]; e < tb.fs[b + 1]; ++e) {
-    const int l = tb.ent_l[e];
-    const float w = tb.ent_w[e];
-    const float qx = tb.lm_p[3 * l] * w, qy = tb.lm_p[3 * l + 1] * w, qz = tb.lm_p[3 * l + 2] * w;
-    const float ox = F.r[0] * qx + F.r[1] * qy + F.r[2] * qz + F.t[0] * w;
-    const float oy = F.r[3] * qx + F.r[4] * qy + F.r[5] * qz + F.t[1] * w;
-    const float oz = F.r[6] * qx + F.r[7] * qy + F.r[8] * qz + F.t[2] * w;
-    float* o = s_out + (3 * l) * kOutLd + tid;
-    if (tb.ent_first[e]) {
-      o[0] = ox; o[kOutLd] = oy; o[2 * kOutLd] = oz;
+    const float4 q = tb.ent_q[e];
+    const int off = tb.ent_off[e];
+    const float ox = fmaf(F.r[0], q.x, fmaf(F.r[1], q.y, fmaf(F.r[2], q.z, F.t[0] * q.w)));
+    const float oy = fmaf(F.r[3], q.x, fmaf(F.r[4], q.y, fmaf(F.r[5], q.z, F.t[1] * q.w)));
+    const float oz = fmaf(F.r[6], q.x, fmaf(F.r[7], q.y, fmaf(F.r[8], q.z, F.t[2] * q.w)));
+    float* o = row + (off & 0xff);
+    if (off < 0) {
+      o[0] = ox; o[1] = oy; o[2] = oz;
     } else {
-      o[0] += ox; o[kOutLd] += oy; o[2 * kOutLd] += oz;
+      o[0] += ox; o[1] += oy; o[2] += oz;
     }
   }
 }
@@ -191,7 +189,6 @@ __global__ void __launch_bounds__(kFast, 3) fk_skin_shared_kernel(const float* _
     J.v[4] = make_float4(k2x, k2y, k2z, 0.f);
     J.v[5] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  if (tid >= 32 && tid < 32 + 63) tb.lm_p[tid - 32] = m.landmark_rest_positions[tid - 32];
   if (tid >= 128 && tid < 128 + 64) {
     const int e = tid - 128;
     int valid = 0, b = 0;
@@ -214,9 +211,10 @@ __global__ void __launch_bounds__(kFast, 3) fk_skin_shared_kernel(const float* _
         pos += before;
         if (before && j / K == l) first = 0;
       }
-      tb.ent_l[pos] = l;
-      tb.ent_w[pos] = m.landmark_rest_bone_weights[e];
-      tb.ent_first[pos] = first;
+      const float w = m.landmark_rest_bone_weights[e];
+      const float* lp = m.landmark_rest_positions + 3 * l;
+      tb.ent_q[pos] = make_float4(lp[0] * w, lp[1] * w, lp[2] * w, w);
+      tb.ent_off[pos] = (3 * l) | (first ? (int)0x80000000 : 0);
     }
     if (e <= kNumFrames) {
       int cnt = 0;
@@ -229,49 +227,57 @@ __global__ void __launch_bounds__(kFast, 3) fk_skin_shared_kernel(const float* _
       tb.lm_has[e] = any;
     }
   }
+  // tile bases are multiples of 16 B (256 hands x 88 / 64 / 252 B), so alignment depends on the pointers only
+  const bool vec_ok = (((uintptr_t)joint_angles | (uintptr_t)wrist | (uintptr_t)landmarks) & 15) == 0;
   // ---- persistent loop over tiles of kFast hands (the tables above are built once per CTA)
   const int64_t n_tiles = (n + kFast - 1) / kFast;
   for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
   const int64_t base = tile * kFast;
   const int n_here = (int)min((int64_t)kFast, n - base);
-  // coalesced input staging: joint angles [n_here,22] -> rows of 23, wrist [n_here,16] -> rows of 17
-  float* s_ja = smem;
-  float* s_wx = smem + kFast * kJaLd;
+  // coalesced input staging: the tile's joint angles [n_here,22] as one flat 16-byte copy; the
+  // wrist rows (64 B per hand, used once) come straight from global memory as three float4
   {
     const float* gja = joint_angles + base * 22;
-    for (int i = tid; i < n_here * 22; i += kFast) {
-      const int h = i / 22, j = i - h * 22;
-      s_ja[h * kJaLd + j] = __ldg(gja + i);
+    const int tot = n_here * 22;
+    int done = 0;
+    if (vec_ok) {
+      const int nv = tot >> 2;
+      const float4* g4 = reinterpret_cast<const float4*>(gja);
+      float4* s4 = reinterpret_cast<float4*>(smem);
+      for (int i = tid; i < nv; i += kFast) s4[i] = __ldg(g4 + i);
+      done = nv << 2;
     }
-    const float* gwx = wrist + base * 16;
-    for (int i = tid; i < n_here * 16; i += kFast) s_wx[(i >> 4) * kWxLd + (i & 15)] = __ldg(gwx + i);
+    for (int i = done + tid; i < tot; i += kFast) smem[i] = __ldg(gja + i);
   }
   __syncthreads();
   const bool active = tid < n_here;
   float ang[20];
   Xf W;
   if (active) {
+    const float2* a2 = reinterpret_cast<const float2*>(smem + tid * 22);
 #pragma unroll
-    for (int j = 0; j < 20; ++j) ang[j] = s_ja[tid * kJaLd + j];
+    for (int j = 0; j < 10; ++j) {
+      const float2 v = a2[j];
+      ang[2 * j] = v.x; ang[2 * j + 1] = v.y;
+    }
     const float sgn = (hand_idx != nullptr && hand_idx[base + tid] == 1) ? -1.0f : 1.0f;
+    const float* gw = wrist + (base + tid) * 16;
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
-      W.r[i * 3 + 0] = sgn * s_wx[tid * kWxLd + i * 4 + 0];
-      W.r[i * 3 + 1] = s_wx[tid * kWxLd + i * 4 + 1];
-      W.r[i * 3 + 2] = s_wx[tid * kWxLd + i * 4 + 2];
-      W.t[i] = s_wx[tid * kWxLd + i * 4 + 3];
+      float4 r;
+      if (vec_ok) r = __ldg(reinterpret_cast<const float4*>(gw) + i);
+      else r = make_float4(__ldg(gw + 4 * i), __ldg(gw + 4 * i + 1), __ldg(gw + 4 * i + 2), __ldg(gw + 4 * i + 3));
+      W.r[i * 3 + 0] = sgn * r.x; W.r[i * 3 + 1] = r.y; W.r[i * 3 + 2] = r.z; W.t[i] = r.w;
     }
   }
-  __syncthreads();  // inputs are in registers: the buffer becomes the [63][kOutLd] landmark accumulator
-  float* s_out = smem;
+  __syncthreads();  // inputs are in registers: the buffer becomes the flat [hands][63] landmark accumulator
+  float* row = smem + tid * 63;
   if (active) {
     for (int l = 0; l < 21; ++l)
-      if (!tb.lm_has[l]) {
-        s_out[(3 * l) * kOutLd + tid] = 0.f; s_out[(3 * l + 1) * kOutLd + tid] = 0.f; s_out[(3 * l + 2) * kOutLd + tid] = 0.f;
-      }
-    emit_frame(tb, s_out, 0, W);
-    emit_frame(tb, s_out, 1, W);
-#pragma unroll 1
+      if (!tb.lm_has[l]) { row[3 * l] = 0.f; row[3 * l + 1] = 0.f; row[3 * l + 2] = 0.f; }
+    emit_frame(tb, row, 0, W);
+    emit_frame(tb, row, 1, W);
+#pragma unroll 1  // (fully unrolled: 0.414 instead of 0.439 of HBM at 4M hands - instruction cache)
     for (int f = 0; f < 5; ++f) {
       Xf cur = W;
 #pragma unroll
@@ -297,19 +303,26 @@ __global__ void __launch_bounds__(kFast, 3) fk_skin_shared_kernel(const float* _
         T.t[2] = -(s1 * c3.z + s2 * c4.z);
         compose(cur, T, nxt);
         cur = nxt;
-        if (i >= 1) emit_frame(tb, s_out, 2 + 3 * f + (i - 1), cur);
+        if (i >= 1) emit_frame(tb, row, 2 + 3 * f + (i - 1), cur);
       }
 #pragma unroll
       for (int q = 0; q < 16; ++q) ang[q] = ang[q + 4];
     }
   }
   __syncthreads();
-  // transposed, fully coalesced store: element idx = hand*63 + comp <- s_out[comp][hand]
-  float* dst = landmarks + base * 63;
-  const int total = n_here * 63;
-  for (int i = tid; i < total; i += kFast) {
-    const int h = i / 63, c = i - h * 63;
-    dst[i] = s_out[c * kOutLd + h];
+  // the accumulator already has the global layout: one flat 16-byte copy
+  {
+    float* dst = landmarks + base * 63;
+    const int tot = n_here * 63;
+    int done = 0;
+    if (vec_ok) {
+      const int nv = tot >> 2;
+      float4* d4 = reinterpret_cast<float4*>(dst);
+      const float4* s4 = reinterpret_cast<const float4*>(smem);
+      for (int i = tid; i < nv; i += kFast) d4[i] = s4[i];
+      done = nv << 2;
+    }
+    for (int i = done + tid; i < tot; i += kFast) dst[i] = smem[i];
   }
   __syncthreads();  // the buffer is reused as the input stage of the next tile
   }
@@ -385,8 +398,7 @@ extern "C" int at_fk_skin_f32(const float* joint_angles, const float* wrist_xfor
     attr_set = true;
   }
   if (!model->per_sample && model->n_weights <= 3) {
-    constexpr int fast_smem = 63 * kOutLd * (int)sizeof(float);
-    static_assert(kFast * (kJaLd + kWxLd) <= 63 * kOutLd, "input staging must fit the output buffer");
+    constexpr int fast_smem = kOutFloats * (int)sizeof(float);
     static bool fast_attr = false;
     if (!fast_attr) {
       cudaFuncSetAttribute(fk_skin_shared_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fast_smem);

@@ -90,6 +90,36 @@ def test_fk_matches_oracle_random_poses_and_per_sample_models(cuda_lib, gold):
     assert one.shape == (21, 3)
 
 
+def test_fk_ragged_tiles_and_unaligned_pointers(cuda_lib, gold):
+    """Several 256-hand tiles with a ragged tail, and plain-`float*` callers whose pointers are only
+    4-byte aligned (the kernel's 16-byte copies must fall back to scalar ones): identical results."""
+    from absolutetrack_b200.lib.common.hand_skinning import skin_landmarks_cuda
+
+    hm = _hand_model_tuple(gold["geometry"], "hm_")
+    rng = np.random.default_rng(5)
+    for n in (256 * 3 + 7, 2049):
+        ja = rng.uniform(-1.5, 1.5, (n, 22)).astype(np.float32)
+        wx = np.tile(np.eye(4, dtype=np.float32), (n, 1, 1))
+        wx[:, :3, :3] = O.so3_exp_map_f32(rng.normal(0, 1, (n, 3)).astype(np.float32))
+        wx[:, :3, 3] = rng.normal(0, 300, (n, 3))
+        hidx = torch.from_numpy(rng.integers(0, 2, n)).cuda()
+        ref = O.landmarks_from_hand_pose(scenario.hand_model(), ja, wx, hidx.cpu().numpy())
+        a = skin_landmarks_cuda(hm, torch.from_numpy(ja).cuda(), torch.from_numpy(wx).cuda(), hand_idx=hidx)
+        assert np.abs(a.cpu().numpy() - ref).max() < 1e-3
+        for off in (1, 2, 3):
+            bj = torch.zeros(n * 22 + 4, device="cuda")
+            bw = torch.zeros(n * 16 + 4, device="cuda")
+            bo = torch.full((n * 63 + 8,), -7.0, device="cuda")
+            vj = bj[off:off + n * 22].view(n, 22).copy_(torch.from_numpy(ja))
+            vw = bw[off:off + n * 16].view(n, 4, 4).copy_(torch.from_numpy(wx))
+            vo = bo[off:off + n * 63].view(n, 21, 3)
+            assert vj.data_ptr() % 16 != 0 and vo.data_ptr() % 16 != 0
+            b = skin_landmarks_cuda(hm, vj, vw, hand_idx=hidx, out=vo)
+            assert b.data_ptr() == vo.data_ptr()
+            assert torch.equal(a, vo)
+            assert bool((bo[:off] == -7.0).all()) and bool((bo[off + n * 63:] == -7.0).all())  # nothing outside
+
+
 def test_fk_empty_batch(cuda_lib, gold):
     from absolutetrack_b200.lib.common.hand_skinning import skin_landmarks_cuda
 

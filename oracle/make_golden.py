@@ -1,6 +1,6 @@
 """Generate tests/golden/*.npz by running the UNMODIFIED reference in the build container.
 
-TEST INFRASTRUCTURE.  Run as `python oracle/make_golden.py [fk] [geometry] [warp] [model]`
+TEST INFRASTRUCTURE.  Run as `python oracle/make_golden.py [fk] [geometry] [warp] [cropcams] [eval] [model]`
 (no argument = all).  /root/reference is read-only and absent on the GPU box, so the
 outputs are committed; this script is the provenance record for every fixture.
 
@@ -18,6 +18,10 @@ Fixtures
                   by visibility instead of camera index, 21/42 crop points, thresholds, up to
                   4 views, poses pushed towards the image borders) -> selected cameras + crop
                   camera intrinsics / extrinsics.
+  eval_user05.npz the reference's own tracking results (tracked_keypoints of the same three user05
+                  pickles) and what the reference's load_eval._compute_metrics (:26-44) +
+                  metric_utils.PCK_curve / normalized_AUC (:34-44,95-121) make of them per recording
+                  and combined (aggregate_metrics :47-92): the README-style table.
   model.npz       reference UmeTrackModel outputs (umetrack_model.py:188-242) for the seeded
                   state dict of absolutetrack_b200 `make_random_state_dict(0)`.
 """
@@ -100,6 +104,44 @@ def make_fk():
         out.update(hand_model_arrays(L.hand_model, p))
     np.savez_compressed(os.path.join(GOLD, "fk_user05.npz"), **out)
     print("fk_user05.npz", sum(int(out[k].sum()) for k in out if k.endswith("valid")), "poses")
+
+
+def make_eval():
+    """Known-answer fixture of the evaluation table: the reference's own aggregation run on its own
+    stored tracking results."""
+    import load_eval as RL
+    from lib.common import metric_utils as RM
+
+    out, errs, accs, gaccs, valids = {}, [], [], [], []
+    for rec in ["00", "02", "11"]:
+        g = np.load(f"{REF}/sample_data/user05/recording_{rec}.npy", allow_pickle=True)
+        g = g if isinstance(g, dict) else g.item()
+        m = RL._compute_metrics(g["gt_keypoints"], g["tracked_keypoints"], g["valid_tracking"])
+        p = f"r{rec}_"
+        tr32 = g["tracked_keypoints"].astype(np.float32)
+        assert np.array_equal(tr32.astype(np.float64), g["tracked_keypoints"])  # float32 values in a float64 array
+        assert np.array_equal(g["gt_keypoints"].astype(np.float32).astype(np.float64), g["gt_keypoints"])
+        out[p + "tracked_keypoints"] = tr32  # gt_keypoints / valid: fk_user05.npz
+        out[p + "sum_error"] = np.float64(m.keypoint_errors.sum())
+        out[p + "sum_accel"] = np.float64(m.keypoint_accelerations.sum())
+        out[p + "sum_gt_accel"] = np.float64(m.gt_keypoint_accelerations.sum())
+        out[p + "n_accel"] = np.int64(m.keypoint_accelerations.size)
+        out[p + "pck_counts"] = np.array([(m.keypoint_errors <= t).sum() for t in RM.PCK_THRESHOLDS], np.int64)
+        errs.append(m.keypoint_errors); accs.append(m.keypoint_accelerations); gaccs.append(m.gt_keypoint_accelerations)
+        valids.append(g["valid_tracking"])
+    e = np.concatenate(errs)
+    pck = RM.PCK_curve(e, RM.PCK_THRESHOLDS) * 100.0
+    v = np.concatenate(valids, axis=1)
+    out["thresholds"] = RM.PCK_THRESHOLDS
+    out["pck_curve"] = pck
+    out["auc"] = np.float64(RM.normalized_AUC(RM.PCK_THRESHOLDS, pck))
+    out["n_valid"], out["n_total"] = np.int64(v.sum()), np.int64(v.size)
+    out["mean_error"] = np.float64(e.mean())
+    out["mean_accel"] = np.float64(np.concatenate(accs).mean())
+    out["mean_gt_accel"] = np.float64(np.concatenate(gaccs).mean())
+    np.savez_compressed(os.path.join(GOLD, "eval_user05.npz"), **out)
+    print("eval_user05.npz", int(out["n_valid"]), "of", int(out["n_total"]), "mean error", float(out["mean_error"]),
+          "auc", float(out["auc"]), "accel", float(out["mean_accel"]), float(out["mean_gt_accel"]))
 
 
 def _frames():
@@ -248,9 +290,11 @@ def make_warp():
 
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
-    what = sys.argv[1:] or ["fk", "geometry", "warp", "cropcams", "model"]
+    what = sys.argv[1:] or ["fk", "geometry", "warp", "cropcams", "eval", "model"]
     if "fk" in what:
         make_fk()
+    if "eval" in what:
+        make_eval()
     if "geometry" in what:
         make_geometry()
     if "cropcams" in what:

@@ -378,3 +378,54 @@ def mean_keypoint_accel(kp, valid):
     ok = valid[:-2] & valid[1:-1] & valid[2:]
     a = np.linalg.norm(kp[:-2] + kp[2:] - 2 * kp[1:-1], axis=-1).mean(-1)
     return float(a[ok].mean()) if ok.any() else 0.0
+
+
+# --------------------------------------------------------------------------------------
+# evaluation table (load_eval.py:26-92, metric_utils.py:16-44,95-121)
+# --------------------------------------------------------------------------------------
+PCK_THRESHOLDS = np.linspace(0, 50, 101)  # metric_utils.py:16-17 (MAX_LANDMARK_ERROR_MM = 50)
+
+
+def recording_metric_sums(gt, tracked, valid, thresholds=PCK_THRESHOLDS):
+    """load_eval._compute_metrics (:26-44) reduced to what aggregate_metrics (:47-92) needs, as sums
+    that add up across recordings: gt / tracked [H,T,21,3], valid [H,T] bool ->
+    dict(sum_error, sum_accel, sum_gt_accel, n_valid, n_total, n_accel, pck_counts[len(thresholds)])."""
+    gt = np.asarray(gt, np.float64)
+    tracked = np.asarray(tracked, np.float64)
+    valid = np.asarray(valid, bool)
+
+    def accel(p):
+        return np.linalg.norm(p[:, 0:-2] + p[:, 2:] - 2 * p[:, 1:-1], axis=-1).mean(axis=-1)
+
+    err = np.linalg.norm(gt - tracked, axis=-1).mean(axis=-1)[valid]
+    if valid.shape[1] >= 3:
+        ok = valid[:, 0:-2] & valid[:, 1:-1] & valid[:, 2:]
+        a, ga = accel(tracked)[ok], accel(gt)[ok]
+    else:
+        a = ga = np.zeros(0)
+    return dict(
+        sum_error=float(err.sum()), sum_accel=float(a.sum()), sum_gt_accel=float(ga.sum()),
+        n_valid=int(valid.sum()), n_total=int(valid.size), n_accel=int(a.size),
+        pck_counts=np.array([(err <= t).sum() for t in thresholds], np.int64),  # metric_utils._PCK_curve :34-44
+    )
+
+
+def normalized_auc(x, y, y_max=1.0):
+    """metric_utils.normalized_AUC (:95-121): trapezoid area over (x[-1]-x[0]) * y_max."""
+    x, y = np.asarray(x, np.float64), np.asarray(y, np.float64)
+    return float(((x[1:] - x[:-1]) * (y[1:] + y[:-1]) * 0.5).sum() / ((x[-1] - x[0]) * y_max))
+
+
+def eval_table(sums, thresholds=PCK_THRESHOLDS):
+    """The numbers aggregate_metrics prints (:71-92) from summed `recording_metric_sums`; PCK is in
+    percent and the AUC is normalised with y_max = 1 exactly as the reference calls it (:68-70)."""
+    n = max(sums["n_valid"], 1)
+    pck = np.where(sums["n_valid"] >= 1e-6, sums["pck_counts"] / n, 0.0) * 100.0  # _safe_div :20-31
+    return dict(
+        success_rate=sums["n_valid"] / sums["n_total"] * 100 if sums["n_total"] else 0.0,
+        mean_error=sums["sum_error"] / n,
+        pck_curve=pck,
+        auc=normalized_auc(thresholds, pck),
+        mean_accel=sums["sum_accel"] / max(sums["n_accel"], 1),
+        mean_gt_accel=sums["sum_gt_accel"] / max(sums["n_accel"], 1),
+    )

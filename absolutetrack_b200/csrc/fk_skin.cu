@@ -366,7 +366,113 @@ eval_accumulate_kernel(const float* __restrict__ lm, const float* __restrict__ g
   }
 }
 
+
+// ------------------------------------------------------------------------------------------
+// Evaluation table of one recording (load_eval._compute_metrics :26-44 and the PCK counts of
+// metric_utils._PCK_curve :34-44) as sums that add up across recordings and ranks.  One warp per
+// hand-frame, lanes = landmarks.  float64 throughout like the reference's numpy arrays, and every
+// sum is taken in numpy's order (norm: (x^2 + y^2) + z^2; mean over 21: the 8-lane pairwise block
+// of numpy's add.reduce, then the 5 remaining terms), so a hand-frame's error is bit-identical to
+// the reference's and the integer PCK counts are exact.
+constexpr int kEvalMaxThresholds = 128;
+
+__device__ __forceinline__ double norm3_np(double x, double y, double z) {
+  return sqrt(__dadd_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)), __dmul_rn(z, z)));
+}
+
+// numpy's pairwise add.reduce of 21 contiguous doubles held by lanes 0..20; result valid in lane 0
+__device__ __forceinline__ double sum21_np(double a, int lane) {
+  const unsigned full = 0xffffffffu;
+  double r = __dadd_rn(a, __shfl_down_sync(full, a, 8));       // r[j] = a[j] + a[j+8], j < 8
+  r = __dadd_rn(r, __shfl_down_sync(full, r, 1));              // r0+r1, r2+r3, ...
+  r = __dadd_rn(r, __shfl_down_sync(full, r, 2));              // (r0+r1)+(r2+r3), (r4+r5)+(r6+r7)
+  r = __dadd_rn(r, __shfl_down_sync(full, r, 4));
+#pragma unroll
+  for (int i = 16; i < 21; ++i) r = __dadd_rn(r, __shfl_sync(full, a, i));
+  (void)lane;
+  return r;
+}
+
+__global__ void __launch_bounds__(256)
+eval_recording_kernel(const float* __restrict__ tracked, const float* __restrict__ gt, const uint8_t* __restrict__ valid,
+                      int64_t n_hands, int64_t T, const double* __restrict__ thresholds, int n_thr,
+                      double* __restrict__ sums, unsigned long long* __restrict__ counts) {
+  __shared__ double s_sum[3];
+  __shared__ unsigned long long s_cnt[3 + kEvalMaxThresholds];
+  for (int i = threadIdx.x; i < 3 + kEvalMaxThresholds; i += blockDim.x) s_cnt[i] = 0ull;
+  if (threadIdx.x < 3) s_sum[threadIdx.x] = 0.0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int64_t n = n_hands * T;
+  const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+  double thr[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) thr[k] = (lane + 32 * k < n_thr) ? thresholds[lane + 32 * k] : -1.0;
+  double se = 0.0, sa = 0.0, sg = 0.0;
+  unsigned nv = 0, na = 0, c[4] = {0, 0, 0, 0};
+  for (int64_t idx = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); idx < n; idx += warps) {
+    if (!valid[idx]) continue;  // warp-uniform
+    const int64_t t = idx % T;
+    const bool tri = t + 2 < T && valid[idx + 1] && valid[idx + 2];  // frames t, t+1, t+2 of the same hand
+    double d = 0.0, a = 0.0, g = 0.0;
+    if (lane < 21) {
+      const float* p = tracked + (idx * 21 + lane) * 3;
+      const float* q = gt + (idx * 21 + lane) * 3;
+      d = norm3_np((double)q[0] - (double)p[0], (double)q[1] - (double)p[1], (double)q[2] - (double)p[2]);
+      if (tri) {
+        double v[3], w[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {  // pts[t] + pts[t+2] - 2 pts[t+1]  (load_eval.py:30)
+          v[k] = __dadd_rn(__dadd_rn((double)p[k], (double)p[k + 126]), -2.0 * (double)p[k + 63]);
+          w[k] = __dadd_rn(__dadd_rn((double)q[k], (double)q[k + 126]), -2.0 * (double)q[k + 63]);
+        }
+        a = norm3_np(v[0], v[1], v[2]);
+        g = norm3_np(w[0], w[1], w[2]);
+      }
+    }
+    const double e = __shfl_sync(0xffffffffu, sum21_np(d, lane), 0) / 21.0;
+    se += e;
+    nv += 1;
+    if (tri) {
+      sa += sum21_np(a, lane) / 21.0;
+      sg += sum21_np(g, lane) / 21.0;
+      na += 1;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) c[k] += (e <= thr[k]) ? 1u : 0u;  // metric_utils.py:40 (thr = -1: never)
+  }
+  if (lane == 0) {
+    atomicAdd(&s_sum[0], se); atomicAdd(&s_sum[1], sa); atomicAdd(&s_sum[2], sg);
+    atomicAdd(&s_cnt[0], (unsigned long long)nv); atomicAdd(&s_cnt[2], (unsigned long long)na);
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    if (c[k]) atomicAdd(&s_cnt[3 + lane + 32 * k], (unsigned long long)c[k]);
+  __syncthreads();
+  if (blockIdx.x == 0 && threadIdx.x == 0) s_cnt[1] = (unsigned long long)n;
+  __syncthreads();
+  if (threadIdx.x < 3 && s_sum[threadIdx.x] != 0.0) atomicAdd(sums + threadIdx.x, s_sum[threadIdx.x]);
+  for (int i = threadIdx.x; i < 3 + n_thr; i += blockDim.x)
+    if (s_cnt[i]) atomicAdd(counts + i, s_cnt[i]);
+}
+
 }  // namespace
+
+extern "C" int at_eval_recording_f32(const float* tracked_keypoints, const float* gt_keypoints, const uint8_t* valid_tracking,
+                                     int64_t n_hands, int64_t n_frames, const double* thresholds, int n_thresholds,
+                                     double* sums, int64_t* counts, void* stream) {
+  AT_REQUIRE(n_hands >= 0 && n_frames >= 0, "at_eval_recording_f32: negative size");
+  AT_REQUIRE(n_thresholds >= 0 && n_thresholds <= kEvalMaxThresholds, "at_eval_recording_f32: at most 128 thresholds");
+  if (n_hands * n_frames == 0) return AT_OK;
+  AT_REQUIRE(tracked_keypoints && gt_keypoints && valid_tracking && sums && counts, "at_eval_recording_f32: NULL pointer");
+  AT_REQUIRE(n_thresholds == 0 || thresholds != nullptr, "at_eval_recording_f32: thresholds is NULL");
+  const int64_t n = n_hands * n_frames;
+  const int64_t blocks = std::min<int64_t>((n + 7) / 8, 4 * at::kNumSMs);
+  eval_recording_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+      tracked_keypoints, gt_keypoints, valid_tracking, n_hands, n_frames, thresholds, n_thresholds, sums,
+      reinterpret_cast<unsigned long long*>(counts));
+  return at::check_launch("eval_recording_kernel");
+}
 
 extern "C" int at_eval_accumulate_f32(const float* landmarks, const float* gt_landmarks, const float* joint_angles,
                                       const float* gt_joint_angles, const uint8_t* valid, int64_t n, double* sums,

@@ -145,6 +145,23 @@ int at_eval_accumulate_f32(const float* landmarks, const float* gt_landmarks, co
                            const float* gt_joint_angles, const uint8_t* valid, int64_t n, double* sums,
                            void* stream);
 
+/* Evaluation table of one recording on the device.  Replaces
+ * load_eval._compute_metrics (load_eval.py:26-44) and the per-threshold counts of
+ * metric_utils._PCK_curve (lib/common/metric_utils.py:34-44) with sums that add up across
+ * recordings and ranks (aggregate_metrics, load_eval.py:47-92, divides them at the end):
+ *   sums[0]   += sum over valid hand-frames of e = mean_l |gt - tracked|            (keypoint_errors)
+ *   sums[1]   += sum over valid triples (t,t+1,t+2) of mean_l |p[t] + p[t+2] - 2 p[t+1]|, p = tracked
+ *   sums[2]   += the same of gt
+ *   counts[0] += valid hand-frames   counts[1] += n_hands * n_frames   counts[2] += valid triples
+ *   counts[3 + k] += #(valid e <= thresholds[k]),  k < n_thresholds <= 128
+ * tracked_keypoints / gt_keypoints: float32 [n_hands, n_frames, 21, 3] (mm; the reference keeps
+ * float32 values in float64 arrays), valid_tracking: uint8 [n_hands, n_frames], thresholds: float64
+ * on the device.  Arithmetic is float64 in numpy's summation order: e is bit-identical to the
+ * reference's, so the integer counts are exact. */
+int at_eval_recording_f32(const float* tracked_keypoints, const float* gt_keypoints, const uint8_t* valid_tracking,
+                          int64_t n_hands, int64_t n_frames, const double* thresholds, int n_thresholds,
+                          double* sums, int64_t* counts, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * (5) Crop-camera generation + model-input assembly on the device.  Replaces
  * HandTracker.gen_crop_cameras (lib/tracker/tracker.py:222-260) with everything below it -

@@ -177,6 +177,55 @@ def test_oracle_metrics():
     assert O.mean_keypoint_accel(lin, np.ones((2, 10), bool)) < 1e-12      # constant velocity
 
 
+def _oracle_eval_arrays(F, E, recs):
+    """Oracle sums of the given user05 recordings in the EvalSums layout (f64 [3], i64 [3 + 101])."""
+    sums, counts = np.zeros(3), np.zeros(3 + 101, np.int64)
+    for rec in recs:
+        p = f"r{rec}_"
+        s = O.recording_metric_sums(F[p + "gt_keypoints"], E[p + "tracked_keypoints"], F[p + "valid"])
+        sums += [s["sum_error"], s["sum_accel"], s["sum_gt_accel"]]
+        counts[:3] += [s["n_valid"], s["n_total"], s["n_accel"]]
+        counts[3:] += s["pck_counts"]
+    return sums, counts
+
+
+def _check_eval_table(t, E):
+    assert (t["n_valid"], t["n_total"]) == (int(E["n_valid"]), int(E["n_total"]))
+    assert abs(t["mean_keypoint_error"] - float(E["mean_error"])) < 1e-11
+    assert np.abs(t["pck_curve"] - E["pck_curve"].reshape(-1)).max() < 1e-12
+    assert abs(t["auc_score"] - float(E["auc"])) < 1e-11
+    assert abs(t["mean_keypoint_acceleration"] - float(E["mean_accel"])) < 1e-11
+    assert abs(t["gt_mean_keypoint_acceleration"] - float(E["mean_gt_accel"])) < 1e-11
+
+
+def test_oracle_eval_table_matches_reference_aggregation(gold):
+    """The reference's load_eval / metric_utils run on its own user05 result pickles: per-recording
+    sums and PCK counts exact, the combined table (success rate, error, PCK, AUC, accelerations)."""
+    from absolutetrack_b200.lib.common import metric_utils as M
+    from absolutetrack_b200.load_eval import table_from_sums
+
+    F, E = gold["fk_user05"], gold["eval_user05"]
+    assert np.array_equal(O.PCK_THRESHOLDS, E["thresholds"]) and np.array_equal(M.PCK_THRESHOLDS, E["thresholds"])
+    tot = None
+    for rec in ("00", "02", "11"):
+        p = f"r{rec}_"
+        s = O.recording_metric_sums(F[p + "gt_keypoints"], E[p + "tracked_keypoints"], F[p + "valid"])
+        assert np.array_equal(s["pck_counts"], E[p + "pck_counts"]) and s["n_accel"] == int(E[p + "n_accel"])
+        for k in ("sum_error", "sum_accel", "sum_gt_accel"):
+            assert abs(s[k] - float(E[p + k])) <= 1e-12 * abs(float(E[p + k]))
+        tot = s if tot is None else {k: tot[k] + s[k] for k in s}
+    t = O.eval_table(tot)
+    assert abs(t["mean_error"] - float(E["mean_error"])) < 1e-11 and abs(t["auc"] - float(E["auc"])) < 1e-11
+    assert np.abs(t["pck_curve"] - E["pck_curve"].reshape(-1)).max() < 1e-12
+    # the host arithmetic of the product (counts -> PCK -> AUC) on the same sums
+    _check_eval_table(table_from_sums(*_oracle_eval_arrays(F, E, ("00", "02", "11")), M.PCK_THRESHOLDS), E)
+    # short sequences: no triples, no valid frames
+    z = O.recording_metric_sums(np.zeros((2, 2, 21, 3)), np.ones((2, 2, 21, 3)), np.zeros((2, 2), bool))
+    assert z["n_accel"] == 0 and z["n_valid"] == 0 and z["n_total"] == 4
+    e = table_from_sums(np.zeros(3), np.zeros(104, np.int64), M.PCK_THRESHOLDS)
+    assert e["success_rate"] == 0.0 and np.isnan(e["mean_keypoint_error"]) and e["auc_score"] == 0.0
+
+
 # ------------------------------------------------------------------ host logic
 def test_state_dict_spec_is_the_reference_key_set():
     from absolutetrack_b200.lib.models.model_loader import make_random_state_dict, pack_state_dict, state_dict_spec
@@ -301,7 +350,16 @@ def _gloo_worker(rank, world, port, out_dir):
     D.all_reduce_metric_sums(sums)
     full = torch.zeros(2, dtype=torch.float64)
     D.mpjpe_accumulate(full, tracked, gt, valid)
-    torch.save({"mine": mine, "sums": sums, "full": full}, os.path.join(out_dir, f"r{rank}.pt"))
+    # evaluation table: the three user05 recordings strided over the ranks, float64 sums + int64 counts
+    from absolutetrack_b200.lib.common import metric_utils as M
+    from absolutetrack_b200.load_eval import all_reduce_eval_sums, table_from_sums
+
+    F = dict(np.load(os.path.join(ROOT, "tests", "golden", "fk_user05.npz")))
+    E = dict(np.load(os.path.join(ROOT, "tests", "golden", "eval_user05.npz")))
+    es, ec = (torch.from_numpy(a) for a in _oracle_eval_arrays(F, E, D.shard(["00", "02", "11"], rank, world)))
+    all_reduce_eval_sums(es, ec)
+    table = table_from_sums(es.numpy(), ec.numpy(), M.PCK_THRESHOLDS)
+    torch.save({"mine": mine, "sums": sums, "full": full, "table": table}, os.path.join(out_dir, f"r{rank}.pt"))
     dist.destroy_process_group()
 
 
@@ -314,11 +372,12 @@ def test_sequences_shard_across_two_ranks_and_metric_sums_all_reduce(tmp_path):
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
     mp.spawn(_gloo_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
-    r0, r1 = (torch.load(tmp_path / f"r{r}.pt") for r in range(2))
+    r0, r1 = (torch.load(tmp_path / f"r{r}.pt", weights_only=False) for r in range(2))
     assert sorted(r0["mine"] + r1["mine"]) == list(range(11)) and not set(r0["mine"]) & set(r1["mine"])
     assert r0["mine"] == list(range(0, 11, 2))                            # reference Sampler striding
     for r in (r0, r1):
         assert torch.allclose(r["sums"], r["full"], rtol=1e-12)           # every rank holds the global sums
+        _check_eval_table(r["table"], dict(np.load(os.path.join(ROOT, "tests", "golden", "eval_user05.npz"))))
 
 
 def test_shard_indices_validate_rank():

@@ -324,3 +324,74 @@ def test_eval_sums_match_oracle_mpjpe(cuda_lib):
     assert abs(s[1] / s[2] - dth) < 1e-4
     accumulate_metric_sums_cuda(lm[:0].cuda(), gt[:0].cuda(), sums)   # empty batch
     assert sums.cpu().numpy()[2] == s[2]
+
+
+# ------------------------------------------------------------------ evaluation table (f4)
+def test_eval_recording_table_matches_reference_aggregation(cuda_lib, gold, tmp_path):
+    """at_eval_recording_f32 against the reference's load_eval / metric_utils run on its own user05
+    result pickles: integer counts exact (the per-frame error is bit-identical: thresholds placed ON
+    error values still count exactly), sums to 1e-12, the printed table to 1e-10."""
+    import pickle
+
+    from absolutetrack_b200.load_eval import EvalSums, aggregate_metrics, compute_metric_sums_cuda
+
+    F, E = gold["fk_user05"], gold["eval_user05"]
+    total = EvalSums()
+    for rec in ("00", "02", "11"):
+        p = f"r{rec}_"
+        gt, tr, valid = F[p + "gt_keypoints"], E[p + "tracked_keypoints"], F[p + "valid"]
+        one = compute_metric_sums_cuda(gt, tr, valid, EvalSums())
+        s, c = one.sums.cpu().numpy(), one.counts.cpu().numpy()
+        assert np.array_equal(c[3:], E[p + "pck_counts"])
+        assert c[0] == valid.sum() and c[1] == valid.size and c[2] == int(E[p + "n_accel"])
+        for got, k in zip(s, ("sum_error", "sum_accel", "sum_gt_accel")):
+            assert abs(got - float(E[p + k])) <= 1e-12 * abs(float(E[p + k])), k
+        # thresholds equal to actual per-frame errors: exact counts need bit-identical errors
+        err = np.linalg.norm(gt.astype(np.float64) - tr.astype(np.float64), axis=-1).mean(axis=-1)[valid]
+        thr = np.sort(err)[:: max(1, err.size // 128)][:128]
+        on = compute_metric_sums_cuda(gt, tr, valid, EvalSums(thresholds=thr))
+        assert np.array_equal(on.counts.cpu().numpy()[3:], [(err <= t).sum() for t in thr])
+        compute_metric_sums_cuda(torch.from_numpy(gt).double(), tr, torch.from_numpy(valid), total)  # float64 in: converted
+        d = tmp_path / "real" / f"user{rec}"
+        d.mkdir(parents=True)
+        with open(d / f"recording_{rec}.npy", "wb") as fp:  # run_eval_known_skeleton.py:96-104
+            pickle.dump({"tracked_keypoints": tr.astype(np.float64), "gt_keypoints": gt.astype(np.float64), "valid_tracking": valid}, fp)
+    for t in (total.table(), aggregate_metrics(str(tmp_path), verbose=False)):
+        assert (t["n_valid"], t["n_total"]) == (int(E["n_valid"]), int(E["n_total"]))
+        assert abs(t["mean_keypoint_error"] - float(E["mean_error"])) < 1e-10
+        assert np.abs(t["pck_curve"] - E["pck_curve"].reshape(-1)).max() < 1e-12
+        assert abs(t["auc_score"] - float(E["auc"])) < 1e-10
+        assert abs(t["mean_keypoint_acceleration"] - float(E["mean_accel"])) < 1e-10
+        assert abs(t["gt_mean_keypoint_acceleration"] - float(E["mean_gt_accel"])) < 1e-10
+    assert aggregate_metrics(str(tmp_path / "nothing_here"), verbose=False) is None
+
+
+def test_eval_recording_edge_cases(cuda_lib):
+    from absolutetrack_b200 import _cabi
+    from absolutetrack_b200.load_eval import EvalSums, compute_metric_sums_cuda
+
+    rng = np.random.default_rng(3)
+    # sequences shorter than a triple, all-invalid hands, triples that straddle an invalid frame or the hand boundary
+    for H, T in ((2, 2), (2, 1), (1, 3), (3, 40), (2, 1000)):
+        gt = rng.normal(0, 80, (H, T, 21, 3)).astype(np.float32)
+        tr = (gt + rng.normal(0, 12, gt.shape)).astype(np.float32)
+        valid = rng.random((H, T)) > 0.15
+        valid[0, :] = T > 3 and H > 2          # one hand all valid (3 x 40 case) or all invalid
+        if T >= 3:
+            valid[-1, -3:] = True               # the last triple of the last hand ends exactly at the buffer end
+        acc = compute_metric_sums_cuda(gt, tr, valid, EvalSums())
+        ref = O.recording_metric_sums(gt, tr, valid)
+        c, s = acc.counts.cpu().numpy(), acc.sums.cpu().numpy()
+        assert [int(c[0]), int(c[1]), int(c[2])] == [ref["n_valid"], ref["n_total"], ref["n_accel"]], (H, T)
+        assert np.array_equal(c[3:], ref["pck_counts"])
+        assert np.allclose(s, [ref["sum_error"], ref["sum_accel"], ref["sum_gt_accel"]], rtol=1e-12, atol=1e-9)
+    # empty recording: nothing launched, accumulators untouched
+    acc = compute_metric_sums_cuda(np.zeros((2, 0, 21, 3)), np.zeros((2, 0, 21, 3)), np.zeros((2, 0), bool), EvalSums())
+    assert int(acc.counts.sum()) == 0
+    with pytest.raises(ValueError):
+        EvalSums(thresholds=np.linspace(0, 1, 129))
+    with pytest.raises(ValueError):
+        compute_metric_sums_cuda(np.zeros((2, 4, 21, 3)), np.zeros((2, 5, 21, 3)), np.zeros((2, 4), bool), EvalSums())
+    z = torch.zeros(8, device="cuda")
+    rc = _cabi.lib().at_eval_recording_f32(z.data_ptr(), z.data_ptr(), z.data_ptr(), 1, 1, None, 200, z.data_ptr(), z.data_ptr(), None)
+    assert rc != 0 and "128" in _cabi.lib().at_last_error_string().decode()

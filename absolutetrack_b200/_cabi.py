@@ -169,6 +169,7 @@ SIGNATURES = {
     "at_crop_resample_fisheye62_u8_ex": (_I, [_VP, _I64, _I64, _I64, _VP, _I, _I, _I, _VP, _I, _I, _VP, _VP]),
     "at_crop_pull_source_boxes_u8": (_I, [_VP, _VP, _I64, _I64, _I64, _I64, _VP, _I, _I, _I, _I, _VP, _VP]),
     "at_resample_homography_f32": (_I, [_VP, _I, _I, _I, _VP, _I, _I, _VP, _F, _VP]),
+    "at_gen_crop_matrices_f32": (_I, [_VP, _VP, _VP, _VP, _I64, _I, _I, _I, _I, _F, _VP, _VP, _VP, _VP, _VP]),
     "at_fk_skin_f32": (_I, [_VP, _VP, _VP, C.POINTER(AtHandModel), _I64, _VP, _VP]),
     "at_eval_accumulate_f32": (_I, [_VP, _VP, _VP, _VP, _VP, _I64, _VP, _VP]),
     "at_eval_recording_f32": (_I, [_VP, _VP, _VP, _I64, _I64, _VP, _I, _VP, _VP, _VP]),

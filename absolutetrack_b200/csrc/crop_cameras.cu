@@ -403,6 +403,115 @@ crop_cameras_emit_kernel(AtCropCameraInputs in, AtCropCameraOpts opt, AtCropCame
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Config-3 preprocessing: data_transform._gen_crop_matrices (:145-209) + _compute_resample_matrix
+// (:57-75) for a batch of pinhole views, one warp per (frame, view).  The views are rigid
+// world->eye transforms (the reference inverts them with numpy; here R^T), the crop camera keeps
+// the view's position, so the resample matrix has no translation:
+//   resample = K_orig [R_orig R_new^T | 0] K_new^-1   (new image -> original image).
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+crop_matrices_kernel(const float* __restrict__ orig_extrinsics, const float* __restrict__ orig_intrinsics,
+                     const float* __restrict__ crop_points, const uint8_t* __restrict__ mirror, int64_t n_frames,
+                     int n_views, int n_pts, int crop_w, int crop_h, float focal_multiplier, float min_focal,
+                     float* __restrict__ extrinsics_xf, float* __restrict__ new_intrinsics,
+                     float* __restrict__ resample_xf, int* __restrict__ n_errors) {
+  const int lane = threadIdx.x & 31;
+  const int64_t item = (int64_t)blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5);
+  if (item >= n_frames * n_views) return;
+  const int64_t frame = item / n_views;
+  const float* E = orig_extrinsics + item * 16;
+  const float* pts = crop_points + frame * n_pts * 3;
+  double Rw[9], tw[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    Rw[i * 3] = E[i * 4]; Rw[i * 3 + 1] = E[i * 4 + 1]; Rw[i * 3 + 2] = E[i * 4 + 2]; tw[i] = E[i * 4 + 3];
+  }
+  // crop.py:57: centre of the points' bounding box
+  float mn[3] = {3.0e38f, 3.0e38f, 3.0e38f}, mx[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+  for (int i = lane; i < n_pts; i += 32)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { mn[k] = fminf(mn[k], pts[i * 3 + k]); mx[k] = fmaxf(mx[k], pts[i * 3 + k]); }
+  double ctr[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) ctr[k] = ((double)warp_min(mn[k]) + (double)warp_max(mx[k])) / 2.0;
+  // affine.py:59-60: the centre in the view's eye frame, unit z direction
+  double lx = Rw[0] * ctr[0] + Rw[1] * ctr[1] + Rw[2] * ctr[2] + tw[0];
+  double ly = Rw[3] * ctr[0] + Rw[4] * ctr[1] + Rw[5] * ctr[2] + tw[1];
+  double lz = Rw[6] * ctr[0] + Rw[7] * ctr[1] + Rw[8] * ctr[2] + tw[2];
+  const double ln = sqrt(lx * lx + ly * ly + lz * lz);
+  lx /= ln; ly /= ln; lz /= ln;
+  // affine.py:34-44 from_two_vectors((0,0,1), z_dir); the camera angle is 0 (data_transform.py:199)
+  const double bn = fmax(5.43e-20, sqrt(lx * lx + ly * ly + lz * lz));
+  const double bx = lx / bn, by = ly / bn, bz = lz / bn;
+  const double v0 = -by, v1 = bx;
+  const double s2 = v0 * v0 + v1 * v1;
+  const double g = (1.0 - bz) / fmax(s2, 1e-15);
+  const double dR[9] = {1.0 - g * v1 * v1, g * v0 * v1,       v1,
+                        g * v0 * v1,       1.0 - g * v0 * v0, -v0,
+                        -v1,               v0,                1.0 - g * s2};
+  // new world->eye rotation = dR^T Rw (inverse of R_e2w dR), first row negated when mirrored (crop.py:63-66)
+  const double mir = (mirror != nullptr && mirror[frame]) ? -1.0 : 1.0;
+  double Wr[9], Wt[3], pos[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) pos[k] = -(Rw[k] * tw[0] + Rw[3 + k] * tw[1] + Rw[6 + k] * tw[2]);  // eye position in the world
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const double m = i == 0 ? mir : 1.0;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) Wr[i * 3 + j] = m * (dR[i] * Rw[j] + dR[3 + i] * Rw[3 + j] + dR[6 + i] * Rw[6 + j]);
+    Wt[i] = -(Wr[i * 3] * pos[0] + Wr[i * 3 + 1] * pos[1] + Wr[i * 3 + 2] * pos[2]);
+  }
+  // crop.py:15-28
+  double big = 0.0;
+  int bad = 0;
+  for (int i = lane; i < n_pts; i += 32) {
+    const double x = pts[i * 3], y = pts[i * 3 + 1], z = pts[i * 3 + 2];
+    const double ex = Wr[0] * x + Wr[1] * y + Wr[2] * z + Wt[0];
+    const double ey = Wr[3] * x + Wr[4] * y + Wr[5] * z + Wt[1];
+    const double ez = Wr[6] * x + Wr[7] * y + Wr[8] * z + Wt[2];
+    big = fmax(big, fmax(fabs(ex / ez), fabs(ey / ez)));
+    bad |= ez < 0.0001;
+  }
+  big = warp_max(big);
+  bad = __any_sync(0xffffffffu, bad);
+  const double cx = ((double)crop_w - 1.0) / 2.0, cy = ((double)crop_h - 1.0) / 2.0;
+  const double fx0 = cx / big, fy0 = cy / big;
+  if (lane == 0 && (bad || fx0 < min_focal || fy0 < min_focal)) atomicAdd(n_errors, 1);
+  const double fx = focal_multiplier * fx0, fy = focal_multiplier * fy0;
+  if (lane == 0) {
+    float* X = extrinsics_xf + item * 16;
+    float* K = new_intrinsics + item * 9;
+    float* S = resample_xf + item * 16;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      X[i * 4] = (float)Wr[i * 3]; X[i * 4 + 1] = (float)Wr[i * 3 + 1]; X[i * 4 + 2] = (float)Wr[i * 3 + 2]; X[i * 4 + 3] = (float)Wt[i];
+    }
+    X[12] = 0.f; X[13] = 0.f; X[14] = 0.f; X[15] = 1.f;
+    K[0] = (float)fx; K[1] = 0.f; K[2] = (float)cx; K[3] = 0.f; K[4] = (float)fy; K[5] = (float)cy; K[6] = 0.f; K[7] = 0.f; K[8] = 1.f;
+    // A = R_orig R_new^T; K_new^-1 = [[1/fx, 0, -cx/fx], [0, 1/fy, -cy/fy], [0, 0, 1]]
+    const float* Ko = orig_intrinsics + item * 9;
+    const double ofx = Ko[0], ofy = Ko[4], ocx = Ko[2], ocy = Ko[5];  // uv_to_window_matrix of f, c (:181-195)
+    double A[9], B[9];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 3; ++j) A[i * 3 + j] = Rw[i * 3] * Wr[j * 3] + Rw[i * 3 + 1] * Wr[j * 3 + 1] + Rw[i * 3 + 2] * Wr[j * 3 + 2];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {  // B = A K_new^-1
+      B[i * 3] = A[i * 3] / fx;
+      B[i * 3 + 1] = A[i * 3 + 1] / fy;
+      B[i * 3 + 2] = A[i * 3 + 2] - A[i * 3] * (cx / fx) - A[i * 3 + 1] * (cy / fy);
+    }
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {  // K_orig B
+      S[j] = (float)(ofx * B[j] + ocx * B[6 + j]);
+      S[4 + j] = (float)(ofy * B[3 + j] + ocy * B[6 + j]);
+      S[8 + j] = (float)B[6 + j];
+    }
+    S[3] = 0.f; S[7] = 0.f; S[11] = 0.f; S[12] = 0.f; S[13] = 0.f; S[14] = 0.f; S[15] = 1.f;
+  }
+}
+
 }  // namespace
 
 extern "C" int64_t at_crop_cameras_workspace_bytes(int n_poses, int max_view_num) {
@@ -458,4 +567,22 @@ extern "C" int at_gen_crop_cameras(const AtCropCameraInputs* in, const AtHandMod
   if (rc) return rc;
   crop_cameras_emit_kernel<<<blocks, kWarpsPerCta * 32, 0, st>>>(*in, *opts, *out, hdr, slots);
   return at::check_launch("crop_cameras_emit_kernel");
+}
+
+extern "C" int at_gen_crop_matrices_f32(const float* orig_extrinsics, const float* orig_intrinsics, const float* crop_points,
+                                        const uint8_t* mirror_image, int64_t n_frames, int n_views, int n_pts, int crop_w,
+                                        int crop_h, float focal_multiplier, float* extrinsics_xf, float* new_intrinsics,
+                                        float* resample_xf, int* n_errors, void* stream) {
+  AT_REQUIRE(n_frames >= 0 && n_views >= 1 && n_pts >= 1, "at_gen_crop_matrices_f32: sizes");
+  AT_REQUIRE(crop_w > 1 && crop_h > 1, "at_gen_crop_matrices_f32: crop size");
+  if (n_frames == 0) return AT_OK;
+  AT_REQUIRE(orig_extrinsics && orig_intrinsics && crop_points && extrinsics_xf && new_intrinsics && resample_xf && n_errors,
+             "at_gen_crop_matrices_f32: NULL pointer");
+  const int64_t items = n_frames * n_views;
+  AT_REQUIRE(items <= 0x7fffffffLL, "at_gen_crop_matrices_f32: too many views");
+  const unsigned blocks = (unsigned)((items + kWarpsPerCta - 1) / kWarpsPerCta);
+  crop_matrices_kernel<<<blocks, kWarpsPerCta * 32, 0, (cudaStream_t)stream>>>(
+      orig_extrinsics, orig_intrinsics, crop_points, mirror_image, n_frames, n_views, n_pts, crop_w, crop_h,
+      focal_multiplier, 5.0f, extrinsics_xf, new_intrinsics, resample_xf, n_errors);
+  return at::check_launch("crop_matrices_kernel");
 }

@@ -1,0 +1,97 @@
+"""Perspective crops of config-3 sequences on the GPU (mirror of the arithmetic in the reference's
+lib/batched_dataset/data_transform.py:57-277).
+
+The reference's DataLoader workers build, per frame and view, a crop camera that looks at the hand
+(`_gen_crop_matrices`, :145-209, numpy + one Python call chain per view) and then resample all views
+of the sequence with a pinhole->pinhole homography (`_resample_images_batched`, :78-144).  Here both
+are one launch each for the whole sequence (C-ABI at_gen_crop_matrices_f32 and
+at_resample_homography_f32) and everything stays on the device.  The msgpack / .torch.idx readers in
+front of this are host IO and not part of this package.  There is no CPU path.
+"""
+from typing import List, Tuple
+
+import torch
+
+from ... import _cabi
+
+
+def _dev():
+    if not torch.cuda.is_available():
+        raise _cabi.AbsoluteTrackError("data_transform needs a CUDA device (no CPU fallback)")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _f32(a, dev):
+    return torch.as_tensor(a).to(device=dev, dtype=torch.float32).contiguous()
+
+
+def gen_crop_matrices_cuda(orig_extrinsics, orig_intrinsics, crop_points, mirror_image, crop_size: Tuple[int, int],
+                           focal_multiplier: float = 0.95):
+    """`_gen_crop_matrices` (:145-209) for a whole sequence.
+
+    orig_extrinsics [F,V,4,4] (world->eye), orig_intrinsics [F,V,3,3], crop_points [F,P,3],
+    mirror_image: bool or [F] bools.  Returns CUDA float32 (extrinsics_xf [F,V,4,4], new_intrinsics
+    [F,V,3,3], resample_xf [F,V,4,4]).  Raises ValueError("Unable to create crop camera") like
+    crop.py:25-26 when any view fails the reference's sanity checks (one 4-byte device read)."""
+    lib = _cabi.lib()
+    dev = _dev()
+    ext, intr, pts = _f32(orig_extrinsics, dev), _f32(orig_intrinsics, dev), _f32(crop_points, dev)
+    if ext.dim() != 4 or tuple(ext.shape[2:]) != (4, 4) or tuple(intr.shape) != tuple(ext.shape[:2]) + (3, 3):
+        raise ValueError(f"expected [F,V,4,4] extrinsics and [F,V,3,3] intrinsics, got {tuple(ext.shape)}, {tuple(intr.shape)}")
+    F, V = int(ext.shape[0]), int(ext.shape[1])
+    if pts.dim() != 3 or int(pts.shape[0]) != F or int(pts.shape[2]) != 3 or int(pts.shape[1]) < 1:
+        raise ValueError(f"expected [F,P,3] crop points, got {tuple(pts.shape)}")
+    if isinstance(mirror_image, (bool, int)):
+        mir = torch.full((F,), int(bool(mirror_image)), dtype=torch.uint8, device=dev)
+    else:
+        mir = torch.as_tensor(mirror_image).to(device=dev).ne(0).to(torch.uint8).reshape(F).contiguous()
+    out_e = torch.empty((F, V, 4, 4), dtype=torch.float32, device=dev)
+    out_k = torch.empty((F, V, 3, 3), dtype=torch.float32, device=dev)
+    out_x = torch.empty((F, V, 4, 4), dtype=torch.float32, device=dev)
+    err = torch.zeros(1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.at_gen_crop_matrices_f32(ext.data_ptr(), intr.data_ptr(), pts.data_ptr(), mir.data_ptr(), F, V,
+                                          int(pts.shape[1]), int(crop_size[0]), int(crop_size[1]), float(focal_multiplier),
+                                          out_e.data_ptr(), out_k.data_ptr(), out_x.data_ptr(), err.data_ptr(),
+                                          _cabi.stream_ptr(dev))
+    _cabi.check(rc, "at_gen_crop_matrices_f32")
+    n_err = int(err.item())
+    if n_err:
+        raise ValueError("Unable to create crop camera", n_err)
+    return out_e, out_k, out_x
+
+
+def resample_images_batched_cuda(images_orig, resample_xfs, out_size: Tuple[int, int], divisor: float = 1.0) -> torch.Tensor:
+    """`_resample_images_batched` (:78-144): images_orig [N,H,W] grey levels, resample_xfs [N,4,4]
+    -> float32 CUDA [N, out_size[1], out_size[0]] (rows = height), divided by `divisor`."""
+    lib = _cabi.lib()
+    dev = _dev()
+    img, xf = _f32(images_orig, dev), _f32(resample_xfs, dev)
+    if img.dim() != 3 or tuple(xf.shape) != (int(img.shape[0]), 4, 4):
+        raise ValueError(f"expected [N,H,W] images and [N,4,4] matrices, got {tuple(img.shape)}, {tuple(xf.shape)}")
+    n, H, W = (int(v) for v in img.shape)
+    ow, oh = int(out_size[0]), int(out_size[1])
+    out = torch.empty((n, oh, ow), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.at_resample_homography_f32(img.data_ptr(), n, H, W, xf.data_ptr(), oh, ow, out.data_ptr(), float(divisor),
+                                            _cabi.stream_ptr(dev))
+    _cabi.check(rc, "at_resample_homography_f32")
+    return out
+
+
+def _perspective_crop_images(orig_images, orig_extrinsics, orig_intrinsics, crop_points, hand_idx: int,
+                             crop_size: Tuple[int, int]) -> List[torch.Tensor]:
+    """The reference's `_perspective_crop_images` (:212-277), same arguments and return order:
+    [cropped_left_images [F,V,h,w] in 0..1, extrinsics_xf [F,V,4,4], new_intrinsics [F,V,3,3]] - as
+    CUDA float32 tensors, ready for the model (data_transform.py:348-356 wraps them with to_th)."""
+    dev = _dev()
+    img = _f32(orig_images, dev)
+    if img.dim() != 4:
+        raise ValueError(f"expected [F,V,H,W] images, got {tuple(img.shape)}")
+    F, V = int(img.shape[0]), int(img.shape[1])
+    ext, intr, xf = gen_crop_matrices_cuda(orig_extrinsics, orig_intrinsics, crop_points, int(hand_idx) == 1, crop_size)
+    if tuple(ext.shape[:2]) != (F, V):
+        raise ValueError("images and camera arrays disagree on [frames, views]")
+    crops = resample_images_batched_cuda(img.reshape(F * V, int(img.shape[2]), int(img.shape[3])), xf.reshape(F * V, 4, 4),
+                                         crop_size, 255.0)  # :275 normalises to 0..1
+    return [crops.reshape(F, V, int(crop_size[1]), int(crop_size[0])), ext, intr]

@@ -102,6 +102,23 @@ int at_crop_pull_source_boxes_u8(const uint8_t* src, uint8_t* dst, int64_t n_fra
                                  int n_crops, int dst_w, int dst_h, int max_ctas,
                                  unsigned long long* pulled_bytes, void* stream);
 
+/* Config-3 (torch_data) preprocessing on the device (the arithmetic of the loader).
+ * Replaces data_transform._gen_crop_matrices (lib/batched_dataset/data_transform.py:145-209) with
+ * crop.gen_crop_parameters_from_points (lib/common/crop.py:31-82) and _compute_resample_matrix
+ * (data_transform.py:57-75) for all n_frames * n_views pinhole views of a sequence in one launch:
+ *   orig_extrinsics [n_frames,n_views,4,4] f32 rigid world->eye, orig_intrinsics [..,3,3] f32 (fx, fy, cx, cy
+ *   are read), crop_points [n_frames,n_pts,3] f32, mirror_image uint8 [n_frames] (NULL = none; 1 = right
+ *   hand, data_transform.py:249), focal_multiplier 0.95 in the reference
+ *   -> extrinsics_xf [..,4,4] (world->eye of the crop camera), new_intrinsics [..,3,3], resample_xf [..,4,4]
+ *      (crop pixel -> original pixel: the `xfs` of at_resample_homography_f32), all f32.
+ * *n_errors (device int, accumulated) counts the views for which crop.py:25-26 raises
+ * ValueError("Unable to create crop camera"): a point closer than 1e-4 in front of the crop camera,
+ * or a focal below 5 px. */
+int at_gen_crop_matrices_f32(const float* orig_extrinsics, const float* orig_intrinsics, const float* crop_points,
+                             const uint8_t* mirror_image, int64_t n_frames, int n_views, int n_pts, int crop_w,
+                             int crop_h, float focal_multiplier, float* extrinsics_xf, float* new_intrinsics,
+                             float* resample_xf, int* n_errors, void* stream);
+
 /* The torch_data pinhole->pinhole resampler.  Replaces data_transform._resample_images_batched
  * (lib/batched_dataset/data_transform.py:78-144): (u,v,1) -> xf[0:3,0:3]*(u,v,1)+xf[0:3,3],
  * /z, mask 0<=x<W-1 & 0<=y<H-1, float bilinear, 0 outside.  images [n,H,W] f32, xfs [n,4,4] f32

@@ -1,6 +1,6 @@
 """Generate tests/golden/*.npz by running the UNMODIFIED reference in the build container.
 
-TEST INFRASTRUCTURE.  Run as `python oracle/make_golden.py [fk] [geometry] [warp] [cropcams] [eval] [model]`
+TEST INFRASTRUCTURE.  Run as `python oracle/make_golden.py [fk] [geometry] [warp] [cropcams] [cropmats] [eval] [model]`
 (no argument = all).  /root/reference is read-only and absent on the GPU box, so the
 outputs are committed; this script is the provenance record for every fixture.
 
@@ -22,6 +22,9 @@ Fixtures
                   pickles) and what the reference's load_eval._compute_metrics (:26-44) +
                   metric_utils.PCK_curve / normalized_AUC (:34-44,95-121) make of them per recording
                   and combined (aggregate_metrics :47-92): the README-style table.
+  crop_matrices.npz  reference data_transform._gen_crop_matrices (:145-209) on 40 seeded two-view
+                  frames (pinhole views, left and mirrored right hands) and
+                  _perspective_crop_images (:212-277) on 3 of them per hand (seeded images).
   model.npz       reference UmeTrackModel outputs (umetrack_model.py:188-242) for the seeded
                   state dict of absolutetrack_b200 `make_random_state_dict(0)`.
 """
@@ -142,6 +145,61 @@ def make_eval():
     np.savez_compressed(os.path.join(GOLD, "eval_user05.npz"), **out)
     print("eval_user05.npz", int(out["n_valid"]), "of", int(out["n_total"]), "mean error", float(out["mean_error"]),
           "auc", float(out["auc"]), "accel", float(out["mean_accel"]), float(out["mean_gt_accel"]))
+
+
+def cropmat_inputs(seed=11, n_frames=40, n_views=2, n_pts=21):
+    """Seeded config-3 style inputs in metres: world->eye of pinhole views around the origin, 3x3
+    intrinsics of 160x120 images, crop points ~0.35 m in front of the cameras."""
+    from scipy.spatial.transform import Rotation
+
+    rng = np.random.default_rng(seed)
+    ext = np.tile(np.eye(4, dtype=np.float32), (n_frames, n_views, 1, 1))
+    ext[..., :3, :3] = Rotation.from_rotvec(rng.normal(0, 0.25, (n_frames * n_views, 3))).as_matrix().reshape(n_frames, n_views, 3, 3)
+    ext[..., :3, 3] = rng.normal(0, 0.06, (n_frames, n_views, 3))
+    intr = np.tile(np.eye(3, dtype=np.float32), (n_frames, n_views, 1, 1))
+    intr[..., 0, 0] = rng.uniform(110, 190, (n_frames, n_views))
+    intr[..., 1, 1] = intr[..., 0, 0] * rng.uniform(0.97, 1.03, (n_frames, n_views))
+    intr[..., 0, 2] = 79.5 + rng.normal(0, 3, (n_frames, n_views))
+    intr[..., 1, 2] = 59.5 + rng.normal(0, 3, (n_frames, n_views))
+    ctr = np.array([0.0, 0.0, 0.35]) + rng.normal(0, 0.04, (n_frames, 1, 3))
+    pts = (ctr + rng.normal(0, 0.035, (n_frames, n_pts, 3))).astype(np.float32)
+    return ext, intr, pts
+
+
+def cropmat_images(seed, n, H=120, W=160):
+    out = np.empty((n, H, W), np.float32)
+    for i in range(n):
+        out[i] = synth_image("smooth" if i % 2 == 0 else "noise", seed + i, H, W)
+    return out
+
+
+def make_cropmats():
+    from lib.batched_dataset import data_transform as DT
+
+    ext, intr, pts = cropmat_inputs()
+    F, V = ext.shape[:2]
+    out = {"orig_extrinsics": ext, "orig_intrinsics": intr, "crop_points": pts}
+    for hand in (0, 1):
+        res = [DT._gen_crop_matrices(ext[f], intr[f], pts[f], hand == 1, (96, 96)) for f in range(F)]
+        out[f"h{hand}_extrinsics_xf"] = np.stack([r[0] for r in res])
+        out[f"h{hand}_new_intrinsics"] = np.stack([r[1] for r in res])
+        out[f"h{hand}_resample_xf"] = np.stack([r[2] for r in res])
+        imgs = cropmat_images(100 * hand, 3 * V).reshape(3, V, 120, 160)
+        crops, e2, i2 = DT._perspective_crop_images(imgs, ext[:3], intr[:3], pts[:3], hand, (96, 96))
+        assert np.array_equal(e2, out[f"h{hand}_extrinsics_xf"][:3]) and np.array_equal(i2, out[f"h{hand}_new_intrinsics"][:3])
+        out[f"h{hand}_crops"] = crops.astype(np.float32)
+        assert crops.dtype == np.float32 and crops.max() <= 1.0 and crops.max() > 0.5
+    # a point behind the new camera: the reference raises (crop.py:25-26)
+    bad = pts[0].copy()
+    bad[3] = -bad[3]
+    try:
+        DT._gen_crop_matrices(ext[0], intr[0], bad, False, (96, 96))
+        raise AssertionError("expected ValueError")
+    except ValueError:
+        pass
+    np.savez_compressed(os.path.join(GOLD, "crop_matrices.npz"), **out)
+    print("crop_matrices.npz", F, "frames x", V, "views x 2 hands; focal range",
+          float(out["h0_new_intrinsics"][..., 0, 0].min()), float(out["h0_new_intrinsics"][..., 0, 0].max()))
 
 
 def _frames():
@@ -290,11 +348,13 @@ def make_warp():
 
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
-    what = sys.argv[1:] or ["fk", "geometry", "warp", "cropcams", "eval", "model"]
+    what = sys.argv[1:] or ["fk", "geometry", "warp", "cropcams", "cropmats", "eval", "model"]
     if "fk" in what:
         make_fk()
     if "eval" in what:
         make_eval()
+    if "cropmats" in what:
+        make_cropmats()
     if "geometry" in what:
         make_geometry()
     if "cropcams" in what:

@@ -429,3 +429,36 @@ def eval_table(sums, thresholds=PCK_THRESHOLDS):
         mean_accel=sums["sum_accel"] / max(sums["n_accel"], 1),
         mean_gt_accel=sums["sum_gt_accel"] / max(sums["n_accel"], 1),
     )
+
+
+# --------------------------------------------------------------------------------------
+# config-3 preprocessing (lib/batched_dataset/data_transform.py:57-277)
+# --------------------------------------------------------------------------------------
+def gen_crop_matrices(orig_extrinsics, orig_intrinsics, crop_points, mirror_image, crop_size, focal_multiplier=0.95):
+    """data_transform._gen_crop_matrices (:145-209) + _compute_resample_matrix (:57-75): for every
+    pinhole view (world->eye [V,4,4], K [V,3,3]) the crop camera that looks at `crop_points`
+    -> (extrinsics_xf [V,4,4], new_intrinsics [V,3,3], resample_xf [V,4,4]) float32."""
+    V = orig_extrinsics.shape[0]
+    ext, K, xf = np.empty((V, 4, 4), np.float32), np.empty((V, 3, 3), np.float32), np.empty((V, 4, 4), np.float32)
+    for v in range(V):
+        c2w_orig = np.linalg.inv(orig_extrinsics[v])                      # :191 (float32 in, float32 out)
+        f, c, c2w_new = gen_crop_parameters_from_points(c2w_orig, crop_points, crop_size, mirror_image, 0, focal_multiplier)
+        ext[v] = np.linalg.inv(c2w_new)                                    # :203-204
+        Kn = np.array([[f[0], 0, c[0]], [0, f[1], c[1]], [0, 0, 1.0]])
+        K[v] = Kn
+        Ko44, Kni44 = np.eye(4), np.eye(4)
+        Ko44[:3, :3] = [[orig_intrinsics[v][0, 0], 0, orig_intrinsics[v][0, 2]],
+                        [0, orig_intrinsics[v][1, 1], orig_intrinsics[v][1, 2]], [0, 0, 1]]
+        Kni44[:3, :3] = np.linalg.inv(Kn)
+        xf[v] = (Ko44 @ np.linalg.inv(c2w_orig) @ c2w_new @ Kni44).astype(np.float32)  # :64-73
+    return ext, K, xf
+
+
+def perspective_crop_images(orig_images, orig_extrinsics, orig_intrinsics, crop_points, hand_idx, crop_size):
+    """data_transform._perspective_crop_images (:212-277): images [F,V,H,W] float32 grey levels ->
+    (crops [F,V,h,w] in 0..1, extrinsics_xf, new_intrinsics)."""
+    F, V = orig_images.shape[:2]
+    mats = [gen_crop_matrices(orig_extrinsics[f], orig_intrinsics[f], crop_points[f], hand_idx == 1, crop_size) for f in range(F)]
+    ext, K, xf = (np.stack([m[i] for m in mats]) for i in range(3))
+    crops = resample_homography(orig_images.reshape((F * V,) + orig_images.shape[2:]), xf.reshape(F * V, 4, 4), crop_size[::-1])
+    return (crops / 255).reshape(F, V, crop_size[1], crop_size[0]).astype(np.float32), ext, K

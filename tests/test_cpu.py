@@ -226,6 +226,28 @@ def test_oracle_eval_table_matches_reference_aggregation(gold):
     assert e["success_rate"] == 0.0 and np.isnan(e["mean_keypoint_error"]) and e["auc_score"] == 0.0
 
 
+def test_oracle_config3_crop_matrices_and_crops_match_reference_golden(gold):
+    """data_transform._gen_crop_matrices / _perspective_crop_images of the reference run here on 40
+    seeded two-view frames.  The reference mixes float32 and float64 (float32 numpy inverses of
+    float32 matrices); the restatement is float64 -> agreement to float32 round-off."""
+    G = gold["crop_matrices"]
+    ext, intr, pts = G["orig_extrinsics"], G["orig_intrinsics"], G["crop_points"]
+    for hand in (0, 1):
+        m = [O.gen_crop_matrices(ext[f], intr[f], pts[f], hand == 1, (96, 96)) for f in range(ext.shape[0])]
+        e, K, x = (np.stack([a[i] for a in m]) for i in range(3))
+        assert np.abs(e - G[f"h{hand}_extrinsics_xf"]).max() < 5e-7
+        assert np.allclose(K, G[f"h{hand}_new_intrinsics"], rtol=2e-6, atol=0)
+        assert np.abs(x - G[f"h{hand}_resample_xf"]).max() < 2e-6 * np.abs(x).max()
+        imgs = np.stack([scenario.synth_image("smooth" if i % 2 == 0 else "noise", 100 * hand + i, 120, 160) for i in range(6)])
+        crops, e3, K3 = O.perspective_crop_images(imgs.astype(np.float32).reshape(3, 2, 120, 160), ext[:3], intr[:3], pts[:3], hand, (96, 96))
+        d = np.abs(crops - G[f"h{hand}_crops"])
+        assert d.max() < 2e-3 and (G[f"h{hand}_crops"] > 0).mean() > 0.3   # 1e-4 px of map round-off on noise images
+    bad = pts[0].copy()
+    bad[3] = -bad[3]
+    with pytest.raises(ValueError):
+        O.gen_crop_matrices(ext[0], intr[0], bad, False, (96, 96))
+
+
 # ------------------------------------------------------------------ host logic
 def test_state_dict_spec_is_the_reference_key_set():
     from absolutetrack_b200.lib.models.model_loader import make_random_state_dict, pack_state_dict, state_dict_spec

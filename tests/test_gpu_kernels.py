@@ -395,3 +395,43 @@ def test_eval_recording_edge_cases(cuda_lib):
     z = torch.zeros(8, device="cuda")
     rc = _cabi.lib().at_eval_recording_f32(z.data_ptr(), z.data_ptr(), z.data_ptr(), 1, 1, None, 200, z.data_ptr(), z.data_ptr(), None)
     assert rc != 0 and "128" in _cabi.lib().at_last_error_string().decode()
+
+
+# ------------------------------------------------------------------ config-3 preprocessing (f3, GPU part)
+def test_config3_crop_matrices_and_crops_match_reference_golden(cuda_lib, gold):
+    """at_gen_crop_matrices_f32 + at_resample_homography_f32 through the data_transform mirror against
+    the reference's _gen_crop_matrices / _perspective_crop_images outputs (float32 round-off: the
+    reference inverts float32 matrices with numpy, the kernel works in float64)."""
+    from absolutetrack_b200.lib.batched_dataset import data_transform as DT
+
+    G = gold["crop_matrices"]
+    ext, intr, pts = G["orig_extrinsics"], G["orig_intrinsics"], G["crop_points"]
+    F = ext.shape[0]
+    for hand in (0, 1):
+        e, K, x = (t.cpu().numpy() for t in DT.gen_crop_matrices_cuda(ext, intr, pts, hand == 1, (96, 96)))
+        assert np.abs(e - G[f"h{hand}_extrinsics_xf"]).max() < 5e-7
+        assert np.allclose(K, G[f"h{hand}_new_intrinsics"], rtol=2e-6, atol=0)
+        assert np.abs(x - G[f"h{hand}_resample_xf"]).max() < 2e-6 * np.abs(x).max()
+        o = [O.gen_crop_matrices(ext[f], intr[f], pts[f], hand == 1, (96, 96)) for f in range(F)]
+        assert np.abs(x - np.stack([a[2] for a in o])).max() < 2e-6 * np.abs(x).max()
+        imgs = np.stack([scenario.synth_image("smooth" if i % 2 == 0 else "noise", 100 * hand + i, 120, 160) for i in range(6)])
+        crops, e3, K3 = DT._perspective_crop_images(imgs.astype(np.float32).reshape(3, 2, 120, 160), ext[:3], intr[:3], pts[:3], hand, (96, 96))
+        assert crops.is_cuda and tuple(crops.shape) == (3, 2, 96, 96)
+        assert np.abs(crops.cpu().numpy() - G[f"h{hand}_crops"]).max() < 2e-3
+        assert np.array_equal(e3.cpu().numpy(), e[:3]) and np.array_equal(K3.cpu().numpy(), K[:3])
+    # per-frame mirror flags = the two uniform calls interleaved
+    flags = np.arange(F) % 2 == 1
+    e, K, x = (t.cpu().numpy() for t in DT.gen_crop_matrices_cuda(ext, intr, pts, flags, (96, 96)))
+    for hand in (0, 1):
+        ref = DT.gen_crop_matrices_cuda(ext, intr, pts, hand == 1, (96, 96))[2].cpu().numpy()
+        assert np.array_equal(x[flags == (hand == 1)], ref[flags == (hand == 1)])
+    # crop.py:25-26: a point behind the crop camera -> ValueError, as in the reference
+    bad = pts.copy()
+    bad[7, 3] = -bad[7, 3]
+    with pytest.raises(ValueError, match="Unable to create crop camera"):
+        DT.gen_crop_matrices_cuda(ext, intr, bad, False, (96, 96))
+    # empty sequence / shape errors
+    e, K, x = DT.gen_crop_matrices_cuda(ext[:0], intr[:0], pts[:0], False, (96, 96))
+    assert tuple(x.shape) == (0, 2, 4, 4)
+    with pytest.raises(ValueError):
+        DT.gen_crop_matrices_cuda(ext, intr[:, :1], pts, False, (96, 96))

@@ -46,6 +46,17 @@ L = []
 for r in rows[hi + 1:]:
     v = float(r[vi].replace(",", ""))
     L.append((r[ki], v / 1e3 if r[ui] == "ns" else v))
+# the launch list itself, compacted (id, kernel, grid, block, duration)
+gi, bi = hdr.index("Grid Size"), hdr.index("Block Size")
+with open(P + f"{R}_bench_launch_list.csv", "w") as f:
+    f.write("# ncu --metrics gpu__time_duration.sum --clock-control none -c 2500, python bench.py --steps 2 --warmup 3 "
+            "--no-cpu-baseline: every launch of the command (kernel names shortened)\n")
+    f.write("id,kernel,grid,block,duration_us\n")
+    for n_, r in enumerate(rows[hi + 1:]):
+        k = r[ki].split("(")[0].replace("void ", "").replace("at::<unnamed>::", "").replace("<unnamed>::", "").replace("at::", "")
+        if "native::" in k:
+            k = "torch:" + k.split("native::")[1].split("<")[0]
+        f.write(f'{n_},"{k}","{r[gi]}","{r[bi]}",{L[n_][1]:.2f}\n')
 idx = [i for i, (k, v) in enumerate(L) if "crop_resample_" in k]
 a, b = idx[3], idx[4]
 

@@ -171,6 +171,7 @@ SIGNATURES = {
     "at_resample_homography_f32": (_I, [_VP, _I, _I, _I, _VP, _I, _I, _VP, _F, _VP]),
     "at_gen_crop_matrices_f32": (_I, [_VP, _VP, _VP, _VP, _I64, _I, _I, _I, _I, _F, _VP, _VP, _VP, _VP, _VP]),
     "at_fk_skin_f32": (_I, [_VP, _VP, _VP, C.POINTER(AtHandModel), _I64, _VP, _VP]),
+    "at_fk_skin_scaled_f32": (_I, [_VP, _VP, _VP, C.POINTER(AtHandModel), _I64, _F, _VP, _VP, _VP]),
     "at_eval_accumulate_f32": (_I, [_VP, _VP, _VP, _VP, _VP, _I64, _VP, _VP]),
     "at_eval_recording_f32": (_I, [_VP, _VP, _VP, _I64, _I64, _VP, _I, _VP, _VP, _VP]),
     "at_crop_cameras_workspace_bytes": (_I64, [_I, _I]),

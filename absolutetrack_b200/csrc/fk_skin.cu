@@ -37,7 +37,8 @@ __device__ __forceinline__ void store_frame(float* __restrict__ s, int frame, co
 __global__ void __launch_bounds__(kBlock) fk_skin_kernel(const float* __restrict__ joint_angles,
                                                          const float* __restrict__ wrist,
                                                          const int64_t* __restrict__ hand_idx, AtHandModel m,
-                                                         int64_t n, float* __restrict__ landmarks) {
+                                                         int64_t n, float* __restrict__ landmarks, float tscale,
+                                                         float* __restrict__ wrist_out) {
   extern __shared__ float smem[];
   const int64_t base = (int64_t)blockIdx.x * kBlock;
   const int64_t h = base + threadIdx.x;
@@ -57,11 +58,16 @@ __global__ void __launch_bounds__(kBlock) fk_skin_kernel(const float* __restrict
       W.r[i * 3 + 0] = sgn * wp[i * 4 + 0];
       W.r[i * 3 + 1] = wp[i * 4 + 1];
       W.r[i * 3 + 2] = wp[i * 4 + 2];
-      W.t[i] = wp[i * 4 + 3];
+      W.t[i] = wp[i * 4 + 3] * tscale;
+    }
+    if (wrist_out != nullptr) {  // the input transform with its translation in the output unit
+      float* wo = wrist_out + h * 16;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) wo[i] = (i < 12 && (i & 3) == 3) ? wp[i] * tscale : wp[i];
     }
     store_frame(smem, 0, W);
     store_frame(smem, 1, W);
-#pragma unroll 1  // (fully unrolled: 0.414 instead of 0.439 of HBM at 4M hands - instruction cache)
+#pragma unroll 1
     for (int f = 0; f < 5; ++f) {
       Xf cur = W;
 #pragma unroll
@@ -162,7 +168,8 @@ __device__ __forceinline__ void emit_frame(const FastTables& tb, float* __restri
 __global__ void __launch_bounds__(kFast, 3) fk_skin_shared_kernel(const float* __restrict__ joint_angles,
                                                                   const float* __restrict__ wrist,
                                                                   const int64_t* __restrict__ hand_idx, AtHandModel m,
-                                                                  int64_t n, float* __restrict__ landmarks) {
+                                                                  int64_t n, float* __restrict__ landmarks, float tscale,
+                                                                  float* __restrict__ wrist_out) {
   extern __shared__ __align__(16) float smem[];
   __shared__ FastTables tb;
   __shared__ int s_b[64];
@@ -229,6 +236,7 @@ __global__ void __launch_bounds__(kFast, 3) fk_skin_shared_kernel(const float* _
   }
   // tile bases are multiples of 16 B (256 hands x 88 / 64 / 252 B), so alignment depends on the pointers only
   const bool vec_ok = (((uintptr_t)joint_angles | (uintptr_t)wrist | (uintptr_t)landmarks) & 15) == 0;
+  const bool wo_vec = ((uintptr_t)wrist_out & 15) == 0;
   // ---- persistent loop over tiles of kFast hands (the tables above are built once per CTA)
   const int64_t n_tiles = (n + kFast - 1) / kFast;
   for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -267,7 +275,17 @@ __global__ void __launch_bounds__(kFast, 3) fk_skin_shared_kernel(const float* _
       float4 r;
       if (vec_ok) r = __ldg(reinterpret_cast<const float4*>(gw) + i);
       else r = make_float4(__ldg(gw + 4 * i), __ldg(gw + 4 * i + 1), __ldg(gw + 4 * i + 2), __ldg(gw + 4 * i + 3));
+      r.w *= tscale;
       W.r[i * 3 + 0] = sgn * r.x; W.r[i * 3 + 1] = r.y; W.r[i * 3 + 2] = r.z; W.t[i] = r.w;
+      if (wrist_out != nullptr) {
+        float* wo = wrist_out + (base + tid) * 16 + 4 * i;
+        if (wo_vec) *reinterpret_cast<float4*>(wo) = r;
+        else { wo[0] = r.x; wo[1] = r.y; wo[2] = r.z; wo[3] = r.w; }
+      }
+    }
+    if (wrist_out != nullptr) {
+      float* wo = wrist_out + (base + tid) * 16 + 12;
+      wo[0] = __ldg(gw + 12); wo[1] = __ldg(gw + 13); wo[2] = __ldg(gw + 14); wo[3] = __ldg(gw + 15);
     }
   }
   __syncthreads();  // inputs are in registers: the buffer becomes the flat [hands][63] landmark accumulator
@@ -487,8 +505,18 @@ extern "C" int at_eval_accumulate_f32(const float* landmarks, const float* gt_la
   return at::check_launch("eval_accumulate_kernel");
 }
 
+extern "C" int at_fk_skin_scaled_f32(const float* joint_angles, const float* wrist_xforms, const int64_t* hand_idx,
+                                     const AtHandModel* model, int64_t n, float translation_scale, float* wrist_out,
+                                     float* landmarks, void* stream);
+
 extern "C" int at_fk_skin_f32(const float* joint_angles, const float* wrist_xforms, const int64_t* hand_idx,
                               const AtHandModel* model, int64_t n, float* landmarks, void* stream) {
+  return at_fk_skin_scaled_f32(joint_angles, wrist_xforms, hand_idx, model, n, 1.0f, nullptr, landmarks, stream);
+}
+
+extern "C" int at_fk_skin_scaled_f32(const float* joint_angles, const float* wrist_xforms, const int64_t* hand_idx,
+                                     const AtHandModel* model, int64_t n, float translation_scale, float* wrist_out,
+                                     float* landmarks, void* stream) {
   AT_REQUIRE(model != nullptr, "at_fk_skin_f32: model is NULL");
   AT_REQUIRE(n >= 0, "at_fk_skin_f32: n < 0");
   if (n == 0) return AT_OK;
@@ -512,13 +540,13 @@ extern "C" int at_fk_skin_f32(const float* joint_angles, const float* wrist_xfor
       fast_attr = true;
     }
     const int64_t fb = std::min<int64_t>((n + kFast - 1) / kFast, 3 * at::kNumSMs);  // persistent: 3 CTAs per SM
-    fk_skin_shared_kernel<<<(unsigned)fb, kFast, fast_smem, (cudaStream_t)stream>>>(joint_angles, wrist_xforms, hand_idx,
-                                                                                     *model, n, landmarks);
+    fk_skin_shared_kernel<<<(unsigned)fb, kFast, fast_smem, (cudaStream_t)stream>>>(
+        joint_angles, wrist_xforms, hand_idx, *model, n, landmarks, translation_scale, wrist_out);
     return at::check_launch("fk_skin_shared_kernel");
   }
   const int64_t blocks = (n + kBlock - 1) / kBlock;
   AT_REQUIRE(blocks <= 0x7fffffffLL, "at_fk_skin_f32: n too large");
   fk_skin_kernel<<<(unsigned)blocks, kBlock, smem_bytes, (cudaStream_t)stream>>>(
-      joint_angles, wrist_xforms, hand_idx, *model, n, landmarks);
+      joint_angles, wrist_xforms, hand_idx, *model, n, landmarks, translation_scale, wrist_out);
   return at::check_launch("fk_skin_kernel");
 }

@@ -17,10 +17,13 @@ def _device_for(*tensors):
     return torch.device("cuda", torch.cuda.current_device())
 
 
-def skin_landmarks_cuda(hand_model: HandModel, joint_angles, wrist_transforms, hand_idx=None, out=None):
+def skin_landmarks_cuda(hand_model: HandModel, joint_angles, wrist_transforms, hand_idx=None, out=None,
+                        translation_scale: float = 1.0, wrist_out=None):
     """Device-resident entry: all inputs are moved to the GPU if they are not there already;
     returns a CUDA tensor [..., 21, 3].  `hand_idx` (optional, [...]) mirrors right hands
-    (perspective_crop.py:46-48) inside the kernel."""
+    (perspective_crop.py:46-48) inside the kernel.  `translation_scale` multiplies the wrist
+    translations first (tracker.py:379, metres -> mm) and `wrist_out` (CUDA float32 [n,4,4],
+    contiguous, not the input) receives the scaled transforms - both inside the same launch."""
     lib = _cabi.lib()
     lead = tuple(joint_angles.shape[:-1])
     n = 1
@@ -49,11 +52,16 @@ def skin_landmarks_cuda(hand_model: HandModel, joint_angles, wrist_transforms, h
     hm = _cabi.AtHandModel(
         axes.data_ptr(), rest.data_ptr(), lms.data_ptr(), bw.data_ptr(), bi.data_ptr(), K, 1 if per_sample else 0
     )
+    if wrist_out is not None:
+        if not (wrist_out.is_cuda and wrist_out.dtype == torch.float32 and wrist_out.is_contiguous()
+                and wrist_out.numel() == n * 16 and wrist_out.data_ptr() != wx.data_ptr()):
+            raise _cabi.AbsoluteTrackError("wrist_out: contiguous CUDA float32 [n,4,4], distinct from the input")
     with torch.cuda.device(dev):
-        rc = lib.at_fk_skin_f32(
-            ja.data_ptr(), wx.data_ptr(), _cabi.ptr(hi), hm, n, out.data_ptr(), _cabi.stream_ptr(dev)
+        rc = lib.at_fk_skin_scaled_f32(
+            ja.data_ptr(), wx.data_ptr(), _cabi.ptr(hi), hm, n, float(translation_scale), _cabi.ptr(wrist_out),
+            out.data_ptr(), _cabi.stream_ptr(dev)
         )
-    _cabi.check(rc, "at_fk_skin_f32")
+    _cabi.check(rc, "at_fk_skin_scaled_f32")
     return out.reshape(lead + (21, 3))
 
 

@@ -203,7 +203,11 @@ class UmeTrackModel(nn.Module):
         extr = frame_data.extrinsics_xf.to(**f32).contiguous()
         srange = frame_desc.sample_range.to(**i64).contiguous()
         midx = frame_desc.memory_idx.to(**i64).contiguous()
-        usem = frame_desc.use_memory.to(device=dev, dtype=torch.uint8).contiguous()
+        usem = frame_desc.use_memory
+        if usem.dtype == torch.bool and usem.device == dev and usem.is_contiguous():
+            usem = usem.view(torch.uint8)  # same bytes: no conversion launch
+        else:
+            usem = usem.to(device=dev, dtype=torch.uint8).contiguous()
         hidx = frame_desc.hand_idx.to(**i64).contiguous()
         n = srange.shape[0]
         if self.memory_capacity_hint is not None:

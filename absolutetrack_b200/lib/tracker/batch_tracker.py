@@ -123,6 +123,9 @@ class BatchedHandTracker:
         self._hm_dev = HandModel(*[
             (v.to(self._device) if isinstance(v, torch.Tensor) else v) for v in hand_model_mm
         ])
+        # the dtypes at_fk_skin_f32 takes, so that skin_landmarks_cuda converts nothing per step
+        self._hm_dev = self._hm_dev._replace(
+            landmark_rest_bone_indices=self._hm_dev.landmark_rest_bone_indices.to(torch.int32).contiguous())
         # host->device ingest: a copy stream and two device staging slots, so that the H2D copy of
         # step i+1 overlaps the kernels of step i (frames are 1.22 MB each: ingest is the e2e bound)
         if ingest not in ("pull", "zero_copy", "copy"):
@@ -158,14 +161,12 @@ class BatchedHandTracker:
             InputFrameDesc(b.sample_range, b.memory_idx, b.use_memory, b.hand_idx),
             self._skel,
         )
-        if getattr(self, "_mm_scale", None) is None:  # metres -> millimetres on the translation column, one launch
-            sc = torch.ones(4, 4, device=self._device)
-            sc[:3, 3] = M_TO_MM
-            self._mm_scale = sc
-        wrist_mm = out.wrist_xfs * self._mm_scale
-        # the model already mirrored right hands (umetrack_model.py:88-89); landmarks_from_hand_pose
+        # metres -> millimetres on the wrist translations (tracker.py:379) inside the FK launch.
+        # The model already mirrored right hands (umetrack_model.py:88-89); landmarks_from_hand_pose
         # mirrors them back before FK (perspective_crop.py:46-48) -> hand_idx does that in-kernel
-        lm = skin_landmarks_cuda(self._hm_dev, out.joint_angles, wrist_mm, hand_idx=b.hand_idx)
+        wrist_mm = torch.empty_like(out.wrist_xfs)
+        lm = skin_landmarks_cuda(self._hm_dev, out.joint_angles, out.wrist_xfs, hand_idx=b.hand_idx,
+                                 translation_scale=M_TO_MM, wrist_out=wrist_mm)
         return BatchResult(out.joint_angles, wrist_mm, lm)
 
     def step(self, host_batch: FrameBatch, out_host: Optional[dict] = None) -> dict:

@@ -150,6 +150,15 @@ typedef struct AtHandModel {
 int at_fk_skin_f32(const float* joint_angles, const float* wrist_xforms, const int64_t* hand_idx,
                    const AtHandModel* model, int64_t n, float* landmarks, void* stream);
 
+/* The same with the unit change of the tracker folded in: HandTracker._track_frame turns the model's
+ * wrist transforms from metres into millimetres (tracker.py:34,379: output_wrist_xforms[..., :3, 3] *=
+ * M_TO_MM) before anything downstream uses them.  The translation column of every wrist transform is multiplied by translation_scale
+ * before use, and the scaled transforms are written to wrist_out [n,4,4] when it is not NULL
+ * (wrist_out must not overlap wrist_xforms).  translation_scale = 1, wrist_out = NULL is at_fk_skin_f32. */
+int at_fk_skin_scaled_f32(const float* joint_angles, const float* wrist_xforms, const int64_t* hand_idx,
+                          const AtHandModel* model, int64_t n, float translation_scale, float* wrist_out,
+                          float* landmarks, void* stream);
+
 /* Evaluation sums on the device.  Replaces the per-frame bookkeeping of
  * run_eval_known_skeleton.py:92-93 (mean keypoint error of a hand-frame) for a batch:
  *   sums[0] += sum over valid hands of mean_l |landmarks[h,l] - gt_landmarks[h,l]|   (input units, mm)

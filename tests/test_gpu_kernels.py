@@ -120,6 +120,37 @@ def test_fk_ragged_tiles_and_unaligned_pointers(cuda_lib, gold):
             assert bool((bo[:off] == -7.0).all()) and bool((bo[off + n * 63:] == -7.0).all())  # nothing outside
 
 
+def test_fk_scaled_entry_folds_the_metre_to_mm_step(cuda_lib, gold):
+    """at_fk_skin_scaled_f32 = scale the wrist translations (tracker.py:379), then at_fk_skin_f32;
+    the scaled transforms come back in the same launch.  Bit-identical to doing it in two steps."""
+    from absolutetrack_b200.lib.common.hand_skinning import skin_landmarks_cuda
+
+    hm = _hand_model_tuple(gold["geometry"], "hm_")
+    rng = np.random.default_rng(9)
+    n = 700
+    ja = torch.from_numpy(rng.uniform(-1.2, 1.2, (n, 22)).astype(np.float32)).cuda()
+    wx = np.tile(np.eye(4, dtype=np.float32), (n, 1, 1))
+    wx[:, :3, :3] = O.so3_exp_map_f32(rng.normal(0, 1, (n, 3)).astype(np.float32))
+    wx[:, :3, 3] = rng.normal(0, 0.3, (n, 3))
+    wx = torch.from_numpy(wx).cuda()
+    hidx = torch.from_numpy(rng.integers(0, 2, n)).cuda()
+    scaled = wx.clone()
+    scaled[:, :3, 3] *= 1000.0
+    per_sample = hm._replace(**{k: getattr(hm, k).expand((n,) + tuple(getattr(hm, k).shape)).contiguous() for k in
+                                ("joint_rotation_axes", "joint_rest_positions", "landmark_rest_positions",
+                                 "landmark_rest_bone_weights", "landmark_rest_bone_indices")})
+    for model in (hm, per_sample):
+        ref = skin_landmarks_cuda(model, ja, scaled, hand_idx=hidx)
+        for off in (0, 1):  # 16-byte aligned and 4-byte aligned wrist_out
+            buf = torch.full((n * 16 + 4,), -3.0, device="cuda")
+            wo = buf[off:off + n * 16].view(n, 4, 4)
+            lm = skin_landmarks_cuda(model, ja, wx, hand_idx=hidx, translation_scale=1000.0, wrist_out=wo)
+            assert torch.equal(lm, ref) and torch.equal(wo, scaled)
+            assert bool((buf[:off] == -3.0).all()) and bool((buf[off + n * 16:] == -3.0).all())
+    with pytest.raises(Exception):
+        skin_landmarks_cuda(hm, ja, wx, wrist_out=wx)  # in place is refused
+
+
 def test_fk_empty_batch(cuda_lib, gold):
     from absolutetrack_b200.lib.common.hand_skinning import skin_landmarks_cuda
 

@@ -1,5 +1,6 @@
 // Shared helpers for the absolutetrack_b200 CUDA sources (sm_100a only).
 #pragma once
+#include <atomic>
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
@@ -38,18 +39,30 @@ constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
 // can only switch configuration when it is empty: with a pull CTA resident, the first conv launch
 // that wants a different carve-out stalls until that CTA exits (measured: the encoder blocked for
 // the whole pull; scripts/overlap_probe.cu).  Kernels outside that window keep the default (more L1).
+// Function attributes belong to a device's context: "once" means once per device, and callers may
+// come from several threads.  `mask` holds one bit per device ordinal.
+inline uint64_t this_device_bit() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return 1ull << (dev & 63);
+}
+// the statements are idempotent attribute calls: two racing first callers may both run them, nobody
+// launches before they have run
+#define AT_ONCE_PER_DEVICE(...)                                    \
+  do {                                                             \
+    static std::atomic<uint64_t> at_once_mask_{0};                 \
+    const uint64_t at_bit_ = at::this_device_bit();                \
+    if ((at_once_mask_.load(std::memory_order_acquire) & at_bit_) == 0) { \
+      __VA_ARGS__;                                                 \
+      at_once_mask_.fetch_or(at_bit_, std::memory_order_release);  \
+    }                                                              \
+  } while (0)
+
 template <typename K>
 inline void prefer_max_smem_carveout(K kernel) {
   cudaFuncSetAttribute((const void*)kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
 }
-#define AT_CARVEOUT_ONCE(kernel)                                   \
-  do {                                                             \
-    static const bool at_carve_done_ = [] {                        \
-      at::prefer_max_smem_carveout(kernel);                        \
-      return true;                                                 \
-    }();                                                           \
-    (void)at_carve_done_;                                          \
-  } while (0)
+#define AT_CARVEOUT_ONCE(kernel) AT_ONCE_PER_DEVICE(at::prefer_max_smem_carveout(kernel))
 
 __host__ __device__ inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
 

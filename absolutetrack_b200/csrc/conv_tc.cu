@@ -28,6 +28,7 @@
 #include <mutex>
 #include <stdlib.h>
 #include <string.h>
+#include <utility>
 #include <vector>
 
 #include "conv.cuh"
@@ -1068,16 +1069,19 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   }
   {
     static std::mutex mu;
-    static std::vector<Kernel> configured;
+    static std::vector<std::pair<int, Kernel>> configured;  // function attributes are per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const std::pair<int, Kernel> key(dev, fn);
     std::lock_guard<std::mutex> lock(mu);
-    if (std::find(configured.begin(), configured.end(), fn) == configured.end()) {
+    if (std::find(configured.begin(), configured.end(), key) == configured.end()) {
       cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget + 4096);
       if (e == cudaSuccess) e = cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
       if (e != cudaSuccess) {
         set_error("cudaFuncSetAttribute(conv_tc_kernel): %s", cudaGetErrorString(e));
         return AT_ERR_CUDA;
       }
-      configured.push_back(fn);
+      configured.push_back(key);
     }
   }
   {

@@ -878,21 +878,15 @@ extern "C" int at_crop_resample_fisheye62_u8_ex(const uint8_t* src, int64_t fram
   } else if (dst_w % kLatSeg == 0 && dst_h % kLatStep == 0 && dst_w <= 96 && dst_h <= 96 &&
              (getenv("AT_CROP_LATTICE") == nullptr || atoi(getenv("AT_CROP_LATTICE")) != 0)) {
     // the model's crop size: bicubic lattice map + staged gather, for device and pinned-host sources alike
-    static bool attr = false;
-    if (!attr) {
-      cudaFuncSetAttribute(crop_resample_lattice_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kLatStageBytes);
-      cudaFuncSetAttribute(crop_resample_lattice_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-      attr = true;
-    }
+    AT_ONCE_PER_DEVICE(
+        cudaFuncSetAttribute(crop_resample_lattice_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kLatStageBytes);
+        cudaFuncSetAttribute(crop_resample_lattice_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     crop_resample_lattice_kernel<<<(unsigned)n_crops, kThreads, kLatStageBytes, (cudaStream_t)stream>>>(
         src, frame_stride, view_stride, row_stride, params, dst_w, dst_h, out, out_dtype, staged_bytes);
   } else if (dst_w % kFastPx == 0 && (src_on_host || staged_bytes != nullptr || getenv("AT_CROP_STAGED") != nullptr)) {
-    static bool attr = false;
-    if (!attr) {
-      cudaFuncSetAttribute(crop_resample_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStageBytes);
-      cudaFuncSetAttribute(crop_resample_staged_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-      attr = true;
-    }
+    AT_ONCE_PER_DEVICE(
+        cudaFuncSetAttribute(crop_resample_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStageBytes);
+        cudaFuncSetAttribute(crop_resample_staged_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     crop_resample_staged_kernel<<<(unsigned)n_crops, kThreads, kStageBytes, (cudaStream_t)stream>>>(
         src, frame_stride, view_stride, row_stride, params, dst_w, dst_h, out, out_dtype, staged_bytes);
   } else if (dst_w % kFastPx == 0) {

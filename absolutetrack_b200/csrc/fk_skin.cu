@@ -525,20 +525,13 @@ extern "C" int at_fk_skin_scaled_f32(const float* joint_angles, const float* wri
                  model->landmark_rest_bone_weights && model->landmark_rest_bone_indices,
              "at_fk_skin_f32: NULL hand-model pointer");
   AT_REQUIRE(model->n_weights >= 1 && model->n_weights <= 8, "at_fk_skin_f32: n_weights out of range");
-  static bool attr_set = false;
   const int smem_bytes = kSmemFloats * (int)sizeof(float);
-  if (!attr_set) {
-    cudaFuncSetAttribute(fk_skin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
-    attr_set = true;
-  }
+  AT_ONCE_PER_DEVICE(cudaFuncSetAttribute(fk_skin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   if (!model->per_sample && model->n_weights <= 3) {
     constexpr int fast_smem = kOutFloats * (int)sizeof(float);
-    static bool fast_attr = false;
-    if (!fast_attr) {
-      cudaFuncSetAttribute(fk_skin_shared_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fast_smem);
-      cudaFuncSetAttribute(fk_skin_shared_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-      fast_attr = true;
-    }
+    AT_ONCE_PER_DEVICE(
+        cudaFuncSetAttribute(fk_skin_shared_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fast_smem);
+        cudaFuncSetAttribute(fk_skin_shared_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     const int64_t fb = std::min<int64_t>((n + kFast - 1) / kFast, 3 * at::kNumSMs);  // persistent: 3 CTAs per SM
     fk_skin_shared_kernel<<<(unsigned)fb, kFast, fast_smem, (cudaStream_t)stream>>>(
         joint_angles, wrist_xforms, hand_idx, *model, n, landmarks, translation_scale, wrist_out);

@@ -128,9 +128,11 @@ __global__ void __launch_bounds__(kBlock) fk_skin_kernel(const float* __restrict
 // (identical to so3_exp_map(axis*angle) of hand_skinning.py:46).  The 17 frames never leave
 // registers: landmarks are visited frame by frame through a CSR table built once per CTA
 // (bone index -> landmarks) and accumulated in shared memory, which doubles as the staging buffer
-// for 16-byte input loads and output stores.  252 B of shared memory per hand -> 3 CTAs x 256
-// threads per SM.
-constexpr int kFast = 256;  // hands per CTA
+// for 16-byte input loads and output stores.  252 B of shared memory and 80 registers per hand -> 768 hands per
+// SM, run as 8 CTAs of 96 (small CTAs: while one copies its tile in or out, seven compute; measured
+// 0.438 / 0.456 / 0.472 / 0.477 of HBM at 3 x 256 / 4 x 192 / 6 x 128 / 8 x 96).
+constexpr int kFast = 96;   // hands per CTA (>= 96: threads 0..19 and the last 64 build the tables)
+constexpr int kFastCtas = 8; // per SM: 8 x 24.2 KB of shared memory, 8 x 96 x 80 registers
 // shared buffer: first the flat [hands][22] joint-angle stage, then the flat [hands][63] landmark
 // accumulator = the exact global layout, so both copies are straight 16-byte moves; the per-thread
 // rows have odd (63) / 8-byte-friendly (22) strides -> conflict-free LDS.64 / STS.32
@@ -165,7 +167,7 @@ __device__ __forceinline__ void emit_frame(const FastTables& tb, float* __restri
   }
 }
 
-__global__ void __launch_bounds__(kFast, 3) fk_skin_shared_kernel(const float* __restrict__ joint_angles,
+__global__ void __launch_bounds__(kFast, kFastCtas) fk_skin_shared_kernel(const float* __restrict__ joint_angles,
                                                                   const float* __restrict__ wrist,
                                                                   const int64_t* __restrict__ hand_idx, AtHandModel m,
                                                                   int64_t n, float* __restrict__ landmarks, float tscale,
@@ -196,8 +198,8 @@ __global__ void __launch_bounds__(kFast, 3) fk_skin_shared_kernel(const float* _
     J.v[4] = make_float4(k2x, k2y, k2z, 0.f);
     J.v[5] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  if (tid >= 128 && tid < 128 + 64) {
-    const int e = tid - 128;
+  if (tid >= kFast - 64) {  // the last 64 threads build the CSR table (threads 0..19: joint constants)
+    const int e = tid - (kFast - 64);
     int valid = 0, b = 0;
     if (e < npairs) {
       valid = m.landmark_rest_bone_weights[e] != 0.0f;   // zero weights dropped (hand_skinning.py:92-94)
@@ -207,8 +209,8 @@ __global__ void __launch_bounds__(kFast, 3) fk_skin_shared_kernel(const float* _
     s_valid[e] = valid;
   }
   __syncthreads();
-  if (tid >= 128 && tid < 128 + 64) {
-    const int e = tid - 128;
+  if (tid >= kFast - 64) {  // the last 64 threads build the CSR table (threads 0..19: joint constants)
+    const int e = tid - (kFast - 64);
     if (e < npairs && s_valid[e]) {
       const int b = s_b[e], l = e / K;
       int pos = 0, first = 1;
@@ -234,7 +236,7 @@ __global__ void __launch_bounds__(kFast, 3) fk_skin_shared_kernel(const float* _
       tb.lm_has[e] = any;
     }
   }
-  // tile bases are multiples of 16 B (256 hands x 88 / 64 / 252 B), so alignment depends on the pointers only
+  // tile bases are multiples of 16 B (96 hands x 88 / 64 / 252 B), so alignment depends on the pointers only
   const bool vec_ok = (((uintptr_t)joint_angles | (uintptr_t)wrist | (uintptr_t)landmarks) & 15) == 0;
   const bool wo_vec = ((uintptr_t)wrist_out & 15) == 0;
   // ---- persistent loop over tiles of kFast hands (the tables above are built once per CTA)
@@ -532,7 +534,7 @@ extern "C" int at_fk_skin_scaled_f32(const float* joint_angles, const float* wri
     AT_ONCE_PER_DEVICE(
         cudaFuncSetAttribute(fk_skin_shared_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fast_smem);
         cudaFuncSetAttribute(fk_skin_shared_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-    const int64_t fb = std::min<int64_t>((n + kFast - 1) / kFast, 3 * at::kNumSMs);  // persistent: 3 CTAs per SM
+    const int64_t fb = std::min<int64_t>((n + kFast - 1) / kFast, kFastCtas * at::kNumSMs);  // persistent
     fk_skin_shared_kernel<<<(unsigned)fb, kFast, fast_smem, (cudaStream_t)stream>>>(
         joint_angles, wrist_xforms, hand_idx, *model, n, landmarks, translation_scale, wrist_out);
     return at::check_launch("fk_skin_shared_kernel");

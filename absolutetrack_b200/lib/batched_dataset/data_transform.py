@@ -10,6 +10,7 @@ front of this are host IO and not part of this package.  There is no CPU path.
 """
 from typing import List, Tuple
 
+import numpy as np
 import torch
 
 from ... import _cabi
@@ -95,3 +96,87 @@ def _perspective_crop_images(orig_images, orig_extrinsics, orig_intrinsics, crop
     crops = resample_images_batched_cuda(img.reshape(F * V, int(img.shape[2]), int(img.shape[3])), xf.reshape(F * V, 4, 4),
                                          crop_size, 255.0)  # :275 normalises to 0..1
     return [crops.reshape(F, V, int(crop_size[1]), int(crop_size[0])), ext, intr]
+
+
+# --------------------------------------------------------------------------------------------
+# sequence -> model input / targets (data_transform.py:23-54,280-397)
+# --------------------------------------------------------------------------------------------
+from dataclasses import dataclass  # noqa: E402
+from typing import Any, Dict, Optional  # noqa: E402
+
+from ..common.hand import HandModel, mirrored_hand_model  # noqa: E402
+from ..data_utils import bundles  # noqa: E402
+from .sample import RawSample, parse_raw_buffers  # noqa: E402
+
+
+@dataclass
+class PoseData:
+    joint_angles: torch.Tensor
+    wrist_xfs: torch.Tensor
+    left_hand_model: HandModel
+
+
+@dataclass
+class ModelInput:
+    orig_pose_data: PoseData
+    s_solved_pose_data: PoseData
+    left_images: torch.Tensor
+    intrinsics: torch.Tensor
+    extrinsics_xf: torch.Tensor
+    hand_idx: torch.Tensor
+
+
+@dataclass
+class PerBranchOutput:
+    joint_angles: torch.Tensor
+    wrist_xfs: torch.Tensor
+    skel_scales: Optional[torch.Tensor] = None
+    pinch_prediction: Optional[torch.Tensor] = None
+
+
+@dataclass
+class ModelTarget:
+    gt_skel_targets: PerBranchOutput
+    preds_targets: PerBranchOutput
+    intrinsics: Optional[torch.Tensor] = None
+    extrinsics_xf: Optional[torch.Tensor] = None
+
+
+def prepare_inputs_targets(sample: RawSample, crop_size: Tuple[int, int]) -> Tuple[ModelInput, ModelTarget]:
+    """`prepare_inputs_targets` of the reference (:280-385): mm -> m, left-hand skeletons, the
+    perspective crops of the whole sequence (two launches on the GPU instead of a Python chain per
+    view), and the targets of both branches.  Images, intrinsics and extrinsics come back as CUDA
+    tensors; the small pose / skeleton tensors stay where the labels were (host)."""
+
+    def to_th(a: np.ndarray) -> torch.Tensor:
+        return torch.from_numpy(np.asarray(a)).float()
+
+    sample.scaled(0.001)
+    seq_length = sample.images.shape[0]
+    is_right = to_th(sample.hand) == 1
+
+    def left_model(hm: HandModel) -> HandModel:
+        rep = bundles.map_fields(lambda t: t.unsqueeze(0).expand(seq_length, *t.shape), hm, only_type=torch.Tensor)
+        return mirrored_hand_model(rep, is_right)
+
+    s_solved = PoseData(wrist_xfs=to_th(sample.solved_wrist_xfs), joint_angles=to_th(sample.solved_joint_angles),
+                        left_hand_model=left_model(sample.generic_hand_model))
+    orig = PoseData(wrist_xfs=to_th(sample.wrist), joint_angles=to_th(sample.joint_angles),
+                    left_hand_model=left_model(sample.hand_model))
+    left_images, extrinsics_xf, intrinsics = _perspective_crop_images(
+        sample.images, sample.extrinsics, sample.intrinsics, sample.enclosing_points, int(sample.hand[0]), crop_size)
+    model_input = ModelInput(orig_pose_data=orig, s_solved_pose_data=s_solved, left_images=left_images,
+                             intrinsics=intrinsics, extrinsics_xf=extrinsics_xf, hand_idx=to_th(sample.hand))
+    pinch = to_th(sample.pinch)
+    target = ModelTarget(
+        gt_skel_targets=PerBranchOutput(orig.joint_angles, orig.wrist_xfs, orig.left_hand_model.hand_scale, pinch),
+        preds_targets=PerBranchOutput(s_solved.joint_angles, s_solved.wrist_xfs, s_solved.left_hand_model.hand_scale, pinch),
+        intrinsics=intrinsics, extrinsics_xf=extrinsics_xf,
+    )
+    return model_input, target
+
+
+def preprocess(data: Dict[str, Any], crop_size: Tuple[int, int]) -> Tuple[ModelInput, ModelTarget]:
+    """One decoded sequence {'mono': uint8 [T,V,H,W], 'labels': msgpack dict} -> (ModelInput,
+    ModelTarget) (data_transform.py:388-397)."""
+    return prepare_inputs_targets(parse_raw_buffers(**data), crop_size)

@@ -1,6 +1,6 @@
 """Generate tests/golden/*.npz by running the UNMODIFIED reference in the build container.
 
-TEST INFRASTRUCTURE.  Run as `python oracle/make_golden.py [fk] [geometry] [warp] [cropcams] [cropmats] [eval] [model]`
+TEST INFRASTRUCTURE.  Run as `python oracle/make_golden.py [fk] [geometry] [warp] [cropcams] [cropmats] [torchdata] [eval] [model]`
 (no argument = all).  /root/reference is read-only and absent on the GPU box, so the
 outputs are committed; this script is the provenance record for every fixture.
 
@@ -25,6 +25,10 @@ Fixtures
   crop_matrices.npz  reference data_transform._gen_crop_matrices (:145-209) on 40 seeded two-view
                   frames (pinhole views, left and mirrored right hands) and
                   _perspective_crop_images (:212-277) on 3 of them per hand (seeded images).
+  torchdata/      two synthetic config-3 sequences written as `.torch.idx/.torch.bin` pairs (frames:
+                  uint8 tensors, labels: msgpack) with absolutetrack_b200's fixture writer, and
+  torchdata.npz   what the REFERENCE makes of those files: TorchIdx (idxbinfile.py:48-347) decoding
+                  and data_transform.preprocess (:388-397) -> ModelInput / ModelTarget.
   model.npz       reference UmeTrackModel outputs (umetrack_model.py:188-242) for the seeded
                   state dict of absolutetrack_b200 `make_random_state_dict(0)`.
 """
@@ -202,6 +206,75 @@ def make_cropmats():
           float(out["h0_new_intrinsics"][..., 0, 0].min()), float(out["h0_new_intrinsics"][..., 0, 0].max()))
 
 
+def make_torchdata():
+    """Fixture files written here, decoded and preprocessed by the unmodified reference."""
+    import json
+
+    from lib.batched_dataset import data_transform as DT
+    from lib.data_utils.idxbinfile import TorchIdx as RefIdx
+
+    sys.path.insert(0, ROOT)
+    from absolutetrack_b200.lib.data_utils.idxbinfile import write_torch_idx_bin
+
+    L = _load_hand_pose_labels(f"{REF}/sample_data/recording_00.json")
+    big = ("mesh_vertices", "mesh_triangles", "dense_bone_weights")  # left out: keeps the fixture small
+    user = {k: v.tolist() for k, v in L.hand_model._asdict().items() if isinstance(v, torch.Tensor) and k not in big}
+    generic = {k: v for k, v in json.load(open(f"{REF}/dataset/generic_hand_model.json")).items()
+               if v is not None and k not in big}
+    for d in (user, generic):
+        d.setdefault("hand_scale", 1.0)
+    ext, intr, pts = cropmat_inputs(seed=23, n_frames=6)
+    rng = np.random.default_rng(23)
+    T, V = 3, 2
+    monos, labels = [], []
+    for si, hand in enumerate((0, 1)):
+        fr = slice(3 * si, 3 * si + 3)
+        e_mm = ext[fr].copy()
+        e_mm[..., :3, 3] *= 1000.0
+        wrist = np.tile(np.eye(4, dtype=np.float32), (T, 1, 1))
+        wrist[:, :3, 3] = rng.normal(0, 200, (T, 3))
+        monos.append(cropmat_images(300 + 10 * si, T * V).reshape(T, V, 120, 160).astype(np.uint8))
+        labels.append({
+            "extrinsics": e_mm.tolist(), "intrinsics": intr[fr].tolist(), "enclosing_points": (pts[fr] * 1000.0).tolist(),
+            "hand": [float(hand)] * T, "hand_model": user, "wrist": wrist.tolist(),
+            "joint_angles": rng.uniform(-0.5, 0.5, (T, 22)).astype(np.float32).tolist(),
+            "solved_wrist_xfs": (wrist + np.float32(0.5)).tolist(),
+            "solved_joint_angles": rng.uniform(-0.5, 0.5, (T, 22)).astype(np.float32).tolist(),
+            "generic_hand_model": generic, "pinch": rng.uniform(0, 1, (T, 4)).astype(np.float32).tolist(),
+        })
+    d = os.path.join(GOLD, "torchdata")
+    write_torch_idx_bin(os.path.join(d, "seq.mono.torch.idx"), monos)
+    write_torch_idx_bin(os.path.join(d, "seq.labels.torch.idx"), labels)
+    # ---- the reference reads them back
+    out = {}
+    im, il = RefIdx(os.path.join(d, "seq.mono.torch.idx")), RefIdx(os.path.join(d, "seq.labels.torch.idx"))
+    out["mono_shape"] = np.array(im.shape, np.int64)
+    out["mono_is_uniform"], out["labels_is_uniform"] = np.array(im.is_uniform), np.array(il.is_uniform)
+    out["labels_byte_offsets"] = np.asarray(il.byte_offsets(0, len(il) + 1), np.int64)
+    out["mono_frame_bytes"] = np.int64(im.frame_size_bytes())
+    bm, bl = open(im.bin_path, "rb").read(), open(il.bin_path, "rb").read()
+    for i in range(len(im)):
+        mono = np.array(im.view_buffer(bm)[i])  # (view_buffer_at on a uniform file trips over numpy-2 promotion in the reference)
+        lab = il.view_buffer_at(i, bl)
+        assert np.array_equal(mono, monos[i]) and lab["hand"] == labels[i]["hand"]
+        out[f"s{i}_mono_sum"] = np.int64(mono.astype(np.int64).sum())
+        mi, mt = DT.preprocess({"mono": mono, "labels": lab}, (96, 96))
+        p = f"s{i}_"
+        out[p + "left_images"] = mi.left_images.numpy()
+        out[p + "intrinsics"], out[p + "extrinsics_xf"] = mi.intrinsics.numpy(), mi.extrinsics_xf.numpy()
+        out[p + "hand_idx"] = mi.hand_idx.numpy()
+        for name, pd in (("orig", mi.orig_pose_data), ("solved", mi.s_solved_pose_data)):
+            out[p + name + "_joint_angles"], out[p + name + "_wrist_xfs"] = pd.joint_angles.numpy(), pd.wrist_xfs.numpy()
+            out[p + name + "_axes"] = pd.left_hand_model.joint_rotation_axes.numpy()
+            out[p + name + "_rest"] = pd.left_hand_model.joint_rest_positions.numpy()
+            out[p + name + "_landmarks"] = pd.left_hand_model.landmark_rest_positions.numpy()
+        out[p + "gt_skel_scales"] = np.asarray(mt.gt_skel_targets.skel_scales)
+        out[p + "pinch"] = mt.preds_targets.pinch_prediction.numpy()
+        assert np.array_equal(mt.intrinsics.numpy(), out[p + "intrinsics"])
+    np.savez_compressed(os.path.join(GOLD, "torchdata.npz"), **out)
+    print("torchdata", {k: os.path.getsize(os.path.join(d, k)) for k in sorted(os.listdir(d))}, out["s0_left_images"].shape)
+
+
 def _frames():
     L = _load_hand_pose_labels(f"{REF}/sample_data/recording_00.json")
     idx = np.arange(0, len(L), 3)
@@ -348,13 +421,15 @@ def make_warp():
 
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
-    what = sys.argv[1:] or ["fk", "geometry", "warp", "cropcams", "cropmats", "eval", "model"]
+    what = sys.argv[1:] or ["fk", "geometry", "warp", "cropcams", "cropmats", "torchdata", "eval", "model"]
     if "fk" in what:
         make_fk()
     if "eval" in what:
         make_eval()
     if "cropmats" in what:
         make_cropmats()
+    if "torchdata" in what:
+        make_torchdata()
     if "geometry" in what:
         make_geometry()
     if "cropcams" in what:

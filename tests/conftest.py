@@ -20,7 +20,7 @@ def pytest_configure(config):
 def gold():
     import numpy as np
 
-    return {n: dict(np.load(os.path.join(GOLD, n + ".npz"))) for n in ("fk_user05", "geometry", "warp", "model", "crop_cameras", "eval_user05", "crop_matrices")}
+    return {n: dict(np.load(os.path.join(GOLD, n + ".npz"))) for n in ("fk_user05", "geometry", "warp", "model", "crop_cameras", "eval_user05", "crop_matrices", "torchdata")}
 
 
 @pytest.fixture(scope="session")

@@ -248,6 +248,101 @@ def test_oracle_config3_crop_matrices_and_crops_match_reference_golden(gold):
         O.gen_crop_matrices(ext[0], intr[0], bad, False, (96, 96))
 
 
+def test_torch_idx_reader_matches_reference_decoding(gold, tmp_path):
+    """lib/data_utils/idxbinfile.TorchIdx on the committed fixture pairs against what the reference's
+    TorchIdx made of the same files (tests/golden/torchdata.npz), a write/read round trip over dtypes
+    and ragged frames, and the reference's error cases."""
+    from absolutetrack_b200.lib.batched_dataset.sample import parse_raw_buffers
+    from absolutetrack_b200.lib.data_utils.idxbinfile import MAGIC, TorchIdx, write_torch_idx_bin
+
+    G = gold["torchdata"]
+    d = os.path.join(ROOT, "tests", "golden", "torchdata")
+    im, il = TorchIdx(os.path.join(d, "seq.mono.torch.idx")), TorchIdx(os.path.join(d, "seq.labels.torch.idx"))
+    assert im.bin_path.endswith("seq.mono.torch.bin")
+    assert im.is_uniform == bool(G["mono_is_uniform"]) and il.is_uniform == bool(G["labels_is_uniform"])
+    assert tuple(im.shape) == tuple(G["mono_shape"]) and im.dtype == np.uint8 and il.shape is None
+    assert im.frame_size_bytes() == int(G["mono_frame_bytes"]) and im.item_shape() == tuple(G["mono_shape"][1:])
+    assert np.array_equal(np.asarray(il.byte_offsets(0, len(il) + 1), np.int64), G["labels_byte_offsets"])
+    mono, labels = im.read_bin(), il.read_bin()
+    assert len(im) == len(il) == len(labels) == 2
+    bm = open(im.bin_path, "rb").read()
+    for i in range(2):
+        assert int(mono[i].astype(np.int64).sum()) == int(G[f"s{i}_mono_sum"])
+        assert np.array_equal(im.view_buffer_at(i, bm), mono[i])
+        s = parse_raw_buffers(np.array(mono[i]), labels[i])
+        assert s.images.shape == (3, 2, 120, 160) and s.extrinsics.dtype == np.float32 and s.hand.tolist() == [float(i)] * 3
+        assert np.array_equal(s.hand, G[f"s{i}_hand_idx"])
+        assert tuple(s.hand_model.joint_rest_positions.shape) == (22, 3) and s.generic_hand_model.joint_limits is not None
+    with pytest.raises(ValueError):
+        il.frame_size_bytes()
+    with pytest.raises(ValueError):
+        im.view_buffer(bm[:-1])
+    # round trip: dtypes, ragged frames, msgpack objects
+    rng = np.random.default_rng(2)
+    for name in ("uint8", "int8", "int16", "int32", "int64", "float32", "float64"):
+        fr = [(rng.normal(0, 50, (4, 5))).astype(name) for _ in range(3)]
+        p = str(tmp_path / f"u_{name}.torch.idx")
+        write_torch_idx_bin(p, fr)
+        t = TorchIdx(p)
+        assert t.is_uniform and t.shape == (3, 4, 5) and t.dtype == np.dtype(name) and np.array_equal(t.read_bin(), np.stack(fr))
+        assert t.byte_offsets_array is None and t.byte_offset(-1) == t.data_size_bytes() == 3 * 20 * np.dtype(name).itemsize
+    ragged = [np.zeros((2, 3), np.float32), np.ones((4,), np.float32), np.full((1, 2, 2), 7, np.float32)]
+    p = str(tmp_path / "r.torch.idx")
+    write_torch_idx_bin(p, ragged)
+    t = TorchIdx(p)
+    assert not t.is_uniform and t.shape is None and [a.shape for a in t.read_bin()] == [(2, 3), (4,), (1, 2, 2)]
+    assert t.item_shape(2) == (1, 2, 2) and np.array_equal(t.read_bin()[-1], ragged[2])
+    with pytest.raises(ValueError):
+        t.item_shape()
+    # header errors (idxbinfile.py:137-157,329-347)
+    good = np.frombuffer(open(p, "rb").read(), np.int64).copy()
+    for pos, val, exc in ((0, 1, ValueError), (1, 2, ValueError), (2, 99, KeyError), (3, 8, ValueError)):
+        bad = good.copy()
+        bad[pos] = val
+        with pytest.raises(exc):
+            TorchIdx(p, buffer=bad.tobytes())
+    with pytest.raises(ValueError):
+        TorchIdx(p, buffer=good.tobytes()[:-3])
+    v0 = good.copy()
+    v0[0], v0[1] = 0, 0                      # version 0 files carry no magic
+    assert len(TorchIdx(p, buffer=v0.tobytes())) == 3 and good[0] == MAGIC
+
+
+def test_config3_preprocess_host_side_matches_reference(gold, monkeypatch):
+    """Everything of data_transform.preprocess except the GPU crop stage (stubbed here; the GPU test
+    covers it): unit change, left-hand skeletons, pose tensors, targets - exact against the
+    reference's preprocess of the same fixture files."""
+    from absolutetrack_b200.lib.batched_dataset import data_transform as DT
+    from absolutetrack_b200.lib.data_utils.idxbinfile import TorchIdx
+
+    G = gold["torchdata"]
+    d = os.path.join(ROOT, "tests", "golden", "torchdata")
+    mono = TorchIdx(os.path.join(d, "seq.mono.torch.idx")).read_bin()
+    labels = TorchIdx(os.path.join(d, "seq.labels.torch.idx")).read_bin()
+    seen = {}
+
+    def fake_crops(images, ext, intr, pts, hand_idx, crop_size):
+        seen.update(ext=np.array(ext), pts=np.array(pts), hand=hand_idx, images=images)
+        return [torch.zeros(3, 2, 96, 96), torch.zeros(3, 2, 4, 4), torch.zeros(3, 2, 3, 3)]
+
+    monkeypatch.setattr(DT, "_perspective_crop_images", fake_crops)
+    for i in range(2):
+        mi, mt = DT.preprocess({"mono": np.array(mono[i]), "labels": labels[i]}, (96, 96))
+        p = f"s{i}_"
+        assert seen["hand"] == i and seen["images"].shape == (3, 2, 120, 160)
+        assert np.abs(seen["ext"][..., :3, 3]).max() < 1.0 and np.abs(seen["pts"]).max() < 1.0   # metres now
+        assert np.array_equal(mi.hand_idx.numpy(), G[p + "hand_idx"])
+        for name, pd in (("orig", mi.orig_pose_data), ("solved", mi.s_solved_pose_data)):
+            assert np.array_equal(pd.joint_angles.numpy(), G[p + name + "_joint_angles"])
+            assert np.array_equal(pd.wrist_xfs.numpy(), G[p + name + "_wrist_xfs"])
+            assert np.array_equal(pd.left_hand_model.joint_rotation_axes.numpy(), G[p + name + "_axes"])
+            assert np.array_equal(pd.left_hand_model.joint_rest_positions.numpy(), G[p + name + "_rest"])
+            assert np.array_equal(pd.left_hand_model.landmark_rest_positions.numpy(), G[p + name + "_landmarks"])
+        assert np.array_equal(np.asarray(mt.gt_skel_targets.skel_scales), G[p + "gt_skel_scales"])
+        assert np.array_equal(mt.preds_targets.pinch_prediction.numpy(), G[p + "pinch"])
+        assert mt.intrinsics is mi.intrinsics and mt.extrinsics_xf is mi.extrinsics_xf
+
+
 # ------------------------------------------------------------------ host logic
 def test_state_dict_spec_is_the_reference_key_set():
     from absolutetrack_b200.lib.models.model_loader import make_random_state_dict, pack_state_dict, state_dict_spec

@@ -466,3 +466,34 @@ def test_config3_crop_matrices_and_crops_match_reference_golden(cuda_lib, gold):
     assert tuple(x.shape) == (0, 2, 4, 4)
     with pytest.raises(ValueError):
         DT.gen_crop_matrices_cuda(ext, intr[:, :1], pts, False, (96, 96))
+
+
+def test_config3_preprocess_from_torch_idx_files_matches_reference(cuda_lib, gold):
+    """The committed .torch.idx/.torch.bin fixture pairs -> TorchIdx -> data_transform.preprocess
+    (crops on the GPU) against the reference's own preprocess of the same files."""
+    import os
+
+    from absolutetrack_b200.lib.batched_dataset import data_transform as DT
+    from absolutetrack_b200.lib.data_utils.idxbinfile import TorchIdx
+
+    G = gold["torchdata"]
+    d = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "torchdata")
+    mono = TorchIdx(os.path.join(d, "seq.mono.torch.idx")).read_bin()
+    labels = TorchIdx(os.path.join(d, "seq.labels.torch.idx")).read_bin()
+    for i in range(2):
+        mi, mt = DT.preprocess({"mono": np.array(mono[i]), "labels": labels[i]}, (96, 96))
+        p = f"s{i}_"
+        assert mi.left_images.is_cuda and tuple(mi.left_images.shape) == (3, 2, 96, 96)
+        assert np.abs(mi.left_images.cpu().numpy() - G[p + "left_images"]).max() < 2e-3
+        assert np.allclose(mi.intrinsics.cpu().numpy(), G[p + "intrinsics"], rtol=2e-6, atol=0)
+        assert np.abs(mi.extrinsics_xf.cpu().numpy() - G[p + "extrinsics_xf"]).max() < 5e-7
+        assert np.array_equal(mi.hand_idx.numpy(), G[p + "hand_idx"])
+        for name, pd in (("orig", mi.orig_pose_data), ("solved", mi.s_solved_pose_data)):
+            assert np.array_equal(pd.joint_angles.numpy(), G[p + name + "_joint_angles"])
+            assert np.array_equal(pd.wrist_xfs.numpy(), G[p + name + "_wrist_xfs"])       # mm -> m on the translations
+            assert np.array_equal(pd.left_hand_model.joint_rotation_axes.numpy(), G[p + name + "_axes"])  # mirrored for the right hand
+            assert np.array_equal(pd.left_hand_model.joint_rest_positions.numpy(), G[p + name + "_rest"])
+            assert np.array_equal(pd.left_hand_model.landmark_rest_positions.numpy(), G[p + name + "_landmarks"])
+        assert np.array_equal(np.asarray(mt.gt_skel_targets.skel_scales), G[p + "gt_skel_scales"])
+        assert np.array_equal(mt.preds_targets.pinch_prediction.numpy(), G[p + "pinch"])
+        assert mt.intrinsics is mi.intrinsics and mt.extrinsics_xf is mi.extrinsics_xf

@@ -269,3 +269,41 @@ def test_batched_tracker_ingest_modes_agree_and_match_oracle(cuda_lib, state_dic
             w[:3, 3] *= 1000.0
             lm_ref = O.landmarks_from_hand_pose(hmn, ref["joint_angles"][i].numpy(), w, int(hb.hand_idx[i]))[0]
             assert np.abs(o["landmarks"][i].numpy() - lm_ref).max() < 0.05   # mm
+
+
+def test_config3_files_to_poses_match_oracle_on_reference_inputs(model, state_dict, gold):
+    """Config 3 end to end: .torch.idx/.torch.bin fixture pairs -> TorchIdx -> preprocess (GPU crops)
+    -> the per-frame calls of run_inference_torch_data._unpack_batched_data (:39-85) on the CUDA
+    model, against the CPU oracle network fed with the REFERENCE's preprocess outputs of the same
+    files.  Tolerances are looser than the network's own (2e-4 rad): the inputs differ by the
+    crop-matrix round-off (crops within 2e-3)."""
+    import os
+
+    from absolutetrack_b200.lib.batched_dataset import data_transform as DT
+    from absolutetrack_b200.lib.data_utils.idxbinfile import TorchIdx
+    from absolutetrack_b200.lib.models.umetrack_model import InputFrameData, InputFrameDesc, InputSkeletonData
+
+    G = gold["torchdata"]
+    d = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "torchdata")
+    mono = TorchIdx(os.path.join(d, "seq.mono.torch.idx")).read_bin()
+    labels = TorchIdx(os.path.join(d, "seq.labels.torch.idx")).read_bin()
+    mis = [DT.preprocess({"mono": np.array(mono[i]), "labels": labels[i]}, (96, 96))[0] for i in range(2)]
+    bs, seq_len, nv = 2, 3, 2
+    st = MO.TemporalState()
+    srange = torch.tensor([(i * nv, (i + 1) * nv) for i in range(bs)])
+    midx = torch.arange(bs)
+    for t in range(seq_len):
+        usem = torch.full((bs,), t != 0)
+        hidx = torch.stack([m.hand_idx[t] for m in mis]).long()
+        axes = torch.stack([m.orig_pose_data.left_hand_model.joint_rotation_axes[t] for m in mis])
+        rest = torch.stack([m.orig_pose_data.left_hand_model.joint_rest_positions[t] for m in mis])
+        out = model.regress_pose_use_skeleton(
+            InputFrameData(torch.cat([m.left_images[t] for m in mis]), torch.cat([m.intrinsics[t] for m in mis]),
+                           torch.cat([m.extrinsics_xf[t] for m in mis])),
+            InputFrameDesc(srange.cuda(), midx.cuda(), usem.cuda(), hidx.cuda()), InputSkeletonData(axes.cuda(), rest.cuda()))
+        g = lambda k: torch.from_numpy(np.concatenate([G[f"s{i}_{k}"][t] for i in range(bs)]))  # noqa: E731
+        ref = MO.forward(state_dict, st, g("left_images"), g("intrinsics"), g("extrinsics_xf"), srange, midx, usem, hidx,
+                         (torch.from_numpy(np.stack([G[f"s{i}_orig_axes"][t] for i in range(bs)])),
+                          torch.from_numpy(np.stack([G[f"s{i}_orig_rest"][t] for i in range(bs)]))))
+        assert np.abs(out.joint_angles.cpu().numpy() - ref["joint_angles"].numpy()).max() < 2e-3
+        assert np.abs(out.wrist_xfs.cpu().numpy() - ref["wrist_xfs"].numpy()).max() < 2e-4

@@ -1,4 +1,6 @@
-"""One raw torch_data sequence (mirror of the reference's lib/batched_dataset/sample.py)."""
+"""One raw torch_data sequence: the decoded frames of a `.torch.bin` pair as typed arrays
+(counterpart of the reference's lib/batched_dataset/sample.py, same names so that
+`RawSample(**...)` / `parse_raw_buffers(**data)` call sites keep working)."""
 from dataclasses import dataclass
 from typing import Any, Dict
 
@@ -7,43 +9,43 @@ import torch
 
 from ..common.hand import HandModel, scaled_hand_model
 
+# label arrays whose translation column / coordinates carry a length (mm in the files)
+_XF_FIELDS = ("extrinsics", "wrist", "solved_wrist_xfs")
+_MODEL_FIELDS = ("hand_model", "generic_hand_model")
+
 
 @dataclass
 class RawSample:
-    """Field names and order of sample.py:17-32: images [T,V,H,W], world->eye extrinsics [T,V,4,4],
-    intrinsics [T,V,3,3], enclosing_points [T,P,3], hand [T], the user's and the generic skeleton
-    with their poses, pinch labels.  Lengths in mm until `scaled(0.001)`."""
+    """T frames, V views, P crop points (sample.py:17-32)."""
 
-    images: np.ndarray
-    extrinsics: np.ndarray
-    intrinsics: np.ndarray
-    enclosing_points: np.ndarray
-    hand: np.ndarray
-    hand_model: HandModel
-    wrist: np.ndarray
-    joint_angles: np.ndarray
-    solved_wrist_xfs: np.ndarray
-    solved_joint_angles: np.ndarray
+    images: np.ndarray               # uint8 [T,V,H,W] mono frames
+    extrinsics: np.ndarray           # f32 [T,V,4,4] world -> eye of every view
+    intrinsics: np.ndarray           # f32 [T,V,3,3]
+    enclosing_points: np.ndarray     # f32 [T,P,3] world points the crop must contain
+    hand: np.ndarray                 # f32 [T] 0 = left, 1 = right
+    hand_model: HandModel            # the user's skeleton (ground truth branch)
+    wrist: np.ndarray                # f32 [T,4,4]
+    joint_angles: np.ndarray         # f32 [T,22]
+    solved_wrist_xfs: np.ndarray     # f32 [T,4,4] pose solved on the generic skeleton
+    solved_joint_angles: np.ndarray  # f32 [T,22]
     generic_hand_model: HandModel
-    pinch: np.ndarray
+    pinch: np.ndarray                # f32 [T,...] pinch labels
 
     def scaled(self, factor: float) -> None:
-        """In-place unit change of every length (sample.py:34-40)."""
-        self.extrinsics[..., :3, 3] *= factor
+        """Unit change of every length, in place (sample.py:34-40; the loader calls it with 0.001)."""
+        for name in _XF_FIELDS:
+            getattr(self, name)[..., :3, 3] *= factor
         self.enclosing_points *= factor
-        self.wrist[..., :3, 3] *= factor
-        self.solved_wrist_xfs[..., :3, 3] *= factor
-        self.hand_model = scaled_hand_model(self.hand_model, factor)
-        self.generic_hand_model = scaled_hand_model(self.generic_hand_model, factor)
+        for name in _MODEL_FIELDS:
+            setattr(self, name, scaled_hand_model(getattr(self, name), factor))
 
 
 def parse_raw_buffers(mono: np.ndarray, labels: Dict[str, Any]) -> RawSample:
-    """The decoded frames of one sequence -> RawSample (sample.py:43-53): hand models become
+    """Frames + msgpack labels of one sequence -> RawSample (sample.py:43-53): skeleton dicts become
     HandModel tuples of tensors, every other label a float32 array."""
-    typed: Dict[str, Any] = {}
-    for name, value in labels.items():
+    def typed(name: str, value: Any):
         if "hand_model" in name:
-            typed[name] = HandModel(**{k: torch.tensor(v) for k, v in value.items()})
-        else:
-            typed[name] = np.array(value, dtype=np.float32)
-    return RawSample(images=mono, **typed)
+            return HandModel(**{k: torch.tensor(v) for k, v in value.items()})
+        return np.array(value, dtype=np.float32)
+
+    return RawSample(images=mono, **{name: typed(name, value) for name, value in labels.items()})

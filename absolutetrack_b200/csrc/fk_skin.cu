@@ -244,32 +244,11 @@ __global__ void __launch_bounds__(kFast, kFastCtas) fk_skin_shared_kernel(const 
   for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
   const int64_t base = tile * kFast;
   const int n_here = (int)min((int64_t)kFast, n - base);
-  // coalesced input staging: the tile's joint angles [n_here,22] as one flat 16-byte copy; the
-  // wrist rows (64 B per hand, used once) come straight from global memory as three float4
-  {
-    const float* gja = joint_angles + base * 22;
-    const int tot = n_here * 22;
-    int done = 0;
-    if (vec_ok) {
-      const int nv = tot >> 2;
-      const float4* g4 = reinterpret_cast<const float4*>(gja);
-      float4* s4 = reinterpret_cast<float4*>(smem);
-      for (int i = tid; i < nv; i += kFast) s4[i] = __ldg(g4 + i);
-      done = nv << 2;
-    }
-    for (int i = done + tid; i < tot; i += kFast) smem[i] = __ldg(gja + i);
-  }
-  __syncthreads();
+  // the wrist rows (64 B per hand, used once) come straight from global memory as three float4,
+  // issued first so that their latency overlaps the joint-angle staging below
   const bool active = tid < n_here;
-  float ang[20];
   Xf W;
   if (active) {
-    const float2* a2 = reinterpret_cast<const float2*>(smem + tid * 22);
-#pragma unroll
-    for (int j = 0; j < 10; ++j) {
-      const float2 v = a2[j];
-      ang[2 * j] = v.x; ang[2 * j + 1] = v.y;
-    }
     const float sgn = (hand_idx != nullptr && hand_idx[base + tid] == 1) ? -1.0f : 1.0f;
     const float* gw = wrist + (base + tid) * 16;
 #pragma unroll
@@ -288,6 +267,30 @@ __global__ void __launch_bounds__(kFast, kFastCtas) fk_skin_shared_kernel(const 
     if (wrist_out != nullptr) {
       float* wo = wrist_out + (base + tid) * 16 + 12;
       wo[0] = __ldg(gw + 12); wo[1] = __ldg(gw + 13); wo[2] = __ldg(gw + 14); wo[3] = __ldg(gw + 15);
+    }
+  }
+  // coalesced input staging: the tile's joint angles [n_here,22] as one flat 16-byte copy
+  {
+    const float* gja = joint_angles + base * 22;
+    const int tot = n_here * 22;
+    int done = 0;
+    if (vec_ok) {
+      const int nv = tot >> 2;
+      const float4* g4 = reinterpret_cast<const float4*>(gja);
+      float4* s4 = reinterpret_cast<float4*>(smem);
+      for (int i = tid; i < nv; i += kFast) s4[i] = __ldg(g4 + i);
+      done = nv << 2;
+    }
+    for (int i = done + tid; i < tot; i += kFast) smem[i] = __ldg(gja + i);
+  }
+  __syncthreads();
+  float ang[20];
+  if (active) {
+    const float2* a2 = reinterpret_cast<const float2*>(smem + tid * 22);
+#pragma unroll
+    for (int j = 0; j < 10; ++j) {
+      const float2 v = a2[j];
+      ang[2 * j] = v.x; ang[2 * j + 1] = v.y;
     }
   }
   __syncthreads();  // inputs are in registers: the buffer becomes the flat [hands][63] landmark accumulator

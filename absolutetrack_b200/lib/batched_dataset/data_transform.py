@@ -180,3 +180,27 @@ def preprocess(data: Dict[str, Any], crop_size: Tuple[int, int]) -> Tuple[ModelI
     """One decoded sequence {'mono': uint8 [T,V,H,W], 'labels': msgpack dict} -> (ModelInput,
     ModelTarget) (data_transform.py:388-397)."""
     return prepare_inputs_targets(parse_raw_buffers(**data), crop_size)
+
+
+def iter_preprocessed_sequences(mono_idx_path: str, labels_idx_path: str, crop_size: Tuple[int, int] = (96, 96),
+                                rank: int = 0, world: int = 1):
+    """The sequences of one `.torch.idx/.torch.bin` pair of files (frames + labels), preprocessed on
+    this rank's GPU: what the reference builds from Sampler + AsyncToIterableDataset + map_dataset(
+    preprocess) (run_inference_torch_data.py:166-177), with the Sampler's rank striding
+    (async_dataset.py:558-559 = distributed.shard_indices) and without worker processes - the
+    per-sequence work is two launches.  Yields (sequence index, ModelInput, ModelTarget)."""
+    from ...distributed import shard_indices
+    from ..data_utils.idxbinfile import TorchIdx
+
+    mono_idx, labels_idx = TorchIdx(mono_idx_path), TorchIdx(labels_idx_path)
+    if len(mono_idx) != len(labels_idx):
+        raise ValueError(f"{mono_idx_path} holds {len(mono_idx)} sequences, {labels_idx_path} {len(labels_idx)}")
+    with open(mono_idx.bin_path, "rb") as fm, open(labels_idx.bin_path, "rb") as fl:
+        for i in shard_indices(len(mono_idx), rank, world):
+            lo, hi = mono_idx.byte_offset(i), mono_idx.byte_offset(i + 1)
+            fm.seek(lo)
+            mono = np.array(mono_idx.view_frame(i, fm.read(hi - lo)))   # writable copy: preprocess owns it
+            lo, hi = labels_idx.byte_offset(i), labels_idx.byte_offset(i + 1)
+            fl.seek(lo)
+            labels = labels_idx.view_frame(i, fl.read(hi - lo))
+            yield (i,) + preprocess({"mono": mono, "labels": labels}, crop_size)

@@ -341,6 +341,11 @@ def test_config3_preprocess_host_side_matches_reference(gold, monkeypatch):
         assert np.array_equal(np.asarray(mt.gt_skel_targets.skel_scales), G[p + "gt_skel_scales"])
         assert np.array_equal(mt.preds_targets.pinch_prediction.numpy(), G[p + "pinch"])
         assert mt.intrinsics is mi.intrinsics and mt.extrinsics_xf is mi.extrinsics_xf
+    # the per-rank iterator over a file pair: rank striding of the reference Sampler, spans read one by one
+    paths = (os.path.join(d, "seq.mono.torch.idx"), os.path.join(d, "seq.labels.torch.idx"))
+    got = {r: [(i, float(mi.hand_idx[0])) for i, mi, _ in DT.iter_preprocessed_sequences(*paths, rank=r, world=2)] for r in (0, 1)}
+    assert got == {0: [(0, 0.0)], 1: [(1, 1.0)]}
+    assert [i for i, _, _ in DT.iter_preprocessed_sequences(*paths)] == [0, 1]
 
 
 # ------------------------------------------------------------------ host logic

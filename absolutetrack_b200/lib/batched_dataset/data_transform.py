@@ -8,12 +8,16 @@ are one launch each for the whole sequence (C-ABI at_gen_crop_matrices_f32 and
 at_resample_homography_f32) and everything stays on the device.  The msgpack / .torch.idx readers in
 front of this are host IO and not part of this package.  There is no CPU path.
 """
-from typing import List, Tuple
+from dataclasses import dataclass
+from typing import Any, Dict, List, Optional, Tuple
 
 import numpy as np
 import torch
 
 from ... import _cabi
+from ..common.hand import HandModel, mirrored_hand_model
+from ..data_utils import bundles
+from .sample import RawSample, parse_raw_buffers
 
 
 def _dev():
@@ -101,12 +105,6 @@ def _perspective_crop_images(orig_images, orig_extrinsics, orig_intrinsics, crop
 # --------------------------------------------------------------------------------------------
 # sequence -> model input / targets (data_transform.py:23-54,280-397)
 # --------------------------------------------------------------------------------------------
-from dataclasses import dataclass  # noqa: E402
-from typing import Any, Dict, Optional  # noqa: E402
-
-from ..common.hand import HandModel, mirrored_hand_model  # noqa: E402
-from ..data_utils import bundles  # noqa: E402
-from .sample import RawSample, parse_raw_buffers  # noqa: E402
 
 
 @dataclass

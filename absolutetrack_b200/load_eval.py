@@ -117,3 +117,25 @@ def aggregate_metrics(output_dir: str, rank: int = 0, world: int = 1, verbose: b
         print(f"  Mean keypoint accelerations: {t['mean_keypoint_acceleration']}")
         print(f"  GT mean keypoint accelerations: {t['gt_mean_keypoint_acceleration']}")
     return t
+
+
+if __name__ == "__main__":
+    # same walk as the reference's `python load_eval.py` (:95-110): tmp/eval_results_<mode>/real/<protocol>
+    # under the given root (default: the current directory); under torchrun the files of each
+    # directory are strided over the ranks and the sums all-reduced
+    import sys
+
+    root = sys.argv[1] if len(sys.argv) > 1 else os.getcwd()
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1:
+        import torch.distributed as dist
+
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+        dist.init_process_group("nccl")
+    for eval_mode in ("known_skeleton", "unknown_skeleton"):
+        for protocol in ("separate_hand", "hand_hand"):
+            if rank == 0:
+                print(f"Evaluation for {eval_mode} on protocol {protocol}")
+            aggregate_metrics(os.path.join(root, "tmp", f"eval_results_{eval_mode}", "real", protocol), rank, world)
+    if world > 1:
+        dist.destroy_process_group()

@@ -148,6 +148,7 @@ struct FastTables {
   int ent_off[64];         // 3 * landmark; bit 31 set: first contribution to that landmark (store)
   int fs[kNumFrames + 1];  // CSR row starts
   int lm_has[21];
+  int n_missing;           // landmarks without any non-zero weight (normally 0: the zero-fill loop is skipped)
 };
 
 // every landmark attached to frame b: out[l] (+)= w * (F [p,1])   (hand_skinning._lbs :56-67)
@@ -235,6 +236,15 @@ __global__ void __launch_bounds__(kFast, kFastCtas) fk_skin_shared_kernel(const 
       for (int k = 0; k < K; ++k) any |= s_valid[e * K + k];
       tb.lm_has[e] = any;
     }
+    if (e == 21) {
+      int miss = 0;
+      for (int l = 0; l < 21; ++l) {
+        int any = 0;
+        for (int k = 0; k < K; ++k) any |= s_valid[l * K + k];
+        miss += !any;
+      }
+      tb.n_missing = miss;
+    }
   }
   // tile bases are multiples of 16 B (96 hands x 88 / 64 / 252 B), so alignment depends on the pointers only
   const bool vec_ok = (((uintptr_t)joint_angles | (uintptr_t)wrist | (uintptr_t)landmarks) & 15) == 0;
@@ -296,8 +306,9 @@ __global__ void __launch_bounds__(kFast, kFastCtas) fk_skin_shared_kernel(const 
   __syncthreads();  // inputs are in registers: the buffer becomes the flat [hands][63] landmark accumulator
   float* row = smem + tid * 63;
   if (active) {
-    for (int l = 0; l < 21; ++l)
-      if (!tb.lm_has[l]) { row[3 * l] = 0.f; row[3 * l + 1] = 0.f; row[3 * l + 2] = 0.f; }
+    if (tb.n_missing)
+      for (int l = 0; l < 21; ++l)
+        if (!tb.lm_has[l]) { row[3 * l] = 0.f; row[3 * l + 1] = 0.f; row[3 * l + 2] = 0.f; }
     emit_frame(tb, row, 0, W);
     emit_frame(tb, row, 1, W);
 #pragma unroll 1  // (fully unrolled: 0.414 instead of 0.439 of HBM at 4M hands - instruction cache)

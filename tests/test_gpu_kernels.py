@@ -151,6 +151,29 @@ def test_fk_scaled_entry_folds_the_metre_to_mm_step(cuda_lib, gold):
         skin_landmarks_cuda(hm, ja, wx, wrist_out=wx)  # in place is refused
 
 
+def test_fk_landmark_without_weights_is_zero(cuda_lib, gold):
+    """A landmark whose bone weights are all zero contributes nothing (hand_skinning.py:92-94 drops zero
+    weights): it comes out as the origin, through the fast path's zero-fill branch."""
+    from absolutetrack_b200.lib.common.hand_skinning import skin_landmarks_cuda
+
+    hm = _hand_model_tuple(gold["geometry"], "hm_")
+    w = hm.landmark_rest_bone_weights.clone()
+    w[5] = 0.0
+    w[20, 1:] = 0.0
+    hm0 = hm._replace(landmark_rest_bone_weights=w)
+    rng = np.random.default_rng(4)
+    n = 300
+    ja = rng.uniform(-1, 1, (n, 22)).astype(np.float32)
+    wx = np.tile(np.eye(4, dtype=np.float32), (n, 1, 1))
+    wx[:, :3, 3] = rng.normal(0, 100, (n, 3))
+    out = skin_landmarks_cuda(hm0, torch.from_numpy(ja), torch.from_numpy(wx)).cpu().numpy()
+    md = {k: np.broadcast_to(getattr(hm0, k).numpy(), (n,) + tuple(getattr(hm0, k).shape)) for k in
+          ("joint_rotation_axes", "joint_rest_positions", "landmark_rest_positions", "landmark_rest_bone_weights",
+           "landmark_rest_bone_indices")}
+    ref = O.skin_landmarks(md, ja, wx)
+    assert np.all(out[:, 5] == 0.0) and np.abs(out - ref).max() < 1e-3 and np.abs(out[:, 4]).max() > 1.0
+
+
 def test_fk_empty_batch(cuda_lib, gold):
     from absolutetrack_b200.lib.common.hand_skinning import skin_landmarks_cuda
 

@@ -146,14 +146,15 @@ struct FastTables {
   JointConst jc[20];
   float4 ent_q[64];        // (w p, w) of entry: out (+)= R (w p) + w t
   int ent_off[64];         // 3 * landmark; bit 31 set: first contribution to that landmark (store)
-  int fs[kNumFrames + 1];  // CSR row starts
+  int2 fs[kNumFrames];     // CSR row of frame b: entries [x, y)
   int lm_has[21];
   int n_missing;           // landmarks without any non-zero weight (normally 0: the zero-fill loop is skipped)
 };
 
 // every landmark attached to frame b: out[l] (+)= w * (F [p,1])   (hand_skinning._lbs :56-67)
 __device__ __forceinline__ void emit_frame(const FastTables& tb, float* __restrict__ row, int b, const Xf& F) {
-  for (int e = tb.fs[b]; e < tb.fs[b + 1]; ++e) {
+  const int2 span = tb.fs[b];  // one LDS.64
+  for (int e = span.x; e < span.y; ++e) {
     const float4 q = tb.ent_q[e];
     const int off = tb.ent_off[e];
     const float ox = fmaf(F.r[0], q.x, fmaf(F.r[1], q.y, fmaf(F.r[2], q.z, F.t[0] * q.w)));
@@ -226,10 +227,13 @@ __global__ void __launch_bounds__(kFast, kFastCtas) fk_skin_shared_kernel(const 
       tb.ent_q[pos] = make_float4(lp[0] * w, lp[1] * w, lp[2] * w, w);
       tb.ent_off[pos] = (3 * l) | (first ? (int)0x80000000 : 0);
     }
-    if (e <= kNumFrames) {
-      int cnt = 0;
-      for (int j = 0; j < npairs; ++j) cnt += s_valid[j] && s_b[j] < e;
-      tb.fs[e] = cnt;
+    if (e < kNumFrames) {
+      int lo = 0, hi = 0;
+      for (int j = 0; j < npairs; ++j) {
+        lo += s_valid[j] && s_b[j] < e;
+        hi += s_valid[j] && s_b[j] <= e;
+      }
+      tb.fs[e] = make_int2(lo, hi);
     }
     if (e < 21) {
       int any = 0;

@@ -36,6 +36,18 @@ def test_cabi_library_exports_every_declared_symbol():
     assert sorted(_cabi.SIGNATURES) == names
 
 
+def test_every_exported_symbol_is_documented_here():
+    """INTEGRATION.md names every entry point that include/absolutetrack_b200.h declares."""
+    import re
+
+    hdr = open(os.path.join(ROOT, "include", "absolutetrack_b200.h")).read()
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    syms = sorted(set(re.findall(r"\b(at_[a-z0-9_]+)\s*\(", hdr)))
+    assert len(syms) > 25
+    missing = [s for s in syms if f"`{s}`" not in doc and f"{s}(" not in doc]
+    assert not missing, missing
+
+
 def test_cabi_host_side_queries_need_no_gpu():
     from absolutetrack_b200 import _cabi
 

@@ -15,6 +15,7 @@ AT_U8, AT_F32, AT_BF16 = 0, 1, 2
 AT_MAP_FP32, AT_MAP_FP64 = 0, 1
 AT_PREC_FP32, AT_PREC_BF16, AT_PREC_FP16 = 0, 1, 2
 AT_HEAD_KNOWN_SKELETON, AT_HEAD_PREDICT_SCALE = 0, 1
+AT_STATUS_BAD_SAMPLE_RANGE, AT_STATUS_FP16_OVERFLOW = 1, 2
 
 
 class AtCropParams(C.Structure):
@@ -193,6 +194,7 @@ SIGNATURES = {
     "at_encoder_forward": (_I, [_VP, _VP, _VP, _I, _I, _VP, _VP, _I64, _I, _VP]),
     "at_encoder_chunk_crops": (_I, []),
     "at_encoder_forward_prepared": (_I, [_VP, _VP, _VP, _I, _I, _VP, _VP, _I64, _I, _I, _VP]),
+    "at_encoder_forward_status": (_I, [_VP, _VP, _VP, _I, _I, _VP, _VP, _I64, _I, _I, _VP, _VP]),
     "at_tail_workspace_bytes": (_I64, [_I]),
     "at_tail_forward": (
         _I,

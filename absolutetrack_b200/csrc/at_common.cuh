@@ -8,7 +8,7 @@
 
 #include "absolutetrack_b200.h"
 
-namespace at {
+namespace abt {
 
 void set_error(const char* fmt, ...);
 void count_launch();  // every kernel launch of this library is counted (at_launch_count)
@@ -26,7 +26,7 @@ inline int check_launch(const char* what) {
 #define AT_REQUIRE(cond, ...)            \
   do {                                   \
     if (!(cond)) {                       \
-      at::set_error(__VA_ARGS__);        \
+      abt::set_error(__VA_ARGS__);        \
       return AT_ERR_INVALID_ARGUMENT;    \
     }                                    \
   } while (0)
@@ -51,7 +51,7 @@ inline uint64_t this_device_bit() {
 #define AT_ONCE_PER_DEVICE(...)                                    \
   do {                                                             \
     static std::atomic<uint64_t> at_once_mask_{0};                 \
-    const uint64_t at_bit_ = at::this_device_bit();                \
+    const uint64_t at_bit_ = abt::this_device_bit();                \
     if ((at_once_mask_.load(std::memory_order_acquire) & at_bit_) == 0) { \
       __VA_ARGS__;                                                 \
       at_once_mask_.fetch_or(at_bit_, std::memory_order_release);  \
@@ -62,8 +62,8 @@ template <typename K>
 inline void prefer_max_smem_carveout(K kernel) {
   cudaFuncSetAttribute((const void*)kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
 }
-#define AT_CARVEOUT_ONCE(kernel) AT_ONCE_PER_DEVICE(at::prefer_max_smem_carveout(kernel))
+#define AT_CARVEOUT_ONCE(kernel) AT_ONCE_PER_DEVICE(abt::prefer_max_smem_carveout(kernel))
 
 __host__ __device__ inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
 
-}  // namespace at
+}  // namespace abt

@@ -11,7 +11,7 @@ thread_local char g_err[512] = "";
 std::atomic<long long> g_launches{0};
 }
 
-namespace at {
+namespace abt {
 void set_error(const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
@@ -19,7 +19,7 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
-}  // namespace at
+}  // namespace abt
 
 extern "C" int64_t at_launch_count(void) { return (int64_t)g_launches.load(); }
 extern "C" int at_version(void) { return AT_VERSION; }

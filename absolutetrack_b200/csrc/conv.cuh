@@ -2,7 +2,7 @@
 #pragma once
 #include "at_common.cuh"
 
-namespace at {
+namespace abt {
 
 struct ConvLayer {
   const char* name;
@@ -54,4 +54,4 @@ int head_tc_forward(const ConvLayer* L4, const float* blob, const void* const* w
 int stem_f32(const ConvLayer& L, const float* blob, const void* crops, int crop_dtype, float* out, int c,
              cudaStream_t stream);
 
-}  // namespace at
+}  // namespace abt

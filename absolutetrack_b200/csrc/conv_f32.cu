@@ -12,7 +12,7 @@
 
 #include "conv.cuh"
 
-namespace at {
+namespace abt {
 
 namespace {
 
@@ -800,4 +800,4 @@ int stem_f32(const ConvLayer& L, const float* blob, const void* crops, int crop_
   return check_launch("stem_kernel");
 }
 
-}  // namespace at
+}  // namespace abt

@@ -34,7 +34,7 @@
 #include "conv.cuh"
 #include "tc_ptx.cuh"
 
-namespace at {
+namespace abt {
 namespace tc {
 
 constexpr int kTileM = 128;
@@ -91,6 +91,7 @@ struct ConvTcParams {
   int slab_shift;          // log2(32-column slabs per accumulator) (0 when not a power of two: MT == 1 then)
   long long* prof;  // optional [grid][16] cycle counters (debug)
   int dbg;          // debug knobs (AT_TC_DBG): 1 no epilogue, 2 no A copies
+  int32_t* status;  // optional device status word: bit 1 (value 2) |= an fp16 activation of this layer saturated / is NaN
 };
 
 // Ring cursor without divisions: slot index + phase parity.
@@ -363,6 +364,7 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
     // which holds for every residual layer (n_slabs is 1, 2, 4 or 8).  Pads and the tail behind
     // the last image are readable (zeros / finite stale data) and masked by `valid` below.
     uint4 rr[4][4];
+    uint32_t ovf = 0u;  // OR of overflow_probe over every fp16 word this thread stores (valid pixels only)
     pdl_wait();  // before the first residual load / output store
     auto res_load = [&](uint4 (&dst)[4], uint32_t tile_gbase, int f) {
       const int m = f >> p.slab_shift, sl = f - (m << p.slab_shift);
@@ -472,6 +474,7 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
                     hi.y = pack2(o[2], o[3], 0); unpack2(hi.y, 0, a, b); lo.y = pack2(o[2] - a, o[3] - b, 0);
                     hi.z = pack2(o[4], o[5], 0); unpack2(hi.z, 0, a, b); lo.z = pack2(o[4] - a, o[5] - b, 0);
                     hi.w = pack2(o[6], o[7], 0); unpack2(hi.w, 0, a, b); lo.w = pack2(o[6] - a, o[7] - b, 0);
+                    ovf |= overflow_probe(hi.x) | overflow_probe(hi.y) | overflow_probe(hi.z) | overflow_probe(hi.w);
                   }
                   uint4* op = p.out + (long long)cg * p.out_plane_px + g;
                   const long long part = (long long)p.split_planes * p.out_plane_px;
@@ -507,6 +510,8 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
                   pk[h].y = pack2(o[2], o[3], p.fmt);
                   pk[h].z = pack2(o[4], o[5], p.fmt);
                   pk[h].w = pack2(o[6], o[7], p.fmt);
+                  if (p.fmt == 0)
+                    ovf |= overflow_probe(pk[h].x) | overflow_probe(pk[h].y) | overflow_probe(pk[h].z) | overflow_probe(pk[h].w);
                 }
               }
             }
@@ -536,6 +541,7 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
       rc.advance(p.as);
       rc.advance(p.as);
     }
+    if (p.status != nullptr && (ovf & kOverflowProbeMask) != 0u) atomicOr(p.status, 2);
     if (p.prof != nullptr && lane == 0 && qd == 0) {
       long long* o = p.prof + blockIdx.x * 16 + 8 + grp * 2;
       o[0] = clock64() - e_start; o[1] = e_wait;
@@ -887,6 +893,7 @@ Divider make_divider(uint32_t d) {
 }
 long long* g_prof = nullptr;
 int g_prof_seq = -1;  // >= 0: launch k writes its counters at g_prof + k * 148 * 16
+thread_local int32_t* g_status = nullptr;  // status word of the encoder call in progress on this thread
 
 // `out_level`: geometry of the OUTPUT (= geometry of the input for stride 1, = geometry of each
 // input phase image for stride 2).  `next`: geometry of the phase images written in mode 1.
@@ -949,6 +956,7 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   p.out_mode = io.out_mode; p.relu = io.relu ? 1 : 0; p.fmt = fmt;
   p.out_f32 = io.out_f32;
   p.prof = g_prof;
+  p.status = g_status;
   { const char* e = getenv("AT_TC_DBG"); p.dbg = e ? atoi(e) : 0; }
   if (g_prof != nullptr && g_prof_seq >= 0) p.prof = g_prof + (long long)(g_prof_seq++) * kNumSMs * 16;
   if (io.out_mode == 1) {
@@ -1169,8 +1177,12 @@ int encoder_prepare_workspace(void* workspace, long long nc, cudaStream_t s) {
 // prepared_c > 0: the caller guarantees that the workspace was prepared for prepared_c crops per
 // chunk (encoder_prepare_workspace) and only written by this function since.
 int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* crops, int crop_dtype, int c, float* features,
-                         void* workspace, int64_t workspace_bytes, int fmt, int prepared_c, cudaStream_t s) {
+                         void* workspace, int64_t workspace_bytes, int fmt, int prepared_c, int32_t* status, cudaStream_t s) {
   using namespace tc;
+  struct StatusScope {  // every conv launch of this call reports fp16 saturation into `status`
+    explicit StatusScope(int32_t* p) { g_status = p; }
+    ~StatusScope() { g_status = nullptr; }
+  } status_scope(status);
   const ConvLayer* T = layer_table();
   (void)T;
   uint4* ws = reinterpret_cast<uint4*>(round_up((int64_t)(uintptr_t)workspace, 128));
@@ -1397,15 +1409,15 @@ int head_tc_forward(const ConvLayer* L4, const float* blob, const void* const* w
   return conv(3, B, h2, y, nullptr);                       // block 1 conv2 + h2, ReLU
 }
 
-}  // namespace at
+}  // namespace abt
 
 extern "C" int64_t at_model_bf16_blob_bytes(void) {
-  at::tc::tc_table();
-  return at::tc::g_tc_bytes;
+  abt::tc::tc_table();
+  return abt::tc::g_tc_bytes;
 }
 
 extern "C" int at_model_prepack_tc(const float* blob, void* tc_blob, int precision, void* stream) {
-  using namespace at;
+  using namespace abt;
   AT_REQUIRE(blob && tc_blob, "at_model_prepack_tc: NULL pointer");
   AT_REQUIRE(precision == AT_PREC_BF16 || precision == AT_PREC_FP16, "at_model_prepack_tc: precision must be bf16 or fp16");
   const ConvLayer* T = layer_table();
@@ -1454,11 +1466,11 @@ extern "C" int at_model_prepack_bf16(const float* blob, void* bf16_blob, void* s
 // in [n,H,W,cin] -> out [n,Ho,Wo,cout]; res (optional) [n,Ho,Wo,cout].  workspace: at_debug_conv_tc_workspace_bytes.
 /* Debug: when non-NULL every conv_tc launch writes [148][16] cycle counters there
  * (MMA warp: total, wait acc_empty, wait a_full, wait w_full, tiles; epilogue groups at +8: total, wait). */
-extern "C" void at_debug_set_prof(long long* dev_ptr) { at::tc::g_prof = dev_ptr; at::tc::g_prof_seq = -1; }
-extern "C" void at_debug_set_prof_seq(long long* dev_ptr) { at::tc::g_prof = dev_ptr; at::tc::g_prof_seq = 0; }
+extern "C" void at_debug_set_prof(long long* dev_ptr) { abt::tc::g_prof = dev_ptr; abt::tc::g_prof_seq = -1; }
+extern "C" void at_debug_set_prof_seq(long long* dev_ptr) { abt::tc::g_prof = dev_ptr; abt::tc::g_prof_seq = 0; }
 
 extern "C" int64_t at_debug_conv_tc_workspace_bytes(int n_img, int H, int W) {
-  using namespace at;
+  using namespace abt;
   tc::Level a = tc::make_level(H, W, 256, n_img);
   return a.buf_units() * 16 * 16 + 4096;
 }
@@ -1466,7 +1478,7 @@ extern "C" int64_t at_debug_conv_tc_workspace_bytes(int n_img, int H, int W) {
 extern "C" int at_debug_conv_tc(const float* blob, const void* tc_blob, int layer_id, const float* in, int n_img, int H,
                                 int W, const float* res, int relu, int precision, int mt, float* out, void* workspace,
                                 int64_t workspace_bytes, void* stream_) {
-  using namespace at;
+  using namespace abt;
   AT_REQUIRE(layer_id >= L_LAYER1 && layer_id <= L_PROJ, "at_debug_conv_tc: layer_id must be a backbone conv");
   AT_REQUIRE(precision == AT_PREC_BF16 || precision == AT_PREC_FP16, "at_debug_conv_tc: bad precision");
   AT_REQUIRE(workspace_bytes >= at_debug_conv_tc_workspace_bytes(n_img, H, W), "at_debug_conv_tc: workspace too small");

@@ -21,9 +21,9 @@
 
 namespace {
 
-using at::Xf;
-using at::compose;
-using at::joint_local;
+using abt::Xf;
+using abt::compose;
+using abt::joint_local;
 
 constexpr int kWarpsPerCta = 4;
 constexpr int kMaxCams = 8;
@@ -44,7 +44,7 @@ struct PoseHeader {  // per pose: views selected (0 = dropped), error flag, outp
   int32_t nsel, err, crop_off, sample_off;
 };
 
-__host__ __device__ inline int64_t header_bytes(int n_poses) { return at::round_up((int64_t)n_poses * sizeof(PoseHeader), 256); }
+__host__ __device__ inline int64_t header_bytes(int n_poses) { return abt::round_up((int64_t)n_poses * sizeof(PoseHeader), 256); }
 
 // camera.py:296-300 world_to_eye (R^T (p - t)), :80-85 arctan projection, :122-143 Fisheye62
 // distortion, :308-312 window coordinates - float64, the reference's operation order.
@@ -548,7 +548,7 @@ extern "C" int at_gen_crop_cameras(const AtCropCameraInputs* in, const AtHandMod
              "at_gen_crop_cameras: NULL output pointer");
   const int64_t need = at_crop_cameras_workspace_bytes(in->n_poses, opts->max_view_num);
   if (workspace == nullptr || workspace_bytes < need) {
-    at::set_error("at_gen_crop_cameras: workspace of %lld bytes needed, %lld given", (long long)need, (long long)workspace_bytes);
+    abt::set_error("at_gen_crop_cameras: workspace of %lld bytes needed, %lld given", (long long)need, (long long)workspace_bytes);
     return AT_ERR_WORKSPACE_TOO_SMALL;
   }
   PoseHeader* hdr = reinterpret_cast<PoseHeader*>(workspace);
@@ -560,13 +560,13 @@ extern "C" int at_gen_crop_cameras(const AtCropCameraInputs* in, const AtHandMod
   AT_CARVEOUT_ONCE(crop_cameras_scan_kernel);
   AT_CARVEOUT_ONCE(crop_cameras_emit_kernel);
   crop_cameras_pose_kernel<<<blocks, kWarpsPerCta * 32, 0, st>>>(*in, *hand_model, *opts, hdr, slots);
-  int rc = at::check_launch("crop_cameras_pose_kernel");
+  int rc = abt::check_launch("crop_cameras_pose_kernel");
   if (rc) return rc;
   crop_cameras_scan_kernel<<<1, 1024, 0, st>>>(hdr, in->n_poses, out->counts);
-  rc = at::check_launch("crop_cameras_scan_kernel");
+  rc = abt::check_launch("crop_cameras_scan_kernel");
   if (rc) return rc;
   crop_cameras_emit_kernel<<<blocks, kWarpsPerCta * 32, 0, st>>>(*in, *opts, *out, hdr, slots);
-  return at::check_launch("crop_cameras_emit_kernel");
+  return abt::check_launch("crop_cameras_emit_kernel");
 }
 
 extern "C" int at_gen_crop_matrices_f32(const float* orig_extrinsics, const float* orig_intrinsics, const float* crop_points,
@@ -584,5 +584,5 @@ extern "C" int at_gen_crop_matrices_f32(const float* orig_extrinsics, const floa
   crop_matrices_kernel<<<blocks, kWarpsPerCta * 32, 0, (cudaStream_t)stream>>>(
       orig_extrinsics, orig_intrinsics, crop_points, mirror_image, n_frames, n_views, n_pts, crop_w, crop_h,
       focal_multiplier, 5.0f, extrinsics_xf, new_intrinsics, resample_xf, n_errors);
-  return at::check_launch("crop_matrices_kernel");
+  return abt::check_launch("crop_matrices_kernel");
 }

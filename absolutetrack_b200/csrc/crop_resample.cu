@@ -443,18 +443,47 @@ constexpr int kLatStep = 4;
 constexpr int kLatMaxDim = 96 / kLatStep + 3;   // 27
 constexpr int kLatPitch = kLatMaxDim + 1;        // 28
 constexpr int kLatSeg = 12;                      // pixels per thread unit (3 lattice cells)
-constexpr int kLatStageBytes = 48 * 1024;        // 4 CTAs per SM
+constexpr int kLatStageBytes = 46 * 1024;        // 4 CTAs per SM (with 8.4 KB of static shared memory each)
 constexpr float kLatMinFocal = 80.0f;            // narrower crops only (see the kernel)
+// Exactness.  cv2.remap only sees rint(32 * map): the interpolated fp32 map u~ (in 1/32 px) gives the
+// reference's result unless the exact value lies on the other side of a rounding boundary k + 1/2, which
+// requires |u~ - (k + 1/2)| < |u~ - u|.  |u~ - u| <= 0.0078 was measured over every pixel of the recording's
+// geometry (numpy emulation of this arithmetic against the float64 map); every pixel inside kLatBand of a
+// boundary (about 6 % of them) is queued and re-evaluated with the reference's own float64 operation
+// sequence (map_pixel<double>) after the fast pass, so the kernel's output is bit-identical to
+// tracker._warp_image.  kLatMaxFlagged bounds the queue; on overflow the whole crop is re-evaluated.
+constexpr float kLatBand = 0.016f;
+constexpr int kLatMaxFlagged = 1024;
+constexpr float kLatClamp = 1048576.0f;          // |32 * map| stored on the lattice (keeps the magic-number rounding valid)
+constexpr float kRoundMagic = 12582912.0f;       // 1.5 * 2^23: (x + magic) - magic == rint(x) for |x| < 2^22
 
 // Gather from the staged tile with pre-scaled coordinates (32 * w): rint -> 1/32-px fixed point.
 // The tile is stored with one pitch + 16 bytes of padding in front and one pitch behind, so the
 // address of tap (ix, iy) may be formed without per-coordinate clamps: taps outside the image get
 // zero weight (cv2's constant-0 border) and whatever byte their address holds is irrelevant; one
 // clamp of the linear address keeps every access inside the buffer.  koff = (1 - y0) * pitch - x0a + 16.
+// round-half-even of a pre-scaled coordinate without F2I, plus the distance to the nearest integer
+__device__ __forceinline__ int round_fixed(float v, float& dist) {
+  const float r = v + kRoundMagic;
+  const int i = __float_as_int(r) - 0x4B400000;
+  dist = v - (r - kRoundMagic);
+  return i;
+}
+
+// FLAG = true: *near is set when a coordinate lies within kLatBand of a rounding boundary (see kLatBand)
+template <bool FLAG>
 __device__ __forceinline__ int remap_fixed_u8_smem_s(const uint8_t* __restrict__ tile, int pitch, int koff, int amax, int W,
-                                                     int H, float sxf, float syf) {
-  const int sx = __float2int_rn(sxf);
-  const int sy = __float2int_rn(syf);
+                                                     int H, float sxf, float syf, bool* near = nullptr) {
+  int sx, sy;
+  if (FLAG) {
+    float dx, dy;
+    sx = round_fixed(sxf, dx);
+    sy = round_fixed(syf, dy);
+    *near = fmaxf(fabsf(dx), fabsf(dy)) > 0.5f - kLatBand;
+  } else {
+    sx = __float2int_rn(sxf);
+    sy = __float2int_rn(syf);
+  }
   const int ix = sx >> 5, iy = sy >> 5;
   const int fx = sx & 31, fy = sy & 31;
   const int wx1 = (unsigned)(ix + 1) < (unsigned)W ? fx : 0, wx0 = (unsigned)ix < (unsigned)W ? 32 - fx : 0;
@@ -466,10 +495,19 @@ __device__ __forceinline__ int remap_fixed_u8_smem_s(const uint8_t* __restrict__
   return (acc + 512) >> 10;   // == ((acc * 32) + 16384) >> 15
 }
 
+template <bool FLAG>
 __device__ __forceinline__ int remap_fixed_u8_s(const uint8_t* __restrict__ img, int64_t row_stride, int W, int H, float sxf,
-                                                float syf) {
-  const int sx = __float2int_rn(sxf);
-  const int sy = __float2int_rn(syf);
+                                                float syf, bool* near = nullptr) {
+  int sx, sy;
+  if (FLAG) {
+    float dx, dy;
+    sx = round_fixed(sxf, dx);
+    sy = round_fixed(syf, dy);
+    *near = fmaxf(fabsf(dx), fabsf(dy)) > 0.5f - kLatBand;
+  } else {
+    sx = __float2int_rn(sxf);
+    sy = __float2int_rn(syf);
+  }
   const int ix = min(max(sx >> 5, -32768), 32767);
   const int iy = min(max(sy >> 5, -32768), 32767);
   const int fx = sx & 31, fy = sy & 31;
@@ -495,21 +533,31 @@ __device__ __forceinline__ float2 lag4(int k, const float2& a, const float2& b, 
   return make_float2(fmaf(w0, a.x, fmaf(w1, b.x, fmaf(w2, c.x, w3 * d.x))), fmaf(w0, a.y, fmaf(w1, b.y, fmaf(w2, c.y, w3 * d.y))));
 }
 
+// one output element in the crop's dtype
+__device__ __forceinline__ void store_level(void* __restrict__ out, int out_dtype, int64_t idx, int v) {
+  if (out_dtype == AT_U8) ((uint8_t*)out)[idx] = (uint8_t)v;
+  else if (out_dtype == AT_F32) ((float*)out)[idx] = __fdiv_rn((float)v, 255.0f);
+  else ((__nv_bfloat16*)out)[idx] = __float2bfloat16_rn(__fdiv_rn((float)v, 255.0f));
+}
+
 __global__ void __launch_bounds__(kThreads, 4)
 crop_resample_lattice_kernel(const uint8_t* __restrict__ src, int64_t frame_stride, int64_t view_stride, int64_t row_stride,
                              const AtCropParams* __restrict__ params, int dst_w, int dst_h, void* __restrict__ out,
-                             int out_dtype, unsigned long long* __restrict__ staged_bytes) {
+                             int out_dtype, unsigned long long* __restrict__ staged_bytes, int exact) {
   extern __shared__ __align__(16) uint8_t tile[];
   __shared__ FastParams P;
+  __shared__ MapParams<double> PD;   // the reference's float64 map, for the boundary pixels
   __shared__ int s_meta[4];
   __shared__ float s_red[kThreads / 32][4];
   __shared__ int s_behind;
+  __shared__ int s_nflag;
   __shared__ int s_box[6];
   __shared__ float2 s_lat[kLatMaxDim * kLatPitch];
+  __shared__ unsigned short s_list[kLatMaxFlagged];
   const int crop = blockIdx.x;
   const AtCropParams& g = params[crop];
-  if (threadIdx.x < 9) P.M[threadIdx.x] = (float)g.M[threadIdx.x];
-  if (threadIdx.x < 3) P.d[threadIdx.x] = (float)g.d[threadIdx.x];
+  if (threadIdx.x < 9) { P.M[threadIdx.x] = (float)g.M[threadIdx.x]; PD.M[threadIdx.x] = g.M[threadIdx.x]; }
+  if (threadIdx.x < 3) { P.d[threadIdx.x] = (float)g.d[threadIdx.x]; PD.d[threadIdx.x] = g.d[threadIdx.x]; }
   if (threadIdx.x == 32) {
     P.ifdx = 1.0f / (float)g.f_dst[0]; P.ifdy = 1.0f / (float)g.f_dst[1];
     P.qx0 = -(float)g.c_dst[0] * P.ifdx; P.qy0 = -(float)g.c_dst[1] * P.ifdy;
@@ -520,6 +568,13 @@ crop_resample_lattice_kernel(const uint8_t* __restrict__ src, int64_t frame_stri
     // the interpolation error grows like (lattice step / focal length)^4: hand crops have f >= 90 px
     // (1.6e-4 px); anything much wider keeps the exact per-pixel map, like crops that look behind the camera
     s_behind = fminf((float)g.f_dst[0], (float)g.f_dst[1]) < kLatMinFocal ? 1 : 0;
+    s_nflag = 0;
+  }
+  if (threadIdx.x == 64) {
+    PD.fdx = g.f_dst[0]; PD.fdy = g.f_dst[1]; PD.cdx = g.c_dst[0]; PD.cdy = g.c_dst[1];
+    PD.fsx = g.f_src[0]; PD.fsy = g.f_src[1]; PD.csx = g.c_src[0]; PD.csy = g.c_src[1];
+    PD.k1 = g.k[0]; PD.k2 = g.k[1]; PD.k3 = g.k[2]; PD.k4 = g.k[3];
+    PD.p1 = g.k[4]; PD.p2 = g.k[5]; PD.k5 = g.k[6]; PD.k6 = g.k[7];
   }
   __syncthreads();
   const int W = s_meta[2], H = s_meta[3];
@@ -533,7 +588,8 @@ crop_resample_lattice_kernel(const uint8_t* __restrict__ src, int64_t frame_stri
     float wx, wy;
     map_pixel_fast(P, fmaf((float)(kLatStep * (lx - 1)), P.ifdx, P.qx0), fmaf((float)(kLatStep * (ly - 1)), P.ifdy, P.qy0), wx, wy);
     if (wx == -1.0f && wy == -1.0f) s_behind = 1;  // ez < 0 at a lattice point: the map is not smooth there
-    s_lat[ly * kLatPitch + lx] = make_float2(wx * 32.0f, wy * 32.0f);
+    s_lat[ly * kLatPitch + lx] = make_float2(fminf(fmaxf(wx * 32.0f, -kLatClamp), kLatClamp),
+                                             fminf(fmaxf(wy * 32.0f, -kLatClamp), kLatClamp));
     if (lx >= 1 && lx <= nlx - 2 && ly >= 1 && ly <= nly - 2) {  // the points spanning [0, W] x [0, H]
       mnx = fminf(mnx, wx); mxx = fmaxf(mxx, wx);
       mny = fminf(mny, wy); mxy = fmaxf(mxy, wy);
@@ -616,65 +672,121 @@ crop_resample_lattice_kernel(const uint8_t* __restrict__ src, int64_t frame_stri
   }
   __syncthreads();
 
+  const int npix = dst_w * dst_h;
+  const int64_t obase = (int64_t)crop * npix;
+  const int koff = (1 - y0) * bw - x0a + 16;       // tap address = iy * pitch + ix + koff (padded tile)
+  const int amax = (bh + 1) * bw + 16 - 2;          // last address whose 2x2 footprint is inside the buffer
+  // one pixel through the reference's own float64 operation sequence (bit-identical map), then the same gather
+  auto exact_pixel = [&](int p) {
+    const int y = p / dst_w, x = p - y * dst_w;
+    float wx, wy;
+    map_pixel<double>(PD, x, y, wx, wy);
+    const int v = direct ? remap_fixed_u8(img, row_stride, W, H, wx, wy)
+                         : remap_fixed_u8_smem_s<false>(tile, bw, koff, amax, W, H, wx * 32.0f, wy * 32.0f);
+    store_level(out, out_dtype, obase + p, v);
+  };
+  if (behind && exact) {  // no smooth map to interpolate: every pixel through the float64 map (rare crops)
+    for (int p = threadIdx.x; p < npix; p += kThreads) exact_pixel(p);
+    return;
+  }
+
   // ---- 3. interpolate the map and gather: units of 12 pixels in a row
   const int segs = dst_w / kLatSeg;
   const int nunits = segs * dst_h;
-  const int64_t obase = (int64_t)crop * dst_w * dst_h;
-  const int koff = (1 - y0) * bw - x0a + 16;       // tap address = iy * pitch + ix + koff (padded tile)
-  const int amax = (bh + 1) * bw + 16 - 2;          // last address whose 2x2 footprint is inside the buffer
-  for (int u = threadIdx.x; u < nunits; u += kThreads) {
+  const int lane = threadIdx.x & 31;
+  for (int u0 = 0; u0 < nunits; u0 += kThreads) {
+    const int u = u0 + threadIdx.x;
     const int y = segs == 8 ? u >> 3 : u / segs, seg = u - y * segs;   // 96-pixel rows: no division
     const int xs = seg * kLatSeg;
-    int v[kLatSeg];
-    if (behind) {  // uniform per CTA
-      const float qy = fmaf((float)y, P.ifdy, P.qy0);
+    unsigned near_mask = 0u;
+    if (u < nunits) {
+      int v[kLatSeg];
+      if (behind) {  // uniform per CTA (exact == 0 only)
+        const float qy = fmaf((float)y, P.ifdy, P.qy0);
 #pragma unroll
-      for (int i = 0; i < kLatSeg; ++i) {
-        float wx, wy;
-        map_pixel_fast(P, fmaf((float)(xs + i), P.ifdx, P.qx0), qy, wx, wy);
-        v[i] = remap_fixed_u8_s(img, row_stride, W, H, wx * 32.0f, wy * 32.0f);
-      }
-    } else {
-      const int cy = y >> 2, ty = y & 3;
-      const float2* L = s_lat + cy * kLatPitch + 3 * seg;
-      float2 col[6];
-#pragma unroll
-      for (int j = 0; j < 6; ++j) col[j] = lag4(ty, L[j], L[kLatPitch + j], L[2 * kLatPitch + j], L[3 * kLatPitch + j]);
-      if (!direct) {
-#pragma unroll
-        for (int c = 0; c < 3; ++c)
-#pragma unroll
-          for (int t = 0; t < 4; ++t) {
-            const float2 m = lag4(t, col[c], col[c + 1], col[c + 2], col[c + 3]);
-            v[c * 4 + t] = remap_fixed_u8_smem_s(tile, bw, koff, amax, W, H, m.x, m.y);
-          }
+        for (int i = 0; i < kLatSeg; ++i) {
+          float wx, wy;
+          map_pixel_fast(P, fmaf((float)(xs + i), P.ifdx, P.qx0), qy, wx, wy);
+          v[i] = remap_fixed_u8_s<false>(img, row_stride, W, H, wx * 32.0f, wy * 32.0f);
+        }
       } else {
+        const int cy = y >> 2, ty = y & 3;
+        const float2* L = s_lat + cy * kLatPitch + 3 * seg;
+        float2 col[6];
 #pragma unroll
-        for (int c = 0; c < 3; ++c)
+        for (int j = 0; j < 6; ++j) col[j] = lag4(ty, L[j], L[kLatPitch + j], L[2 * kLatPitch + j], L[3 * kLatPitch + j]);
+        if (!direct) {
 #pragma unroll
-          for (int t = 0; t < 4; ++t) {
-            const float2 m = lag4(t, col[c], col[c + 1], col[c + 2], col[c + 3]);
-            v[c * 4 + t] = remap_fixed_u8_s(img, row_stride, W, H, m.x, m.y);
-          }
+          for (int c = 0; c < 3; ++c)
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              const float2 m = lag4(t, col[c], col[c + 1], col[c + 2], col[c + 3]);
+              bool near;
+              v[c * 4 + t] = remap_fixed_u8_smem_s<true>(tile, bw, koff, amax, W, H, m.x, m.y, &near);
+              near_mask |= near ? 1u << (c * 4 + t) : 0u;
+            }
+        } else {
+#pragma unroll
+          for (int c = 0; c < 3; ++c)
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              const float2 m = lag4(t, col[c], col[c + 1], col[c + 2], col[c + 3]);
+              bool near;
+              v[c * 4 + t] = remap_fixed_u8_s<true>(img, row_stride, W, H, m.x, m.y, &near);
+              near_mask |= near ? 1u << (c * 4 + t) : 0u;
+            }
+        }
+      }
+      const int64_t o = obase + (int64_t)y * dst_w + xs;
+      if (out_dtype == AT_U8) {
+        uchar4* op = reinterpret_cast<uchar4*>((uint8_t*)out + o);
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+          op[q] = make_uchar4((uint8_t)v[4 * q], (uint8_t)v[4 * q + 1], (uint8_t)v[4 * q + 2], (uint8_t)v[4 * q + 3]);
+      } else if (out_dtype == AT_F32) {
+        float4* op = reinterpret_cast<float4*>((float*)out + o);
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+          op[q] = make_float4(__fdiv_rn((float)v[4 * q], 255.0f), __fdiv_rn((float)v[4 * q + 1], 255.0f),
+                              __fdiv_rn((float)v[4 * q + 2], 255.0f), __fdiv_rn((float)v[4 * q + 3], 255.0f));
+      } else {
+        __nv_bfloat16* ob = (__nv_bfloat16*)out + o;
+#pragma unroll
+        for (int i = 0; i < kLatSeg; ++i) ob[i] = __float2bfloat16_rn(__fdiv_rn((float)v[i], 255.0f));
       }
     }
-    const int64_t o = obase + (int64_t)y * dst_w + xs;
-    if (out_dtype == AT_U8) {
-      uchar4* op = reinterpret_cast<uchar4*>((uint8_t*)out + o);
+    if (exact) {  // queue the pixels next to a rounding boundary (warp-aggregated append)
+      const int cnt = __popc(near_mask);
+      int incl = cnt;
 #pragma unroll
-      for (int q = 0; q < 3; ++q)
-        op[q] = make_uchar4((uint8_t)v[4 * q], (uint8_t)v[4 * q + 1], (uint8_t)v[4 * q + 2], (uint8_t)v[4 * q + 3]);
-    } else if (out_dtype == AT_F32) {
-      float4* op = reinterpret_cast<float4*>((float*)out + o);
-#pragma unroll
-      for (int q = 0; q < 3; ++q)
-        op[q] = make_float4(__fdiv_rn((float)v[4 * q], 255.0f), __fdiv_rn((float)v[4 * q + 1], 255.0f),
-                            __fdiv_rn((float)v[4 * q + 2], 255.0f), __fdiv_rn((float)v[4 * q + 3], 255.0f));
-    } else {
-      __nv_bfloat16* ob = (__nv_bfloat16*)out + o;
-#pragma unroll
-      for (int i = 0; i < kLatSeg; ++i) ob[i] = __float2bfloat16_rn(__fdiv_rn((float)v[i], 255.0f));
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+      }
+      const int total = __shfl_sync(0xffffffffu, incl, 31);
+      if (total) {
+        int base = 0;
+        if (lane == 31) base = atomicAdd(&s_nflag, total);
+        base = __shfl_sync(0xffffffffu, base, 31);
+        int pos = base + incl - cnt;
+        while (near_mask) {
+          const int b = __ffs(near_mask) - 1;
+          near_mask &= near_mask - 1;
+          if (pos < kLatMaxFlagged) s_list[pos] = (unsigned short)(y * dst_w + xs + b);
+          ++pos;
+        }
+      }
     }
+  }
+  if (!exact) return;
+
+  // ---- 4. the queued pixels again, through the float64 map (their stores follow the fast pass's: barrier)
+  __syncthreads();
+  const int nf = s_nflag;
+  if (nf > kLatMaxFlagged) {
+    for (int p = threadIdx.x; p < npix; p += kThreads) exact_pixel(p);
+  } else {
+    for (int i = threadIdx.x; i < nf; i += kThreads) exact_pixel((int)s_list[i]);
   }
 }
 
@@ -881,8 +993,9 @@ extern "C" int at_crop_resample_fisheye62_u8_ex(const uint8_t* src, int64_t fram
     AT_ONCE_PER_DEVICE(
         cudaFuncSetAttribute(crop_resample_lattice_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kLatStageBytes);
         cudaFuncSetAttribute(crop_resample_lattice_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    static const int exact = getenv("AT_CROP_EXACT") == nullptr || atoi(getenv("AT_CROP_EXACT")) != 0;  // 0: A/B only
     crop_resample_lattice_kernel<<<(unsigned)n_crops, kThreads, kLatStageBytes, (cudaStream_t)stream>>>(
-        src, frame_stride, view_stride, row_stride, params, dst_w, dst_h, out, out_dtype, staged_bytes);
+        src, frame_stride, view_stride, row_stride, params, dst_w, dst_h, out, out_dtype, staged_bytes, exact);
   } else if (dst_w % kFastPx == 0 && (src_on_host || staged_bytes != nullptr || getenv("AT_CROP_STAGED") != nullptr)) {
     AT_ONCE_PER_DEVICE(
         cudaFuncSetAttribute(crop_resample_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStageBytes);
@@ -896,7 +1009,7 @@ extern "C" int at_crop_resample_fisheye62_u8_ex(const uint8_t* src, int64_t fram
     crop_resample_kernel<float><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
         src, frame_stride, view_stride, row_stride, params, dst_w, dst_h, out, out_dtype);
   }
-  return at::check_launch("crop_resample_kernel");
+  return abt::check_launch("crop_resample_kernel");
 }
 
 extern "C" int at_resample_homography_f32(const float* images, int n, int H, int W, const float* xfs, int oh, int ow,
@@ -908,7 +1021,7 @@ extern "C" int at_resample_homography_f32(const float* images, int n, int H, int
   AT_REQUIRE(out_divisor != 0.0f, "at_resample_homography_f32: out_divisor is 0");
   dim3 grid((unsigned)n, kSplit);
   resample_homography_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(images, H, W, xfs, oh, ow, out, out_divisor);
-  return at::check_launch("resample_homography_kernel");
+  return abt::check_launch("resample_homography_kernel");
 }
 
 extern "C" int at_crop_pull_source_boxes_u8(const uint8_t* src, uint8_t* dst, int64_t n_frames, int64_t frame_stride,
@@ -930,7 +1043,7 @@ extern "C" int at_crop_pull_source_boxes_u8(const uint8_t* src, uint8_t* dst, in
     if (!ok) cudaGetLastError();
     AT_REQUIRE(ok, "at_crop_pull_source_boxes_u8: the source must be pinned host memory (or device memory)");
   }
-  int grid = max_ctas > 0 ? max_ctas : at::kNumSMs;
+  int grid = max_ctas > 0 ? max_ctas : abt::kNumSMs;
   if (grid > n_crops) grid = n_crops;
   // Bytes in flight = grid x depth x 1 KB.  Measured on B200 (scripts/pull_time.py, bench.py): PCIe
   // saturates (~36-39 GB/s on these short rows) from ~150 KB in flight; every SM-issued PCIe read
@@ -949,5 +1062,5 @@ extern "C" int at_crop_pull_source_boxes_u8(const uint8_t* src, uint8_t* dst, in
   else if (depth == 8) AT_PULL_LAUNCH(8);
   else AT_PULL_LAUNCH(4);
 #undef AT_PULL_LAUNCH
-  return at::check_launch("crop_pull_boxes_kernel");
+  return abt::check_launch("crop_pull_boxes_kernel");
 }

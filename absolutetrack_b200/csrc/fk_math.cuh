@@ -4,7 +4,7 @@
 #pragma once
 #include "at_common.cuh"
 
-namespace at {
+namespace abt {
 
 struct Xf {  // rigid 3x4: rotation r (row-major) + translation t
   float r[9];
@@ -49,4 +49,4 @@ __device__ __forceinline__ void compose(const Xf& a, const Xf& b, Xf& o) {  // o
   }
 }
 
-}  // namespace at
+}  // namespace abt

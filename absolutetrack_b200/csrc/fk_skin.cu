@@ -14,9 +14,9 @@
 
 namespace {
 
-using at::Xf;
-using at::compose;
-using at::joint_local;
+using abt::Xf;
+using abt::compose;
+using abt::joint_local;
 
 constexpr int kBlock = 64;         // hands (= threads) per CTA
 constexpr int kFrameFloats = 12;   // 3x4 rigid frame
@@ -505,11 +505,11 @@ extern "C" int at_eval_recording_f32(const float* tracked_keypoints, const float
   AT_REQUIRE(tracked_keypoints && gt_keypoints && valid_tracking && sums && counts, "at_eval_recording_f32: NULL pointer");
   AT_REQUIRE(n_thresholds == 0 || thresholds != nullptr, "at_eval_recording_f32: thresholds is NULL");
   const int64_t n = n_hands * n_frames;
-  const int64_t blocks = std::min<int64_t>((n + 7) / 8, 4 * at::kNumSMs);
+  const int64_t blocks = std::min<int64_t>((n + 7) / 8, 4 * abt::kNumSMs);
   eval_recording_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
       tracked_keypoints, gt_keypoints, valid_tracking, n_hands, n_frames, thresholds, n_thresholds, sums,
       reinterpret_cast<unsigned long long*>(counts));
-  return at::check_launch("eval_recording_kernel");
+  return abt::check_launch("eval_recording_kernel");
 }
 
 extern "C" int at_eval_accumulate_f32(const float* landmarks, const float* gt_landmarks, const float* joint_angles,
@@ -519,10 +519,10 @@ extern "C" int at_eval_accumulate_f32(const float* landmarks, const float* gt_la
   if (n == 0) return AT_OK;
   AT_REQUIRE(landmarks && gt_landmarks && sums, "at_eval_accumulate_f32: NULL pointer");
   AT_REQUIRE((joint_angles == nullptr) == (gt_joint_angles == nullptr), "at_eval_accumulate_f32: give both joint-angle arrays or none");
-  const int64_t blocks = std::min<int64_t>((n + kEvalWarps - 1) / kEvalWarps, 4 * at::kNumSMs);
+  const int64_t blocks = std::min<int64_t>((n + kEvalWarps - 1) / kEvalWarps, 4 * abt::kNumSMs);
   eval_accumulate_kernel<<<(unsigned)blocks, kEvalWarps * 32, 0, (cudaStream_t)stream>>>(landmarks, gt_landmarks, joint_angles,
                                                                                         gt_joint_angles, valid, n, sums);
-  return at::check_launch("eval_accumulate_kernel");
+  return abt::check_launch("eval_accumulate_kernel");
 }
 
 extern "C" int at_fk_skin_scaled_f32(const float* joint_angles, const float* wrist_xforms, const int64_t* hand_idx,
@@ -552,14 +552,14 @@ extern "C" int at_fk_skin_scaled_f32(const float* joint_angles, const float* wri
     AT_ONCE_PER_DEVICE(
         cudaFuncSetAttribute(fk_skin_shared_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fast_smem);
         cudaFuncSetAttribute(fk_skin_shared_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-    const int64_t fb = std::min<int64_t>((n + kFast - 1) / kFast, kFastCtas * at::kNumSMs);  // persistent
+    const int64_t fb = std::min<int64_t>((n + kFast - 1) / kFast, kFastCtas * abt::kNumSMs);  // persistent
     fk_skin_shared_kernel<<<(unsigned)fb, kFast, fast_smem, (cudaStream_t)stream>>>(
         joint_angles, wrist_xforms, hand_idx, *model, n, landmarks, translation_scale, wrist_out);
-    return at::check_launch("fk_skin_shared_kernel");
+    return abt::check_launch("fk_skin_shared_kernel");
   }
   const int64_t blocks = (n + kBlock - 1) / kBlock;
   AT_REQUIRE(blocks <= 0x7fffffffLL, "at_fk_skin_f32: n too large");
   fk_skin_kernel<<<(unsigned)blocks, kBlock, smem_bytes, (cudaStream_t)stream>>>(
       joint_angles, wrist_xforms, hand_idx, *model, n, landmarks, translation_scale, wrist_out);
-  return at::check_launch("fk_skin_kernel");
+  return abt::check_launch("fk_skin_kernel");
 }

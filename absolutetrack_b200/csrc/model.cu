@@ -9,7 +9,7 @@
 
 #include "conv.cuh"
 
-namespace at {
+namespace abt {
 
 namespace {
 
@@ -129,14 +129,14 @@ int encoder_forward_f32(const float* blob, const void* crops, int crop_dtype, in
   return conv_nhwc_f32(T[L_PROJ], blob, X, 256, 0, nullptr, 0, features, 72, 0, c, H, W, false, s);
 }
 
-}  // namespace at
+}  // namespace abt
 
-namespace at { int64_t encoder_workspace_bytes_bf16(int c); }
+namespace abt { int64_t encoder_workspace_bytes_bf16(int c); }
 
 extern "C" int at_model_layer_table(AtLayerInfo* table, int capacity) {
-  const at::ConvLayer* T = at::layer_table();
+  const abt::ConvLayer* T = abt::layer_table();
   if (table != nullptr) {
-    for (int i = 0; i < at::L_COUNT && i < capacity; ++i) {
+    for (int i = 0; i < abt::L_COUNT && i < capacity; ++i) {
       memset(&table[i], 0, sizeof(AtLayerInfo));
       strncpy(table[i].name, T[i].name, sizeof(table[i].name) - 1);
       table[i].cin = T[i].cin; table[i].cout = T[i].cout; table[i].ksize = T[i].ksize; table[i].stride = T[i].stride;
@@ -144,28 +144,28 @@ extern "C" int at_model_layer_table(AtLayerInfo* table, int capacity) {
       table[i].bias_offset = T[i].bias_offset;
     }
   }
-  return at::L_COUNT;
+  return abt::L_COUNT;
 }
 
-extern "C" int64_t at_model_blob_floats(void) { return at::blob_floats(); }
+extern "C" int64_t at_model_blob_floats(void) { return abt::blob_floats(); }
 
 extern "C" int64_t at_encoder_workspace_bytes(int c, int precision) {
   if (c < 0) return AT_ERR_INVALID_ARGUMENT;
-  if (precision == AT_PREC_BF16 || precision == AT_PREC_FP16) return at::encoder_workspace_bytes_bf16(c);
+  if (precision == AT_PREC_BF16 || precision == AT_PREC_FP16) return abt::encoder_workspace_bytes_bf16(c);
   // X, T, Y (full) + D (half)
-  return (int64_t)sizeof(float) * (at::kActFloatsPerCrop * 3 + at::kActFloatsPerCrop / 2) * (int64_t)c + 256;
+  return (int64_t)sizeof(float) * (abt::kActFloatsPerCrop * 3 + abt::kActFloatsPerCrop / 2) * (int64_t)c + 256;
 }
 
-namespace at {
+namespace abt {
 // tcgen05 path (conv_tc.cu)
 int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* crops, int crop_dtype, int c,
                          float* features, void* workspace, int64_t workspace_bytes, int fmt, int prepared_c,
-                         cudaStream_t s);
+                         int32_t* status, cudaStream_t s);
 int64_t encoder_workspace_bytes_bf16(int c);
 int encoder_chunk_crops();
-}  // namespace at
+}  // namespace abt
 
-extern "C" int at_encoder_chunk_crops(void) { return at::encoder_chunk_crops(); }
+extern "C" int at_encoder_chunk_crops(void) { return abt::encoder_chunk_crops(); }
 
 extern "C" int at_encoder_forward(const float* blob, const void* bf16_blob, const void* crops, int crop_dtype, int c,
                                   float* features, void* workspace, int64_t workspace_bytes, int precision,
@@ -177,23 +177,30 @@ extern "C" int at_encoder_forward(const float* blob, const void* bf16_blob, cons
 extern "C" int at_encoder_forward_prepared(const float* blob, const void* bf16_blob, const void* crops, int crop_dtype,
                                            int c, float* features, void* workspace, int64_t workspace_bytes,
                                            int precision, int prepared_chunk, void* stream) {
+  return at_encoder_forward_status(blob, bf16_blob, crops, crop_dtype, c, features, workspace, workspace_bytes, precision,
+                                   prepared_chunk, nullptr, stream);
+}
+
+extern "C" int at_encoder_forward_status(const float* blob, const void* bf16_blob, const void* crops, int crop_dtype,
+                                         int c, float* features, void* workspace, int64_t workspace_bytes,
+                                         int precision, int prepared_chunk, int32_t* status, void* stream) {
   AT_REQUIRE(c >= 0, "at_encoder_forward: c < 0");
   if (c == 0) return AT_OK;
   AT_REQUIRE(blob && crops && features && workspace, "at_encoder_forward: NULL pointer");
   AT_REQUIRE(crop_dtype == AT_U8 || crop_dtype == AT_F32, "at_encoder_forward: crops must be AT_U8 or AT_F32");
   AT_REQUIRE(c <= 200000, "at_encoder_forward: at most 200000 crops per call");
   if (workspace_bytes < at_encoder_workspace_bytes(c, precision)) {
-    at::set_error("at_encoder_forward: workspace too small (%lld < %lld)", (long long)workspace_bytes,
+    abt::set_error("at_encoder_forward: workspace too small (%lld < %lld)", (long long)workspace_bytes,
                   (long long)at_encoder_workspace_bytes(c, precision));
     return AT_ERR_WORKSPACE_TOO_SMALL;
   }
   if (precision == AT_PREC_FP32)
-    return at::encoder_forward_f32(blob, crops, crop_dtype, c, features, workspace, (cudaStream_t)stream);
+    return abt::encoder_forward_f32(blob, crops, crop_dtype, c, features, workspace, (cudaStream_t)stream);
   if (precision == AT_PREC_BF16 || precision == AT_PREC_FP16) {
     AT_REQUIRE(bf16_blob != nullptr, "at_encoder_forward: the prepacked 16-bit blob is required for AT_PREC_BF16/FP16");
-    return at::encoder_forward_bf16(blob, bf16_blob, crops, crop_dtype, c, features, workspace, workspace_bytes,
-                                    precision == AT_PREC_BF16 ? 1 : 0, prepared_chunk, (cudaStream_t)stream);
+    return abt::encoder_forward_bf16(blob, bf16_blob, crops, crop_dtype, c, features, workspace, workspace_bytes,
+                                    precision == AT_PREC_BF16 ? 1 : 0, prepared_chunk, status, (cudaStream_t)stream);
   }
-  at::set_error("at_encoder_forward: bad precision %d", precision);
+  abt::set_error("at_encoder_forward: bad precision %d", precision);
   return AT_ERR_INVALID_ARGUMENT;
 }

@@ -10,7 +10,7 @@
 
 #include "conv.cuh"
 
-namespace at {
+namespace abt {
 namespace {
 
 constexpr int kPix = 36;
@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(128) tail_prepare_kernel(PrepArgs a) {
     int nv = (int)(r1 - r0);
     bool bad = r0 < 0 || r1 > a.in.c || nv < 1 || nv > 2 || m < 0 || m >= a.st.capacity;
     if (bad) {
-      atomicExch(a.status, 1);
+      atomicOr(a.status, 1);  // AT_STATUS_BAD_SAMPLE_RANGE (the encoder ORs its own bit into the same word)
       nv = 0;
     }
     s_info[0] = (int)r0; s_info[1] = nv; s_info[2] = (int)m; s_info[3] = bad ? 0 : (int)a.in.use_memory[i];
@@ -395,15 +395,15 @@ constexpr int64_t kWsSkel = 144;
 constexpr int64_t kWsPerSample = kWsFuseIn + kWsF1 + kWsF2 + kWsF3 + 4 * kWsT + 3 * kWsH + kWsHo + kWsSkel;
 
 }  // namespace
-}  // namespace at
+}  // namespace abt
 
 extern "C" int64_t at_tail_workspace_bytes(int n) {
   if (n < 0) return AT_ERR_INVALID_ARGUMENT;
   // fp32 NHWC activations of the tail + the split fp16 planes of the tcgen05 pose head
-  return (int64_t)sizeof(float) * at::kWsPerSample * (int64_t)n + 256 + at::head_tc_workspace_bytes(n);
+  return (int64_t)sizeof(float) * abt::kWsPerSample * (int64_t)n + 256 + abt::head_tc_workspace_bytes(n);
 }
 
-namespace at {
+namespace abt {
 namespace {
 // byte offset of layer `id`'s pre-split fp16 weights inside the tail operand blob (layers L_FUSION.. in order)
 int64_t f16_blob_offset(int id) {
@@ -414,9 +414,9 @@ int64_t f16_blob_offset(int id) {
   return off;
 }
 }  // namespace
-}  // namespace at
+}  // namespace abt
 
-namespace at {
+namespace abt {
 namespace {
 // the tcgen05 operands of the 8 pose-head 3x3 convs (4 per head) follow the mma.sync operands
 int64_t head_tc_blob_offset(int id) {
@@ -424,12 +424,12 @@ int64_t head_tc_blob_offset(int id) {
   return round_up(f16_blob_offset(L_COUNT), 256) + (int64_t)k * round_up(head_tc_weight_bytes(), 256);
 }
 }  // namespace
-}  // namespace at
+}  // namespace abt
 
-extern "C" int64_t at_tail_f16_blob_bytes(void) { return at::head_tc_blob_offset(at::L_HEAD_U + 4); }
+extern "C" int64_t at_tail_f16_blob_bytes(void) { return abt::head_tc_blob_offset(abt::L_HEAD_U + 4); }
 
 extern "C" int at_tail_prepack_f16(const float* blob, void* f16_blob, void* stream) {
-  using namespace at;
+  using namespace abt;
   AT_REQUIRE(blob && f16_blob, "at_tail_prepack_f16: NULL argument");
   AT_REQUIRE((((uintptr_t)f16_blob) & 15) == 0, "at_tail_prepack_f16: the operand blob must be 16-byte aligned");
   const ConvLayer* T = layer_table();
@@ -454,7 +454,7 @@ extern "C" int at_tail_forward(const float* blob, const AtTailInputs* in, AtTemp
 extern "C" int at_tail_forward_f16(const float* blob, const void* f16_blob, const AtTailInputs* in,
                                    AtTemporalState* state, const AtTailOutputs* out, void* workspace,
                                    int64_t workspace_bytes, void* stream_) {
-  using namespace at;
+  using namespace abt;
   AT_REQUIRE(blob && in && state && out, "at_tail_forward: NULL argument");
   AT_REQUIRE((((uintptr_t)f16_blob) & 15) == 0, "at_tail_forward: the fp16 operand blob must be 16-byte aligned");
   const int n = in->n, c = in->c;

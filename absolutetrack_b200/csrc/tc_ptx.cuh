@@ -5,7 +5,7 @@
 #include <cuda_fp16.h>
 #include <stdint.h>
 
-namespace at {
+namespace abt {
 namespace ptx {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -162,10 +162,16 @@ __device__ __forceinline__ uint32_t pack2(float a, float b, int fmt) {
     __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<uint32_t*>(&v);
   }
-  // saturate instead of overflowing to inf (fp16 max 65504)
-  __half2 v = __floats2half2_rn(fminf(fmaxf(a, -65504.f), 65504.f), fminf(fmaxf(b, -65504.f), 65504.f));
-  return *reinterpret_cast<uint32_t*>(&v);
+  // one F2FP.SATFINITE: |x| > 65504 becomes +-65504 instead of inf, NaN stays NaN; overflow_probe
+  // (below) sees both, so a saturated activation is reported instead of silently clamped
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  return r;
 }
+// fp16 pairs: bit 15 / 31 of the result is set when a half is +-65504 (saturated), inf or NaN
+// ((h & 0x7FFF) >= 0x7BFF).  OR the probes of many words together and test `& 0x80008000` once.
+__device__ __forceinline__ uint32_t overflow_probe(uint32_t packed_f16x2) { return (packed_f16x2 & 0x7FFF7FFFu) + 0x04010401u; }
+constexpr uint32_t kOverflowProbeMask = 0x80008000u;
 __device__ __forceinline__ void unpack2(uint32_t u, int fmt, float& a, float& b) {
   if (fmt) {
     a = __uint_as_float(u << 16);
@@ -181,9 +187,8 @@ __device__ __forceinline__ uint16_t pack1(float a, int fmt) {
     __nv_bfloat16 v = __float2bfloat16_rn(a);
     return *reinterpret_cast<uint16_t*>(&v);
   }
-  __half v = __float2half_rn(fminf(fmaxf(a, -65504.f), 65504.f));
-  return *reinterpret_cast<uint16_t*>(&v);
+  return (uint16_t)(pack2(a, 0.f, 0) & 0xFFFFu);
 }
 
 }  // namespace ptx
-}  // namespace at
+}  // namespace abt

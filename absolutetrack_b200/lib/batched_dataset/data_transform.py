@@ -14,7 +14,7 @@ from typing import Any, Dict, List, Optional, Tuple
 import numpy as np
 import torch
 
-from ... import _cabi
+from .. import _cabi
 from ..common.hand import HandModel, mirrored_hand_model
 from ..data_utils import bundles
 from .sample import RawSample, parse_raw_buffers
@@ -187,7 +187,7 @@ def iter_preprocessed_sequences(mono_idx_path: str, labels_idx_path: str, crop_s
     preprocess) (run_inference_torch_data.py:166-177), with the Sampler's rank striding
     (async_dataset.py:558-559 = distributed.shard_indices) and without worker processes - the
     per-sequence work is two launches.  Yields (sequence index, ModelInput, ModelTarget)."""
-    from ...distributed import shard_indices
+    from absolutetrack_b200.distributed import shard_indices
     from ..data_utils.idxbinfile import TorchIdx
 
     mono_idx, labels_idx = TorchIdx(mono_idx_path), TorchIdx(labels_idx_path)

@@ -11,9 +11,21 @@ writer).
 """
 import math
 import os
-from typing import Any, List, Optional, Sequence, Tuple, Union
+from enum import Enum
+from typing import Any, Dict, List, Optional, Sequence, Tuple, Union
 
 import numpy as np
+
+# type names the reference's own readers import from this module (async_dataset.py:42, idxbinfile.py:24-33)
+Buffer = Union[bytes, memoryview]
+MsgpackObject = Dict[str, Any]
+RawField = Union[np.ndarray, MsgpackObject]
+
+
+class BinFormat(Enum):
+    TENSOR = 0
+    MSGPACK = 1
+
 
 MAGIC = 0x584449544E54
 _CODE_TO_DTYPE = {1: "uint8", 2: "int8", 3: "int16", 4: "int32", 5: "int64", 6: "float32", 7: "float64", 8: "object"}

@@ -6,6 +6,7 @@ preceding conv / linear and packs one float32 blob in the layout the CUDA librar
 through at_model_layer_table() ([kh][kw][Cin][CoutP] + bias[CoutP] per layer).
 """
 import math
+import os
 from typing import Dict, List, Tuple
 
 import torch
@@ -55,10 +56,43 @@ def _has_bias(name: str) -> bool:
     return True
 
 
+def network_layers() -> List[Dict]:
+    """The 46 conv / linear layers of the network in blob order: name, cin, cout, ksize, stride.
+    Pure Python (the architecture is fixed: model_opts.py:12 `resnet_layers_2352-f32`,
+    model_utils.py:107-208); tests assert that it equals the C library's at_model_layer_table()."""
+    out = []
+
+    def add(name, cin, cout, k, stride=1):
+        out.append(dict(name=name, cin=cin, cout=cout, ksize=k, stride=stride))
+
+    add("backbone.stem", 1, 32, 3)
+    cin = 32
+    for li, (nb, cout, stride) in enumerate(((2, 32, 1), (3, 64, 2), (5, 128, 2), (2, 256, 2)), start=1):
+        for b in range(nb):
+            st = stride if b == 0 else 1
+            add(f"backbone.layer{li}.{b}.conv1", cin, cout, 3, st)
+            add(f"backbone.layer{li}.{b}.conv2", cout, cout, 3)
+            if st != 1 or cin != cout:
+                add(f"backbone.layer{li}.{b}.down", cin, cout, 1, st)
+            cin = cout
+    add("backbone.proj", 256, 72, 1)
+    for i, (ci, co) in enumerate(((144, 108), (108, 72), (72, 72))):
+        add(f"fusion.{i}", ci, co, 1)
+    for i in range(3):
+        add(f"temporal.{i}", 90, 90, 1)
+    add("skeleton", 132, 144, 1)
+    for head, c, n_out in (("head_k", 76, 62), ("head_u", 72, 63)):
+        for blk in range(2):
+            add(f"{head}.{blk}.conv1", c, c, 3)
+            add(f"{head}.{blk}.conv2", c, c, 3)
+        add(f"{head}.out", c, n_out, 1)
+    return out
+
+
 def state_dict_spec() -> List[Tuple[str, Tuple[int, ...]]]:
-    """(key, shape) of every tensor of the reference checkpoint (252 entries)."""
+    """(key, shape) of every tensor of the reference checkpoint (252 entries).  No native code involved."""
     spec = []
-    for L in _cabi.layer_table():
+    for L in network_layers():
         conv, bn = _layer_keys(L["name"])
         if L["name"] == "skeleton":
             spec.append((conv + ".weight", (L["cout"], L["cin"])))
@@ -158,8 +192,16 @@ def model_from_state_dict(sd: Dict[str, torch.Tensor], **kwargs) -> UmeTrackMode
     return UmeTrackModel(pack_state_dict(sd), model_opts=ModelOpts(), **kwargs)
 
 
+DEFAULT_PRECISION = "fp16"
+
+
 def load_pretrained_model(model_path: str) -> UmeTrackModel:
-    """Reference model_loader.py:53-88: build the model and load the checkpoint at `model_path`."""
+    """Reference model_loader.py:53-88: build the model and load the checkpoint at `model_path`.
+
+    The encoder format is chosen without editing a script: environment variable AT_PRECISION =
+    "fp16" (default: the tcgen05 encoder, inside north_star's 0.1 mm end-to-end tolerance, and
+    with an overflow flag, UmeTrackModel.check_status), "bf16" (same kernels, 8-bit mantissa) or
+    "fp32" (CUDA-core reference-grade encoder)."""
     with open(model_path, "rb") as fp:
         sd = torch.load(fp, map_location="cpu")
-    return model_from_state_dict(sd)
+    return model_from_state_dict(sd, precision=os.environ.get("AT_PRECISION", DEFAULT_PRECISION))

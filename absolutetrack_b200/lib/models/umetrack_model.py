@@ -114,6 +114,7 @@ class UmeTrackModel(nn.Module):
         cur = self._mem_features.shape[0] if self._mem_features.numel() else 0
         if cur >= required and self._mem_features.device == device:
             return
+        required = max(cur, required)  # a pure device move keeps every slot (the state may have grown before)
         mem = torch.zeros(required, 6, 6, 18, dtype=torch.float32, device=device)
         ext = torch.zeros(required, 4, 4, dtype=torch.float32, device=device)
         if cur:  # grow, keeping old entries (temporal.py:105-125)
@@ -182,11 +183,11 @@ class UmeTrackModel(nn.Module):
         prepared = self._enc_prepared[1] if self._enc_prepared is not None and self._enc_prepared[0] == key else 0
         self._enc_prepared = None
         with torch.cuda.device(dev):
-            rc = lib.at_encoder_forward_prepared(
+            rc = lib.at_encoder_forward_status(
                 self._blob.data_ptr(), _cabi.ptr(bf), crops.data_ptr(), dt, c, feats.data_ptr(), ws.data_ptr(),
-                ws.numel(), prec, prepared, _cabi.stream_ptr(dev),
+                ws.numel(), prec, prepared, self._status_word(dev).data_ptr(), _cabi.stream_ptr(dev),
             )
-        _cabi.check(rc, "at_encoder_forward_prepared")
+        _cabi.check(rc, "at_encoder_forward_status")
         if c > 0:
             chunk = lib.at_encoder_chunk_crops()
             self._enc_prepared = (key, c % chunk if c % chunk else min(c, chunk))
@@ -227,8 +228,7 @@ class UmeTrackModel(nn.Module):
         out_wrist = torch.empty(n, 4, 4, **f32)
         out_sig = torch.empty(n, 21, **f32)
         out_scale = torch.empty(n, **f32) if head_mode == _cabi.AT_HEAD_PREDICT_SCALE else None
-        if self._status is None or self._status.device != dev:
-            self._status = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._status_word(dev)
         tin = _cabi.AtTailInputs(
             feats.data_ptr(), intr.data_ptr(), extr.data_ptr(), srange.data_ptr(), midx.data_ptr(), usem.data_ptr(),
             hidx.data_ptr(), _cabi.ptr(axes), _cabi.ptr(rest), n, c, n_skel, head_mode,
@@ -253,11 +253,25 @@ class UmeTrackModel(nn.Module):
             joint_angles=out_angles, wrist_xfs=out_wrist, skel_scales=out_scale, landmark_uncertainty_sigmas=out_sig
         )
 
+    def _status_word(self, dev) -> torch.Tensor:
+        if self._status is None or self._status.device != dev:
+            self._status = torch.zeros(1, dtype=torch.int32, device=dev)
+        return self._status
+
     def check_status(self) -> None:
-        """Raise if any call since the last check saw a bad sample_range / memory_idx (syncs)."""
-        if self._status is not None and int(self._status.item()) != 0:
-            self._status.zero_()
-            raise _cabi.AbsoluteTrackError(
-                "at_tail_forward: invalid sample_range (views per sample must be 1 or 2, inside the crop "
-                "batch) or memory_idx outside the temporal-state capacity"
-            )
+        """Raise if any call since the last check saw a bad sample_range / memory_idx, or an fp16
+        activation of the encoder beyond the fp16 range (syncs; clears the flags)."""
+        if self._status is None:
+            return
+        st = int(self._status.item())
+        if st == 0:
+            return
+        self._status.zero_()
+        msgs = []
+        if st & _cabi.AT_STATUS_BAD_SAMPLE_RANGE:
+            msgs.append("at_tail_forward: invalid sample_range (views per sample must be 1 or 2, inside the crop "
+                        "batch) or memory_idx outside the temporal-state capacity")
+        if st & _cabi.AT_STATUS_FP16_OVERFLOW:
+            msgs.append("at_encoder_forward: an fp16 activation saturated at +-65504 (or is inf / NaN): these weights "
+                        "need precision='bf16' or 'fp32' (AT_PRECISION)")
+        raise _cabi.AbsoluteTrackError("; ".join(msgs) or f"device status {st}")

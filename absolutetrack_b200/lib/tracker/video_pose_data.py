@@ -54,9 +54,13 @@ def load_hand_model_from_dict(hand_model_dict) -> HandModel:
     return HandModel(**{k: (torch.Tensor(v) if isinstance(v, list) else v) for k, v in hand_model_dict.items()})
 
 
-def _load_hand_pose_labels(p: str) -> HandPoseLabels:
+def _load_json(p: str):
     with open(p, "rb") as f:
-        labels = json.load(f)
+        return json.load(f)
+
+
+def _load_hand_pose_labels(p: str) -> HandPoseLabels:
+    labels = _load_json(p)
     return HandPoseLabels(
         cameras=[read_camera_from_json(c) for c in labels["cameras"]],
         camera_angles=labels["camera_angles"],

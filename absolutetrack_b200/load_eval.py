@@ -15,8 +15,17 @@ from typing import Dict, Optional
 import numpy as np
 import torch
 
-from . import _cabi
-from .lib.common import metric_utils
+try:
+    from . import _cabi
+    from .lib.common import metric_utils
+except ImportError:  # found as top-level `load_eval` (absolutetrack_b200/ itself on sys.path)
+    import sys
+
+    _root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if _root not in sys.path:
+        sys.path.append(_root)
+    from absolutetrack_b200 import _cabi
+    from absolutetrack_b200.lib.common import metric_utils
 
 
 class EvalSums:
@@ -96,7 +105,7 @@ def aggregate_metrics(output_dir: str, rank: int = 0, world: int = 1, verbose: b
     ({'tracked_keypoints', 'gt_keypoints', 'valid_tracking'}, written by run_eval_*.py:96-104).
     With world > 1 the files are strided across ranks (distributed.shard) and the accumulators
     all-reduced; every rank returns the same table."""
-    from .distributed import shard
+    from absolutetrack_b200.distributed import shard
 
     files = []
     for cur_dir, _, filenames in os.walk(output_dir):

@@ -14,5 +14,7 @@ for f in at_error fk_skin crop_resample crop_cameras conv_f32 conv_tc model tail
   fi
 done
 for p in "${pids[@]}"; do wait $p; done
-nvcc -shared -o $OUT build/*.o -lcudart
+# only the C-ABI (at_*) is exported: internal C++ symbols (namespace abt) stay local to the library
+printf '{ global: at_*; local: *; };\n' > build/exports.map
+nvcc -shared -o $OUT build/*.o -lcudart -Xlinker --version-script=build/exports.map
 echo "built $OUT"

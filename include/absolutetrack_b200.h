@@ -310,6 +310,18 @@ int at_encoder_forward_prepared(const float* blob, const void* bf16_blob, const 
                                 int c, float* features, void* workspace, int64_t workspace_bytes,
                                 int precision, int prepared_chunk, void* stream);
 
+/* Same call with a device status word (may be NULL).  AT_PREC_FP16 stores activations as fp16, whose
+ * range ends at 65504 where the reference's fp32 activations (backbone_resnet.py:56-72: twelve residual
+ * blocks without normalisation after the BN fold) have none: a value beyond it is stored as +-65504, and
+ * bit 1 of *status (value AT_STATUS_FP16_OVERFLOW) is set by the layer that produced it - also for inf /
+ * NaN - so that an overflow is reported instead of silently clamped.  *status is only ever OR-ed into;
+ * it is the same word at_tail_forward sets to AT_STATUS_BAD_SAMPLE_RANGE (bit 0). */
+#define AT_STATUS_BAD_SAMPLE_RANGE 1
+#define AT_STATUS_FP16_OVERFLOW 2
+int at_encoder_forward_status(const float* blob, const void* bf16_blob, const void* crops, int crop_dtype,
+                              int c, float* features, void* workspace, int64_t workspace_bytes,
+                              int precision, int prepared_chunk, int32_t* status, void* stream);
+
 /* Test/debug entry: ONE backbone conv layer (layer_id from at_model_layer_table, 1..28) through the
  * tcgen05 path on float32 NHWC tensors: in [n,H,W,cin] -> out [n,H/stride,W/stride,cout], optional
  * residual res [n,H/stride,W/stride,cout], optional ReLU.  mt = 128-pixel sub-tiles per CTA tile (0 = default). */

@@ -3,7 +3,7 @@
 #include <cstdio>
 #include <cuda_runtime.h>
 #include "tc_ptx.cuh"
-using namespace at::ptx;
+using namespace abt::ptx;
 
 __device__ __forceinline__ uint64_t desc_any(uint32_t addr, uint32_t lbo, uint32_t sbo) {
   uint64_t d = 0;

@@ -216,14 +216,35 @@ def test_crop_fp64_map_is_bit_exact_vs_reference_golden(cuda_lib, gold):
     assert mism == 0, f"{mism} of {out.size} pixels differ"
 
 
-def test_crop_fp32_map_within_one_grey_level_on_smooth_images(cuda_lib, gold):
+def test_crop_fp32_lattice_map_is_bit_exact_vs_reference_golden(cuda_lib, gold):
+    """The fp32 lattice-map mode (the one bench.py times) re-evaluates every pixel whose interpolated
+    coordinate lies next to a 1/32-px rounding boundary through the float64 map: all 52 golden crops,
+    noise images included, must be identical to tracker._warp_image (north_star: crops within 1/255 per
+    pixel - here 0), in every output dtype."""
     W = gold["warp"]
-    out = _run_crops(W["meta"], "fp32").astype(np.int32)
-    ref = W["crops"].astype(np.int32)
-    smooth = W["meta"][:, 3] == 1
-    d = np.abs(out - ref)
-    assert d[smooth].max() <= 1                      # north_star: crops within 1/255 per pixel
-    assert (d[~smooth] > 1).mean() < 2e-3             # noise images: rare 1/32-px bin flips only
+    out = _run_crops(W["meta"], "fp32")
+    mism = int((out != W["crops"]).sum())
+    assert mism == 0, f"{mism} of {out.size} pixels differ"
+    f = _run_crops(W["meta"][:6], "fp32", torch.float32)
+    assert np.array_equal(f, W["crops"][:6].astype(np.float32) / 255.0)
+
+
+def test_crop_fp32_lattice_map_is_bit_exact_on_every_golden_frame(cuda_lib, gold):
+    """Wider sweep than warp.npz: every crop of the 123 geometry frames (up to 4 per frame) on a noise and a
+    smooth multi-view frame, fp32 lattice mode == fp64 mode (itself pinned bit-exact to the reference above)."""
+    from absolutetrack_b200.lib.tracker.tracker import crop_resample_cuda, pack_crop_params
+
+    G = gold["geometry"]
+    K = G["crop_cam"].shape[0]
+    meta = [(k, h, s, 0, 0) for k in range(K) for h in range(2) for s in range(2) if G["crop_cam"][k, h, s] >= 0]
+    recs = [(i % 2, int(G["crop_cam"][m[0], m[1], m[2]]), r) for i, (m, r) in enumerate(zip(meta, _crop_records(np.array(meta))))]
+    frames = torch.from_numpy(np.stack([scenario.synth_frame("noise", 31), scenario.synth_frame("smooth", 32)])).cuda()
+    params = torch.from_numpy(pack_crop_params(recs)).cuda()
+    args = (frames, 480 * 2544, 636, 2544, params, (96, 96), torch.uint8)
+    a = crop_resample_cuda(*args, "fp32")
+    b = crop_resample_cuda(*args, "fp64")
+    mism = int((a != b).sum())
+    assert mism == 0, f"{mism} of {a.numel()} pixels differ over {len(meta)} crops"
 
 
 def test_crop_float_output_is_level_over_255(cuda_lib, gold):

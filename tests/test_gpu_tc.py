@@ -157,3 +157,29 @@ def test_16bit_tracker_within_tolerance_of_reference(state_dict, gold, precision
     print(precision, "vs reference: dMPJPE per hand (mm)", np.round(errs, 4), "mean |dtheta| (deg)", np.round(dthetas, 4))
     assert np.mean(errs) < E2E_TOL[precision][0], errs
     assert np.mean(dthetas) < E2E_TOL[precision][1], dthetas
+
+
+def test_fp16_overflow_is_reported_not_silently_clamped(state_dict):
+    """fp16 activations end at 65504.  With weights whose activations exceed that (stem gain x 1e6) the
+    encoder must raise the AT_STATUS_FP16_OVERFLOW flag (UmeTrackModel.check_status); the seeded weights
+    themselves, and the bf16 / fp32 encoders on the large-gain weights, must not."""
+    from absolutetrack_b200 import _cabi
+    from absolutetrack_b200.lib.models.model_loader import model_from_state_dict
+
+    g = torch.Generator(device="cuda").manual_seed(3)
+    crops = torch.randint(0, 256, (8, 96, 96), dtype=torch.uint8, device="cuda", generator=g)
+    ok = model_from_state_dict(state_dict, precision="fp16").cuda()
+    ok.encode(crops)
+    ok.check_status()  # no flag
+    big = dict(state_dict)
+    k = "_feature_extractor._image_backbone.0._layers.0.0.weight"
+    big[k] = state_dict[k] * 1e6
+    m = model_from_state_dict(big, precision="fp16").cuda()
+    m.encode(crops)
+    with pytest.raises(_cabi.AbsoluteTrackError, match="fp16 activation saturated"):
+        m.check_status()
+    m.check_status()  # cleared by the raise
+    for prec in ("bf16", "fp32"):
+        m2 = model_from_state_dict(big, precision=prec).cuda()
+        m2.encode(crops)
+        m2.check_status()

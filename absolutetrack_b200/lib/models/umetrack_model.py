@@ -194,9 +194,13 @@ class UmeTrackModel(nn.Module):
         return feats
 
     def _forward(self, frame_data, frame_desc, skel_data, head_mode) -> RegressorOutput:
+        return self.tail(self.encode(frame_data.left_images), frame_data, frame_desc, skel_data, head_mode)
+
+    def tail(self, feats: torch.Tensor, frame_data, frame_desc, skel_data, head_mode=_cabi.AT_HEAD_KNOWN_SKELETON) -> RegressorOutput:
+        """Everything after the per-view encoder (FTL, fusion, SimpleConvRNN step, skeleton features, pose
+        head, decoders, wrist->world) on encoder features [c,6,6,72]; `frame_data.left_images` is not read."""
         lib = _cabi.lib()
         dev = self._blob.device
-        feats = self.encode(frame_data.left_images)
         c = feats.shape[0]
         f32 = dict(device=dev, dtype=torch.float32)
         i64 = dict(device=dev, dtype=torch.int64)

@@ -223,6 +223,8 @@ def main():
     ap.add_argument("--ref-frames", type=int, default=24, help="frames per step of the CPU reference arm")
     ap.add_argument("--cpu-frames", type=int, default=96, help="bounded CPU-baseline sample (frames)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the parity block (timed path vs the CPU oracle, rank 0, N=1)")
+    ap.add_argument("--parity-seqs", type=int, default=256, help="sequences of the parity block (x 8 steps x 2 hands)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -397,11 +399,13 @@ def main():
     crops = [None]
     feats = [None]
 
+    box_bytes = torch.zeros(1, dtype=torch.int64, device=dev)  # source-box bytes the resampler staged (counted by the kernel)
+
     def st_crop(i):
         b = devb[i % NB]
         crops[0] = crop_resample_cuda(
             b.frames, synthetic.H * synthetic.V * synthetic.W, synthetic.W, synthetic.V * synthetic.W, b.crop_params,
-            (96, 96), torch.uint8, args.map_mode)
+            (96, 96), torch.uint8, args.map_mode, staged_bytes=box_bytes)
 
     def st_enc(i):
         feats[0] = model.encode(crops[0])
@@ -412,15 +416,26 @@ def main():
     def st_fk(i):
         skin_landmarks_cuda(tracker._hm_dev, ja_d, wx_d, hand_idx=b0.hand_idx)
 
+    from absolutetrack_b200.lib.models.umetrack_model import InputFrameData, InputFrameDesc
+
+    def st_tail(i):  # everything between the encoder and FK, timed directly on the encoder's features
+        b = devb[i % NB]
+        model.tail(feats[0], InputFrameData(None, b.intrinsics, b.extrinsics),
+                   InputFrameDesc(b.sample_range, b.memory_idx, b.use_memory, b.hand_idx), tracker._skel)
+
     ms_crop, _ = timed(st_crop, args.steps, 3)
+    box0 = int(box_bytes.item())
+    st_crop(0)
+    torch.cuda.synchronize()
+    crop_src_bytes = int(box_bytes.item()) - box0       # of one launch over batch 0
     ms_enc, enc_launches = timed(st_enc, args.steps, 3)
+    ms_tail, tail_launches = timed(st_tail, args.steps, 3)
     ms_fk, _ = timed(st_fk, args.steps, 3)
-    ms_crop /= args.steps; ms_enc /= args.steps; ms_fk /= args.steps
-    ms_tail = max(ms_step - ms_crop - ms_enc - ms_fk, 0.0)
+    ms_crop /= args.steps; ms_enc /= args.steps; ms_fk /= args.steps; ms_tail /= args.steps
 
     enc_tflops = ENCODER_FLOP_PER_CROP * c / (ms_enc * 1e-3) / 1e12
     tf_peak = peaks["tf_burst"]  # the encoder is timed alone, in short bursts -> burst denominator
-    crop_bytes = c * (CROP_SRC_BYTES + 96 * 96 * 1 + 256)
+    crop_bytes = crop_src_bytes + c * (96 * 96 * 1 + 256)   # source boxes (summed by the kernel) + u8 crops + parameter records
     crop_gbs = crop_bytes / (ms_crop * 1e-3) / 1e9
     fk_gbs = n * FK_BYTES_PER_HAND / (ms_fk * 1e-3) / 1e9
 
@@ -443,6 +458,15 @@ def main():
                         "sample": f"{args.cpu_frames} consecutive 2-hand frames of the same stream, frame by frame "
                                   f"(numpy fp64 warp + fixed-point remap, torch-CPU fp32 network with {cores} threads, numpy FK); "
                                   "value_with_crop_cameras adds the reference's per-frame gen_crop_cameras (the baseline of e2e_from_poses)"}
+
+    parity_block = None
+    if rank == 0 and world == 1 and not args.no_parity:
+        # the timed configuration against the CPU oracle (oracle/ is test infrastructure: here only as the checker)
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import parity
+
+        parity_block = parity.timed_path_parity(S=args.parity_seqs, T=8, precision=args.precision, map_mode=args.map_mode,
+                                                ingest=args.ingest)
 
     if rank == 0:
         sys.stdout.flush()
@@ -469,8 +493,12 @@ def main():
                          "frac_of_sustained_peak": enc_tflops / peaks["tf_sust"],
                          "launches_per_step": enc_launches // max(1, args.steps)},
             "stages": {"crop_ms": ms_crop, "encoder_ms": ms_enc, "tail_ms": ms_tail, "fk_ms": ms_fk,
+                       "tail_launches": tail_launches // max(1, args.steps),
+                       "note": "each stage timed on its own with CUDA events (the tail directly on the encoder's features, not by subtraction)",
                        "crop_gbs": crop_gbs, "crop_hbm_frac": crop_gbs / peaks["hbm"],
+                       "crop_source_box_bytes_per_crop": crop_src_bytes / max(1, c),
                        "fk_gbs": fk_gbs, "fk_hbm_frac": fk_gbs / peaks["hbm"]},
+            "parity": parity_block,
             "mpjpe_vs_gt_mm_random_weights": mpjpe,
             "cpu_baseline": cpu_baseline,
             "clocks": clocks,

@@ -106,6 +106,7 @@ class AtRigCamera(C.Structure):
     ]
 
 
+CROP_CAMERAS_STATIC_MAX_POSES = 2048  # AT_CROP_CAMERAS_STATIC_MAX_POSES
 RIG_CAMERA_BYTES = 112
 assert C.sizeof(AtRigCamera) == RIG_CAMERA_BYTES
 
@@ -180,6 +181,11 @@ SIGNATURES = {
         _I,
         [C.POINTER(AtCropCameraInputs), C.POINTER(AtHandModel), C.POINTER(AtCropCameraOpts),
          C.POINTER(AtCropCameraOutputs), _VP, _I64, _VP],
+    ),
+    "at_gen_crop_cameras_static": (
+        _I,
+        [C.POINTER(AtCropCameraInputs), C.POINTER(AtHandModel), C.POINTER(AtCropCameraOpts),
+         C.POINTER(AtCropCameraOutputs), _VP],
     ),
     "at_model_layer_table": (_I, [C.POINTER(AtLayerInfo), _I]),
     "at_model_blob_floats": (_I64, []),

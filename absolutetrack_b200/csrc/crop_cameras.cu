@@ -16,6 +16,8 @@
 //      offsets and the (n, c) counts the host needs to size the next launches.
 //   3. crop_cameras_emit_kernel   one warp per pose: copy the slots to their compacted position
 //      (the reference's order), sample_range / hand_idx / memory_idx / use_memory, history update.
+#include <mutex>
+
 #include "at_common.cuh"
 #include "fk_math.cuh"
 
@@ -585,4 +587,64 @@ extern "C" int at_gen_crop_matrices_f32(const float* orig_extrinsics, const floa
       orig_extrinsics, orig_intrinsics, crop_points, mirror_image, n_frames, n_views, n_pts, crop_w, crop_h,
       focal_multiplier, 5.0f, extrinsics_xf, new_intrinsics, resample_xf, n_errors);
   return abt::check_launch("crop_matrices_kernel");
+}
+
+// ------------------------------------------------------------------------------------------
+// at_gen_crop_cameras_static: the same three launches with the between-pass scratch (pose headers + per-view
+// slots) in a file-scope device array instead of a caller-provided workspace.  No counterpart in the
+// reference; added for callers that cannot allocate device memory
+// (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Every GPU that loads the
+// library holds the array (about 4 MB) until the process exits.
+namespace {
+
+constexpr int kStaticMaxPoses = AT_CROP_CAMERAS_STATIC_MAX_POSES;
+constexpr int64_t kStaticScratchBytes =
+    (kStaticMaxPoses * (int64_t)sizeof(PoseHeader) + 255) / 256 * 256 + (int64_t)kStaticMaxPoses * kMaxViews * (int64_t)sizeof(CropSlot);
+
+static __device__ __align__(256) unsigned char g_crop_cameras_scratch[kStaticScratchBytes];
+
+// In host code `g_crop_cameras_scratch` is only a stand-in for the symbol, not a device address: the address
+// is looked up once per device, with that device current, and cached.
+constexpr int kMaxDevices = 64;
+std::mutex g_scratch_mu;
+void* g_scratch_ptr[kMaxDevices] = {};
+
+int static_scratch_address(void** ptr) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    abt::set_error("at_gen_crop_cameras_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+    return AT_ERR_CUDA;
+  }
+  std::lock_guard<std::mutex> lock(g_scratch_mu);
+  if (g_scratch_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_crop_cameras_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      abt::set_error("at_gen_crop_cameras_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return AT_ERR_CUDA;
+    }
+    g_scratch_ptr[dev] = p;
+  }
+  *ptr = g_scratch_ptr[dev];
+  return AT_OK;
+}
+
+}  // namespace
+
+extern "C" int at_gen_crop_cameras_static(const AtCropCameraInputs* in, const AtHandModel* hand_model,
+                                          const AtCropCameraOpts* opts, const AtCropCameraOutputs* out, void* stream) {
+  AT_REQUIRE(in && hand_model && opts && out, "at_gen_crop_cameras_static: NULL argument struct");
+  AT_REQUIRE(opts->max_view_num >= 1 && opts->max_view_num <= kMaxViews, "at_gen_crop_cameras_static: max_view_num must be 1..4");
+  if (in->n_poses > kStaticMaxPoses) {
+    abt::set_error("at_gen_crop_cameras_static: %d poses exceed the static scratch of AT_CROP_CAMERAS_STATIC_MAX_POSES = %d "
+                   "(use at_gen_crop_cameras with a caller-provided workspace)", in->n_poses, kStaticMaxPoses);
+    return AT_ERR_WORKSPACE_TOO_SMALL;
+  }
+  void* scratch = nullptr;
+  const int rc = static_scratch_address(&scratch);
+  if (rc) return rc;
+  // Nothing in the scratch has to start at zero: pass 1 writes the header of every pose and the slots of
+  // every selected view before pass 2 / 3 read them, so the previous call's contents are never observed.
+  return at_gen_crop_cameras(in, hand_model, opts, out, scratch, kStaticScratchBytes, stream);
 }

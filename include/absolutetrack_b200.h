@@ -259,6 +259,22 @@ int at_gen_crop_cameras(const AtCropCameraInputs* in, const AtHandModel* hand_mo
                         const AtCropCameraOpts* opts, const AtCropCameraOutputs* out, void* workspace,
                         int64_t workspace_bytes, void* stream);
 
+/* at_gen_crop_cameras without a workspace argument and without any allocation.  NO COUNTERPART IN THE
+ * REFERENCE: added for callers that cannot allocate device memory (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The scratch between the
+ * three launches lives in a file-scope `static __device__` array of the library, sized for
+ * AT_CROP_CAMERAS_STATIC_MAX_POSES poses x 4 views (about 4 MB; every GPU that loads the library holds it until the
+ * process exits).  in->n_poses beyond that limit returns AT_ERR_WORKSPACE_TOO_SMALL with a message naming the
+ * limit.  The call itself runs no cudaMalloc / cudaFree / allocating library routine; the first call on each
+ * device looks the array's device address up (cudaGetSymbolAddress) - make one call per device before capturing
+ * a graph.  Inputs, outputs and results are exactly at_gen_crop_cameras's.  All calls on a device SHARE the
+ * array: it keeps the previous call's contents (nothing in it has to start at zero - every header and slot is
+ * written before it is read), and two calls that overlap on the GPU (different streams, or graphs launched
+ * concurrently) race on it - serialise them or give the others their own workspace through at_gen_crop_cameras. */
+#define AT_CROP_CAMERAS_STATIC_MAX_POSES 2048
+int at_gen_crop_cameras_static(const AtCropCameraInputs* in, const AtHandModel* hand_model /* shared, mm */,
+                               const AtCropCameraOpts* opts, const AtCropCameraOutputs* out, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * (2)+(3) Network.  Replaces UmeTrackModel.regress_pose_use_skeleton / regress_pose_pred_skel_scale
  * (lib/models/umetrack_model.py:188-242) and everything below them: backbone

@@ -637,7 +637,8 @@ void build_tc_table() {
     if (i == L_STEM) {  // stem GEMM: 8 blocks (4 pooling phases x 2 rows) of [2 pixels][32][8]
       g_tc[i].n_pad = 32; g_tc[i].kc = 16; g_tc[i].nk = 1;
       g_tc[i].offset = off;
-      off += 8 * 1024;
+      off += 8 * 1024;          // GEMM stem blocks (tcgen05 variant)
+      off += 16 * 32 * 8;       // mma.sync B fragments (stem_mma_kernel)
       continue;
     }
     g_tc[i].n_pad = (int)round_up(T[i].cout, 16);
@@ -800,6 +801,8 @@ __global__ void __launch_bounds__(256) stem_tc_kernel(const TIn* __restrict__ cr
     out[(long long)cg * L.plane_px + g] = pk;
   }
 }
+
+#include "stem_mma.cuh"
 
 // ------------------------------------------------------------------------------------------
 // layout converters (debug entry point + tests)
@@ -1197,9 +1200,26 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
     Level phl[3];
     for (int l = 0; l < 3; ++l) phl[l] = make_level(P.lv[l + 1].H, P.lv[l + 1].W, P.lv[l].C, nc);
     auto buf = [&](int l, int i) { return ws + P.off_lv[l] + i * P.buf_units[l] + P.lv[l].guard; };
-    // stem: pack the crops into the 2x2-block plane S (first plane of the unused D buffer of
-    // level 0), then the stem GEMM writes X of level 0
-    {
+    // stem.  Default: mma.sync kernel straight from the crops (registers, no TMEM read-back, no pack kernel).
+    // AT_STEM_MMA=0: pack the crops into the 2x2-block plane S (first plane of the unused D buffer of level 0),
+    // then the tcgen05 stem GEMM writes X of level 0 (A/B).
+    static const bool stem_mma = getenv("AT_STEM_MMA") == nullptr || atoi(getenv("AT_STEM_MMA")) != 0;
+    if (stem_mma) {
+      const Level& L0 = P.lv[0];
+      const uint2* wf = reinterpret_cast<const uint2*>(reinterpret_cast<const uint8_t*>(tc_blob) + tc_table()[L_STEM].offset + 8 * 1024);
+      const float* bias = blob + layer_table()[L_STEM].bias_offset;
+      const int grid = (int)std::min<long long>(nc, 2 * kNumSMs);
+#define AT_STEM_LAUNCH(TIN, F)                                                                                        \
+  do {                                                                                                              \
+    AT_CARVEOUT_ONCE((stem_mma_kernel<TIN, F>));                                                                    \
+    stem_mma_kernel<TIN, F><<<grid, kStemThreads, 0, s>>>((const TIN*)crops + (size_t)c0 * 96 * 96, (int)nc, wf, bias, \
+                                                          buf(0, 0), L0, g_status);                                 \
+  } while (0)
+      if (crop_dtype == AT_U8) { if (fmt) AT_STEM_LAUNCH(uint8_t, 1); else AT_STEM_LAUNCH(uint8_t, 0); }
+      else { if (fmt) AT_STEM_LAUNCH(float, 1); else AT_STEM_LAUNCH(float, 0); }
+#undef AT_STEM_LAUNCH
+      if ((rc = check_launch("stem_mma_kernel"))) return rc;
+    } else {
       const Level& L0 = P.lv[0];
       const unsigned blocks = (unsigned)((L0.P + 255) / 256);
       if (crop_dtype == AT_U8) {
@@ -1427,6 +1447,13 @@ extern "C" int at_model_prepack_tc(const float* blob, void* tc_blob, int precisi
       precision == AT_PREC_BF16 ? 1 : 0);
   {
     int rc = check_launch("prepack_stem_kernel");
+    if (rc) return rc;
+  }
+  tc::prepack_stem_frag_kernel<<<2, 256, 0, (cudaStream_t)stream>>>(
+      blob + T[L_STEM].weight_offset, reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(tc_blob) + TT[L_STEM].offset + 8 * 1024),
+      precision == AT_PREC_BF16 ? 1 : 0);
+  {
+    int rc = check_launch("prepack_stem_frag_kernel");
     if (rc) return rc;
   }
   for (int i = L_LAYER1; i <= L_PROJ; ++i) {

@@ -92,6 +92,9 @@ struct ConvTcParams {
   long long* prof;  // optional [grid][16] cycle counters (debug)
   int dbg;          // debug knobs (AT_TC_DBG): 1 no epilogue, 2 no A copies
   int32_t* status;  // optional device status word: bit 1 (value 2) |= an fp16 activation of this layer saturated / is NaN
+  // cta_group::2 (conv_tc2_kernel): each CTA of a pair holds n / 2 output channels of every weight block
+  uint32_t w_src_bytes;   // bytes of a whole weight block in global memory (= block stride)
+  uint32_t w_kg_bytes;    // bytes of one 8-channel K group of a whole block in global memory (n * 16)
 };
 
 // Ring cursor without divisions: slot index + phase parity.
@@ -556,6 +559,8 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
   if (p.prof != nullptr && threadIdx.x == 0) p.prof[blockIdx.x * 16 + 6] = (long long)globaltimer_ns();
 }
 
+#include "conv_tc2.cuh"
+
 // ------------------------------------------------------------------------------------------
 // geometry
 struct Level {
@@ -898,6 +903,116 @@ long long* g_prof = nullptr;
 int g_prof_seq = -1;  // >= 0: launch k writes its counters at g_prof + k * 148 * 16
 thread_local int32_t* g_status = nullptr;  // status word of the encoder call in progress on this thread
 
+
+// conv_tc2_kernel (CTA pairs): ring / residency configuration and launch.  `p` arrives with the layer, tap, source
+// and shortcut fields filled by launch_conv_tc.
+constexpr int kSmemBudget2 = 226 * 1024;
+
+int launch_conv_tc2(ConvTcParams p, const char* name, const Level& OL, int out_mode, int mt, int max_shift, cudaStream_t stream) {
+  const int taps = 9;
+  const int nblocks = p.n_kchunks * taps + p.sc_nk;
+  p.w_src_bytes = (uint32_t)(p.kc * p.n * 2);
+  p.w_kg_bytes = (uint32_t)(p.n * 16);
+  p.w_block_bytes = p.w_src_bytes / 2;   // per CTA: half of the output channels
+  p.sc_w_bytes /= 2;
+  const int64_t misc = 3072;             // bias + barriers + alignment
+  auto a_slot = [&](int m) { return (int64_t)p.n_src * (p.kc / 8) * round_up(kTileM * m + max_shift - p.min_shift, 8) * 16; };
+  // weights resident when at least 2 activation slots still fit (smaller tiles first give up their second sub-tile)
+  int res_mt = 0;
+  for (int m = mt; m >= 1; m >>= 1)
+    if ((int64_t)nblocks * p.w_block_bytes + 2 * a_slot(m) + misc <= kSmemBudget2) { res_mt = m; break; }
+  int64_t ra;
+  if (res_mt > 0) {
+    mt = res_mt; p.w_resident = 1; p.ws = nblocks;
+    ra = (kSmemBudget2 - misc - (int64_t)nblocks * p.w_block_bytes) / a_slot(mt);
+  } else {
+    p.w_resident = 0; p.ws = 4;
+    for (;; mt >>= 1) {
+      ra = (kSmemBudget2 - misc - (int64_t)p.ws * p.w_block_bytes) / a_slot(mt);
+      if (ra >= 3 || mt == 1) break;
+    }
+    while (ra < 2 && p.ws > 2) { --p.ws; ra = (kSmemBudget2 - misc - (int64_t)p.ws * p.w_block_bytes) / a_slot(mt); }
+  }
+  if (ra < 2) {
+    set_error("conv_tc2: layer %s does not fit shared memory", name);
+    return AT_ERR_UNSUPPORTED;
+  }
+  if (ra > 8) ra = 8;
+  p.mt = mt; p.ra = (int)ra;
+  p.npix = (int)round_up(kTileM * mt + max_shift - p.min_shift, 8);
+  p.a_plane_bytes = (uint32_t)p.npix * 16u;
+  p.a_slot_bytes = (uint32_t)a_slot(mt);
+  p.sc_a_bytes = (uint32_t)p.sc_planes * p.a_plane_bytes;
+  const int64_t w_bytes = (int64_t)p.ws * p.w_block_bytes;
+  p.acc_cols = (uint32_t)round_up(mt * p.n, 32);
+  p.as = (int)(512 / p.acc_cols);
+  if (p.as > 4) p.as = 4;
+  uint32_t cols = 32;
+  while (cols < p.as * p.acc_cols) cols <<= 1;
+  p.tmem_cols = cols;
+  p.smem_a_off = 0;
+  p.smem_w_off = (uint32_t)round_up((int64_t)p.ra * p.a_slot_bytes, 128);
+  p.smem_bias_off = (uint32_t)round_up(p.smem_w_off + w_bytes, 128);
+  p.smem_bar_off = (uint32_t)round_up(p.smem_bias_off + p.n * 4, 128);
+  const uint32_t smem_bytes = p.smem_bar_off + 8 * (3 * p.ra + 3 * p.ws + 2 * p.as) + 16;
+  p.n_tiles = (OL.P + kTileM * mt - 1) / (kTileM * mt);
+  const long long n_pair_tiles = (p.n_tiles + 1) / 2;
+  const int grid = 2 * (int)std::min<long long>(n_pair_tiles, kNumSMs / 2);
+  if (grid == 0) return AT_OK;
+  p.div_hw = make_divider((uint32_t)(OL.Hp * OL.Wp));
+  p.div_wp = make_divider((uint32_t)OL.Wp);
+  const int ksteps = p.kc >> 4;
+  const int mode = out_mode == 1 ? 5 : 0;
+  using Kernel = void (*)(const ConvTcParams);
+  Kernel fn = nullptr;
+#define AT_TC2_CASE(K, M, R, O) \
+  if (ksteps == K && mt == M && p.w_resident == R && mode == O) fn = conv_tc2_kernel<K, M, R, O>;
+#define AT_TC2_CASES(K, M) AT_TC2_CASE(K, M, 0, 0) AT_TC2_CASE(K, M, 0, 5) AT_TC2_CASE(K, M, 1, 0) AT_TC2_CASE(K, M, 1, 5)
+  AT_TC2_CASES(2, 1) AT_TC2_CASES(2, 2) AT_TC2_CASES(4, 1) AT_TC2_CASES(4, 2)
+#undef AT_TC2_CASES
+#undef AT_TC2_CASE
+  if (fn == nullptr) {
+    set_error("conv_tc2: no kernel for kc=%d mt=%d resident=%d mode=%d", p.kc, mt, p.w_resident, mode);
+    return AT_ERR_UNSUPPORTED;
+  }
+  {
+    static std::mutex mu;
+    static std::vector<std::pair<int, Kernel>> configured;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const std::pair<int, Kernel> key(dev, fn);
+    std::lock_guard<std::mutex> lock(mu);
+    if (std::find(configured.begin(), configured.end(), key) == configured.end()) {
+      cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget2 + 1024);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+      if (e != cudaSuccess) {
+        set_error("cudaFuncSetAttribute(conv_tc2_kernel): %s", cudaGetErrorString(e));
+        return AT_ERR_CUDA;
+      }
+      configured.push_back(key);
+    }
+  }
+  static const bool use_pdl = getenv("AT_TC_PDL") == nullptr || atoi(getenv("AT_TC_PDL")) != 0;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem_bytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = use_pdl ? 1 : 0;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, fn, p);
+  if (e != cudaSuccess) {
+    count_launch();
+    set_error("conv_tc2_kernel launch (%s, smem %u): %s", name, smem_bytes, cudaGetErrorString(e));
+    return AT_ERR_CUDA;
+  }
+  return check_launch("conv_tc2_kernel");
+}
+
 // `out_level`: geometry of the OUTPUT (= geometry of the input for stride 1, = geometry of each
 // input phase image for stride 2).  `next`: geometry of the phase images written in mode 1.
 int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const Level& OL, const Level* next,
@@ -1003,6 +1118,13 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
     p.sc_src = io.sc_src; p.sc_plane_px = io.sc_plane_px;
     p.bias2 = blob + S.bias_offset;
     p.sc_w_bytes = (uint32_t)(kc_sc * p.n * 2);
+  }
+  {
+    // CTA pairs (cta_group::2) for the 3x3 convs with >= 64 output channels; AT_TC_CG2=0 keeps the single-CTA kernel (A/B)
+    static const bool use_cg2 = getenv("AT_TC_CG2") == nullptr || atoi(getenv("AT_TC_CG2")) != 0;
+    if (use_cg2 && desc == nullptr && !is_stem && taps == 9 && p.n >= 64 && p.n % 32 == 0 && io.res == nullptr &&
+        (io.out_mode == 0 || io.out_mode == 1) && p.cout == p.n)
+      return launch_conv_tc2(p, L.name, OL, io.out_mode, mt, max_shift, stream);
   }
   const int nblocks = p.n_kchunks * taps + p.sc_nk;
   const int64_t misc = 4096;

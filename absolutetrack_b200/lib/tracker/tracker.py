@@ -130,6 +130,21 @@ def crop_pull_source_boxes_cuda(
         raise _cabi.AbsoluteTrackError("pull source and destination must be contiguous and of one shape")
     if not (src.is_cuda or src.is_pinned()):
         raise _cabi.AbsoluteTrackError("the pull source must be pinned host memory (pageable memory is not GPU-readable)")
+    n_frames = src.numel() // frame_stride
+    max_frames = ((1 << 32) - 32) // frame_stride          # the kernel addresses a call's frames with 32-bit offsets
+    if n_frames > max_frames:                               # rare (> 4 GiB of frames per step): one call per frame range
+        frame_of = params.view(torch.int32)[:, 0]
+        flat_src, flat_dst = src.reshape(-1), dst.reshape(-1)
+        for f0 in range(0, n_frames, max_frames):
+            f1 = min(n_frames, f0 + max_frames)
+            sel = ((frame_of >= f0) & (frame_of < f1)).nonzero().squeeze(1)
+            if sel.numel() == 0:
+                continue
+            sub = params[sel].contiguous()
+            sub.view(torch.int32)[:, 0] -= f0
+            crop_pull_source_boxes_cuda(flat_src[f0 * frame_stride: f1 * frame_stride], flat_dst[f0 * frame_stride: f1 * frame_stride],
+                                        frame_stride, view_stride, row_stride, sub, dst_wh, max_ctas, pulled_bytes)
+        return
     with torch.cuda.device(dst.device):
         rc = lib.at_crop_pull_source_boxes_u8(
             src.data_ptr(), dst.data_ptr(), src.numel() // frame_stride, frame_stride, view_stride, row_stride,

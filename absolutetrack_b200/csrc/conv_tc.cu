@@ -918,15 +918,20 @@ int launch_conv_tc2(ConvTcParams p, const char* name, const Level& OL, int out_m
   const int64_t misc = 3072;             // bias + barriers + alignment
   auto a_slot = [&](int m) { return (int64_t)p.n_src * (p.kc / 8) * round_up(kTileM * m + max_shift - p.min_shift, 8) * 16; };
   // weights resident when at least 2 activation slots still fit (smaller tiles first give up their second sub-tile)
+  // experiment knobs: AT_TC2_RES=0 never keeps weights resident, AT_TC2_WS=<n> ring depth of streamed weights,
+  // AT_TC2_MINRA=<n> activation slots a resident configuration must leave (default 2)
+  static const int knob_res = getenv("AT_TC2_RES") ? atoi(getenv("AT_TC2_RES")) : 1;
+  static const int knob_ws = getenv("AT_TC2_WS") ? atoi(getenv("AT_TC2_WS")) : 4;
+  static const int knob_minra = getenv("AT_TC2_MINRA") ? atoi(getenv("AT_TC2_MINRA")) : 2;
   int res_mt = 0;
-  for (int m = mt; m >= 1; m >>= 1)
-    if ((int64_t)nblocks * p.w_block_bytes + 2 * a_slot(m) + misc <= kSmemBudget2) { res_mt = m; break; }
+  for (int m = mt; m >= 1 && knob_res; m >>= 1)
+    if ((int64_t)nblocks * p.w_block_bytes + knob_minra * a_slot(m) + misc <= kSmemBudget2) { res_mt = m; break; }
   int64_t ra;
   if (res_mt > 0) {
     mt = res_mt; p.w_resident = 1; p.ws = nblocks;
     ra = (kSmemBudget2 - misc - (int64_t)nblocks * p.w_block_bytes) / a_slot(mt);
   } else {
-    p.w_resident = 0; p.ws = 4;
+    p.w_resident = 0; p.ws = knob_ws;
     for (;; mt >>= 1) {
       ra = (kSmemBudget2 - misc - (int64_t)p.ws * p.w_block_bytes) / a_slot(mt);
       if (ra >= 3 || mt == 1) break;
@@ -1120,8 +1125,13 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
     p.sc_w_bytes = (uint32_t)(kc_sc * p.n * 2);
   }
   {
-    // CTA pairs (cta_group::2) for the 3x3 convs with >= 64 output channels; AT_TC_CG2=0 keeps the single-CTA kernel (A/B)
-    static const bool use_cg2 = getenv("AT_TC_CG2") == nullptr || atoi(getenv("AT_TC_CG2")) != 0;
+    // CTA pairs (cta_group::2) for the 3x3 convs with >= 64 output channels: opt-in through AT_TC_CG2=<mask> (A/B)
+    // bit mask by padded Cout: 1 -> 64 (layer 2), 2 -> 128 (layer 3), 4 -> 256 (layer 4)
+    // Default 0: measured on B200 (profiles/r2_cg2_experiments.log) the pair kernel is correct (all conv / encoder / parity
+    // tests pass with mask 7) but not faster than conv_tc_kernel in any ring configuration (2.49 vs 2.44 ms per 2048 crops
+    // at best, layer 3 with resident weights): the relay / multicast-commit turnaround costs more than the halved B reads save.
+    static const int cg2_mask = getenv("AT_TC_CG2") == nullptr ? 0 : atoi(getenv("AT_TC_CG2"));
+    const bool use_cg2 = (cg2_mask & (p.n == 64 ? 1 : p.n == 128 ? 2 : 4)) != 0;
     if (use_cg2 && desc == nullptr && !is_stem && taps == 9 && p.n >= 64 && p.n % 32 == 0 && io.res == nullptr &&
         (io.out_mode == 0 || io.out_mode == 1) && p.cout == p.n)
       return launch_conv_tc2(p, L.name, OL, io.out_mode, mt, max_shift, stream);

@@ -92,6 +92,10 @@ struct ConvTcParams {
   long long* prof;  // optional [grid][16] cycle counters (debug)
   int dbg;          // debug knobs (AT_TC_DBG): 1 no epilogue, 2 no A copies
   int32_t* status;  // optional device status word: bit 1 (value 2) |= an fp16 activation of this layer saturated / is NaN
+  // Work items of conv_tc_kernel: tiles [0, t_full) as a whole, then every remaining tile (the partial last wave of the
+  // persistent grid) as n_split = 2^split_shift items of n / n_split output channels each, so that the last wave costs
+  // 1 / n_split of a tile time instead of a whole one (layer 3: 9.13 -> 10 waves without it).  n_split = 1: plain tiles.
+  int t_full, n_split, split_shift, n_items;
   // cta_group::2 (conv_tc2_kernel): each CTA of a pair holds n / 2 output channels of every weight block
   uint32_t w_src_bytes;   // bytes of a whole weight block in global memory (= block stride)
   uint32_t w_kg_bytes;    // bytes of one 8-channel K group of a whole block in global memory (n * 16)
@@ -157,9 +161,17 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem + (tmem_slot - sbase));
 
-  const int first_tile = blockIdx.x;
-  const int n_tiles = (int)p.n_tiles;
+  const int first_tile = blockIdx.x;   // first work item of this CTA; items are strided by the grid size
+  const int n_tiles = p.n_items;
   const int n_my = first_tile < n_tiles ? (n_tiles - first_tile + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  // work item -> (tile, channel slice sp); sp < 0: the whole tile
+  auto item_tile = [&](int w, int& sp) -> int {
+    if (w < p.t_full) { sp = -1; return w; }
+    const int r = w - p.t_full;
+    sp = r & (p.n_split - 1);
+    return p.t_full + (r >> p.split_shift);
+  };
+  const int n_part = p.n >> p.split_shift;   // output channels of a slice
   const int nk = p.n_kchunks;
   // NTAPS == 8 is the stem GEMM: 8 MMAs (4 pooling phases x 2 rows), one 8-channel input plane,
   // the two K halves of an MMA are two neighbouring pixels (LBO = 16 B), 4 accumulators.
@@ -212,7 +224,12 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
     long long t_acc = 0, t_a = 0, t_w = 0, t_start = clock64(), t0;
     const bool prof = p.prof != nullptr && (p.dbg & 16);
     if (p.prof != nullptr && lane == 0) p.prof[blockIdx.x * 16 + 7] = (long long)globaltimer_ns();
+    const uint32_t idesc_full = idesc, idesc_part = umma_idesc(kTileM, n_part, p.fmt);
     for (int it = 0; it < n_my; ++it) {
+      int sp;
+      item_tile(first_tile + it * (int)gridDim.x, sp);
+      const uint32_t idesc = sp < 0 ? idesc_full : idesc_part;
+      const uint32_t b_sp = sp < 0 ? 0u : (uint32_t)(sp * n_part);   // rows of B skipped (16-byte units)
       if (prof) t0 = clock64();
       mbar_wait(acc_empty + 8 * rc.slot, rc.phase ^ 1u);
       if (prof) t_acc += clock64() - t0;
@@ -231,7 +248,7 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
             tc_fence_after();
           }
           if (elect_one()) {
-            const uint32_t b_lo = b_lo0 + kci * NTAPS * w_blk16;
+            const uint32_t b_lo = b_lo0 + kci * NTAPS * w_blk16 + b_sp;
 #pragma unroll
             for (int t = 0; t < NTAPS; ++t) {
 #pragma unroll
@@ -258,7 +275,7 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
             if (prof) t_w += clock64() - t0;
             tc_fence_after();
             if (elect_one()) {
-              const uint32_t b_lo = b_lo0 + rw.slot * w_blk16;
+              const uint32_t b_lo = b_lo0 + rw.slot * w_blk16 + b_sp;
 #pragma unroll
               for (int j = 0; j < KSTEPS; ++j) {
                 const uint64_t bd = ((uint64_t)desc_hi << 32) | (b_lo + j * b_kstep16);
@@ -288,11 +305,11 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
             mbar_wait(w_full + 8 * (nk * NTAPS + sc), 0);
             tc_fence_after();
           }
-          b_lo = b_lo0 + (nk * NTAPS + sc) * w_blk16;
+          b_lo = b_lo0 + (nk * NTAPS + sc) * w_blk16 + b_sp;
         } else {
           mbar_wait(w_full + 8 * rw.slot, rw.phase);
           tc_fence_after();
-          b_lo = b_lo0 + rw.slot * w_blk16;
+          b_lo = b_lo0 + rw.slot * w_blk16 + b_sp;
         }
         if (elect_one()) {
           for (int j = 0; j < p.sc_ksteps; ++j) {
@@ -323,7 +340,8 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
       Ring ra;
       pdl_wait();  // the previous layer's output must be complete before the first load
       for (int it = 0; it < n_my; ++it) {
-        const long long g0 = (long long)(first_tile + it * (int)gridDim.x) * kTilePx + p.min_shift;
+        int sp_unused;
+        const long long g0 = (long long)item_tile(first_tile + it * (int)gridDim.x, sp_unused) * kTilePx + p.min_shift;
         for (int kci = 0; kci < nk; ++kci) {
           if (p.dbg & 8) mbar_wait_sleep(a_empty + 8 * ra.slot, ra.phase ^ 1u, 100);
           else mbar_wait(a_empty + 8 * ra.slot, ra.phase ^ 1u);
@@ -358,8 +376,8 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
     const int ncg = (p.cout + 7) >> 3;
     constexpr bool has_res = MODE == 1 || MODE == 2;
     constexpr int out_mode = (MODE == 2 || MODE == 5) ? 1 : (MODE == 3 ? 2 : (MODE == 4 ? 3 : 0));
-    const int n_slabs = (p.n + 31) >> 5;  // 32-column slabs (the last one may hold 16)
-    const int S = MT * n_slabs;           // slabs of one tile in flat order f = m * n_slabs + sl
+    const int n_slabs_full = (p.n + 31) >> 5;  // 32-column slabs (the last one may hold 16)
+    // slabs of one work item in flat order f = m * n_slabs + sl (per item: see below)
     // Residual ring: 4 slots of one slab (4 channel groups x 16 B per lane).  Slot f & 3 holds flat
     // slab f; after slab f is consumed the slot is refilled with slab f + 4 of the same tile or,
     // past the end, with the matching slab of this group's NEXT tile, so every global load is
@@ -380,10 +398,16 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
       const uint32_t gb = (uint32_t)(first_tile + grp * (int)gridDim.x) * kTilePx + qd * 32 + lane;
 #pragma unroll
       for (int k = 0; k < 4; ++k)
-        if (k < S) res_load(rr[k], gb, k);
+        if (k < MT * n_slabs_full) res_load(rr[k], gb, k);   // (residual layers are never channel-sliced)
     }
     for (int it = grp; it < n_my; it += 2) {
-      const int tile = first_tile + it * (int)gridDim.x;
+      int sp;
+      const int tile = item_tile(first_tile + it * (int)gridDim.x, sp);
+      // a channel slice: n_part channels starting at c_off, accumulated in TMEM columns [0, n_part) of each sub-tile
+      const int c_off = sp < 0 ? 0 : sp * n_part;
+      const int n_slabs = sp < 0 ? n_slabs_full : n_slabs_full >> p.split_shift;
+      const int slab_shift = sp < 0 ? p.slab_shift : p.slab_shift - p.split_shift;
+      const int S = MT * n_slabs;
       const uint32_t gbase = (uint32_t)tile * kTilePx + qd * 32 + lane;
       const bool has_next = it + 2 < n_my;
       const uint32_t gbase_next = gbase + 2u * gridDim.x * kTilePx;
@@ -402,8 +426,8 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
           for (int k = 0; k < 4; ++k) {
             const int f = f0 + k;
             if (f >= S) break;
-            const int m = MT == 1 ? 0 : (MODE == 4 ? (f >= n_slabs ? 1 : 0) : f >> p.slab_shift);
-            const int sl = MT == 1 ? f : (MODE == 4 ? f - m * n_slabs : f - (m << p.slab_shift));
+            const int m = MT == 1 ? 0 : (MODE == 4 ? (f >= n_slabs ? 1 : 0) : f >> slab_shift);
+            const int sl = MT == 1 ? f : (MODE == 4 ? f - m * n_slabs : f - (m << slab_shift));
             if (sl == 0) {  // new sub-tile: decode the pixel of this lane
               g = gbase + m * kTileM;
               const uint32_t img = fast_div(g, p.div_hw);
@@ -421,7 +445,7 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
               }
             }
             const int c0 = sl << 5;
-            const bool wide = c0 + 32 <= p.n;
+            const bool wide = c_off + c0 + 32 <= p.n;
             uint32_t v[32];
             if (wide) tmem_ld_x32(taddr + c0, v);
             else tmem_ld_x16(taddr + c0, *reinterpret_cast<uint32_t(*)[16]>(v));
@@ -440,7 +464,7 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
             uint4 pk[4];
 #pragma unroll
             for (int h = 0; h < 4; ++h) {
-              const int cg = (c0 >> 3) + h;
+              const int cg = ((c_off + c0) >> 3) + h;
               float o[8];
               const float4 b0 = *reinterpret_cast<const float4*>(bias_s + (cg < ncg ? cg : 0) * 8);
               const float4 b1 = *reinterpret_cast<const float4*>(bias_s + (cg < ncg ? cg : 0) * 8 + 4);
@@ -526,7 +550,7 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
             if (out_mode != 2 && out_mode != 3) {
 #pragma unroll
               for (int h = 0; h < 4; ++h) {
-                const int cg = (c0 >> 3) + h;
+                const int cg = ((c_off + c0) >> 3) + h;
                 if (cg < ncg && (wide || h < 2)) {
                   if (out_mode == 0)
                     p.out[(long long)cg * p.out_plane_px + g] = pk[h];
@@ -1177,7 +1201,19 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   p.smem_bar_off = (uint32_t)round_up(p.smem_bias_off + p.n * 4, 128);
   const uint32_t smem_bytes = p.smem_bar_off + 8 * (2 * p.ra + 2 * p.ws + 2 * p.as) + 16;
   p.n_tiles = (OL.P + kTileM * mt - 1) / (kTileM * mt);
-  const int grid = (int)std::min<long long>(p.n_tiles, kNumSMs);
+  // the partial last wave of the persistent grid, sliced by output channels (AT_TC_NSPLIT=0 switches it off for A/B)
+  p.t_full = (int)p.n_tiles; p.n_split = 1; p.split_shift = 0;
+  {
+    static const bool nsplit = getenv("AT_TC_NSPLIT") == nullptr || atoi(getenv("AT_TC_NSPLIT")) != 0;
+    const int rest = (int)(p.n_tiles % kNumSMs);
+    if (nsplit && rest > 0 && !is_stem && io.res == nullptr && io.out_mode != 3 && io.out_mode != 2 && p.cout == p.n && p.n % 64 == 0) {
+      int sh = 0;
+      while ((p.n >> (sh + 1)) % 32 == 0 && (rest << (sh + 1)) <= kNumSMs) ++sh;   // slices of >= 32 channels, one wave
+      if (sh > 0) { p.t_full = (int)p.n_tiles - rest; p.split_shift = sh; p.n_split = 1 << sh; }
+    }
+  }
+  p.n_items = p.t_full + ((int)p.n_tiles - p.t_full) * p.n_split;
+  const int grid = (int)std::min<long long>(p.n_items, kNumSMs);
   if (grid == 0) return AT_OK;
   const int ksteps = p.kc >> 4;
   p.div_hw = make_divider((uint32_t)(OL.Hp * OL.Wp));

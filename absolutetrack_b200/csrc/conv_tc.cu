@@ -927,6 +927,31 @@ long long* g_prof = nullptr;
 int g_prof_seq = -1;  // >= 0: launch k writes its counters at g_prof + k * 148 * 16
 thread_local int32_t* g_status = nullptr;  // status word of the encoder call in progress on this thread
 
+// "The encoder is under way" event: recorded on the encoder's stream right after layer1.0.conv1 has been launched, and
+// `release_stream` is made to wait for it.  Side-stream work released at that point (the source-box pull of the NEXT step)
+// meets an SM array that is full of conv CTAs and spreads over their leftover registers, instead of piling up on
+// the SMs that happen to be free at a kernel boundary and pushing a CTA of the 148-CTA persistent conv grids into a second wave.
+int release_after_launch(cudaStream_t s, cudaStream_t release_stream) {
+  static std::mutex mu;
+  static cudaEvent_t ev[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  cudaEvent_t e;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (ev[dev & 63] == nullptr && cudaEventCreateWithFlags(&ev[dev & 63], cudaEventDisableTiming) != cudaSuccess) {
+      set_error("at_encoder_forward: cudaEventCreate: %s", cudaGetErrorString(cudaGetLastError()));
+      return AT_ERR_CUDA;
+    }
+    e = ev[dev & 63];
+  }
+  if (cudaEventRecord(e, s) != cudaSuccess || cudaStreamWaitEvent(release_stream, e, 0) != cudaSuccess) {
+    set_error("at_encoder_forward: release event: %s", cudaGetErrorString(cudaGetLastError()));
+    return AT_ERR_CUDA;
+  }
+  return AT_OK;
+}
+
 
 // conv_tc2_kernel (CTA pairs): ring / residency configuration and launch.  `p` arrives with the layer, tap, source
 // and shortcut fields filled by launch_conv_tc.
@@ -1348,7 +1373,8 @@ int encoder_prepare_workspace(void* workspace, long long nc, cudaStream_t s) {
 // prepared_c > 0: the caller guarantees that the workspace was prepared for prepared_c crops per
 // chunk (encoder_prepare_workspace) and only written by this function since.
 int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* crops, int crop_dtype, int c, float* features,
-                         void* workspace, int64_t workspace_bytes, int fmt, int prepared_c, int32_t* status, cudaStream_t s) {
+                         void* workspace, int64_t workspace_bytes, int fmt, int prepared_c, int32_t* status,
+                         cudaStream_t release_stream, cudaStream_t s) {
   using namespace tc;
   struct StatusScope {  // every conv launch of this call reports fp16 saturation into `status`
     explicit StatusScope(int32_t* p) { g_status = p; }
@@ -1440,6 +1466,9 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
           io.a_base = buf(l, cur); io.a_plane_px = LV.plane_px;
           io.out = Tm; io.out_plane_px = LV.plane_px; io.out_mode = 0; io.relu = true;
           if ((rc = launch_conv_tc(id, blob, tc_blob, LV, nullptr, io, fmt, s))) return rc;
+          if (release_stream != nullptr && l == 0 && b == 0 && c0 + kChunkCrops >= c &&   // last chunk: layer1.0.conv1 is launched
+              (rc = release_after_launch(s, release_stream)))
+            return rc;
           resid = buf(l, cur);
         }
         memset(&io, 0, sizeof(io));

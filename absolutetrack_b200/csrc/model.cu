@@ -160,7 +160,7 @@ namespace abt {
 // tcgen05 path (conv_tc.cu)
 int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* crops, int crop_dtype, int c,
                          float* features, void* workspace, int64_t workspace_bytes, int fmt, int prepared_c,
-                         int32_t* status, cudaStream_t s);
+                         int32_t* status, cudaStream_t release_stream, cudaStream_t s);
 int64_t encoder_workspace_bytes_bf16(int c);
 int encoder_chunk_crops();
 }  // namespace abt
@@ -184,6 +184,14 @@ extern "C" int at_encoder_forward_prepared(const float* blob, const void* bf16_b
 extern "C" int at_encoder_forward_status(const float* blob, const void* bf16_blob, const void* crops, int crop_dtype,
                                          int c, float* features, void* workspace, int64_t workspace_bytes,
                                          int precision, int prepared_chunk, int32_t* status, void* stream) {
+  return at_encoder_forward_release(blob, bf16_blob, crops, crop_dtype, c, features, workspace, workspace_bytes, precision,
+                                    prepared_chunk, status, nullptr, stream);
+}
+
+extern "C" int at_encoder_forward_release(const float* blob, const void* bf16_blob, const void* crops, int crop_dtype,
+                                          int c, float* features, void* workspace, int64_t workspace_bytes,
+                                          int precision, int prepared_chunk, int32_t* status, void* release_stream,
+                                          void* stream) {
   AT_REQUIRE(c >= 0, "at_encoder_forward: c < 0");
   if (c == 0) return AT_OK;
   AT_REQUIRE(blob && crops && features && workspace, "at_encoder_forward: NULL pointer");
@@ -194,12 +202,23 @@ extern "C" int at_encoder_forward_status(const float* blob, const void* bf16_blo
                   (long long)at_encoder_workspace_bytes(c, precision));
     return AT_ERR_WORKSPACE_TOO_SMALL;
   }
-  if (precision == AT_PREC_FP32)
-    return abt::encoder_forward_f32(blob, crops, crop_dtype, c, features, workspace, (cudaStream_t)stream);
+  if (precision == AT_PREC_FP32) {
+    const int rc = abt::encoder_forward_f32(blob, crops, crop_dtype, c, features, workspace, (cudaStream_t)stream);
+    if (rc == AT_OK && release_stream != nullptr) {  // no mid-encoder point on this path: release behind the whole encoder
+      cudaEvent_t e;
+      if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess || cudaEventRecord(e, (cudaStream_t)stream) != cudaSuccess ||
+          cudaStreamWaitEvent((cudaStream_t)release_stream, e, 0) != cudaSuccess || cudaEventDestroy(e) != cudaSuccess) {
+        abt::set_error("at_encoder_forward_release: %s", cudaGetErrorString(cudaGetLastError()));
+        return AT_ERR_CUDA;
+      }
+    }
+    return rc;
+  }
   if (precision == AT_PREC_BF16 || precision == AT_PREC_FP16) {
     AT_REQUIRE(bf16_blob != nullptr, "at_encoder_forward: the prepacked 16-bit blob is required for AT_PREC_BF16/FP16");
     return abt::encoder_forward_bf16(blob, bf16_blob, crops, crop_dtype, c, features, workspace, workspace_bytes,
-                                    precision == AT_PREC_BF16 ? 1 : 0, prepared_chunk, status, (cudaStream_t)stream);
+                                    precision == AT_PREC_BF16 ? 1 : 0, prepared_chunk, status, (cudaStream_t)release_stream,
+                                    (cudaStream_t)stream);
   }
   abt::set_error("at_encoder_forward: bad precision %d", precision);
   return AT_ERR_INVALID_ARGUMENT;

@@ -135,7 +135,16 @@ class BatchedHandTracker:
         self.pull_ctas = 0  # CTAs of the pull kernel (0 = one per SM)
         self.trace = None   # debug: a list -> step() appends (ingest start, ingest end, compute start, compute end) events
         # high priority: the ingest kernels are tiny and must not queue behind the encoder's CTAs
+        # The ingest stream is released from INSIDE the encoder (at_encoder_forward_release: the copy stream waits until
+        # layer1.0.conv1 of the current step has been launched and finished).  Released at a kernel boundary (behind the
+        # resampler, as in round 1) the pull kernel's one-warp CTAs are placed on whichever SMs are free at that moment
+        # and pile up there; a conv grid of 148 persistent CTAs that loses one SM to them runs a second wave (measured
+        # on B200: compute at half speed while the pull was in flight, e2e 234k -> 305k hand-frames/s on the same box,
+        # profiles/r2_e2e_ingest_release_ab.log).  AT_INGEST_RELEASE=crops restores the old release point (A/B).
         self._copy_stream = torch.cuda.Stream(device=self._device, priority=int(os.environ.get("AT_INGEST_PRIORITY", "-1")))
+        self._release_in_encoder = os.environ.get("AT_INGEST_RELEASE", "encoder") == "encoder"
+        if self._release_in_encoder:
+            self._model.release_stream = self._copy_stream
         self._stage = [None, None]
         self._stage_free = [None, None]
         self._slot = 0
@@ -154,8 +163,9 @@ class BatchedHandTracker:
         )
         # the next step's ingest kernel is released after this point: the resampler runs with its own
         # (L1-heavy) shared-memory configuration and must not meet resident ingest CTAs
-        self._crops_done = torch.cuda.Event()
-        self._crops_done.record()
+        if not self._release_in_encoder:
+            self._crops_done = torch.cuda.Event()
+            self._crops_done.record()
         out = self._model.regress_pose_use_skeleton(
             InputFrameData(crops, b.intrinsics, b.extrinsics),
             InputFrameDesc(b.sample_range, b.memory_idx, b.use_memory, b.hand_idx),

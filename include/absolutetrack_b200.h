@@ -338,6 +338,17 @@ int at_encoder_forward_status(const float* blob, const void* bf16_blob, const vo
                               int c, float* features, void* workspace, int64_t workspace_bytes,
                               int precision, int prepared_chunk, int32_t* status, void* stream);
 
+/* Same call, plus a release point for side-stream work: when release_stream is not NULL it is made to wait
+ * (cudaStreamWaitEvent, asynchronous) until the encoder of this call is under way - the 16-bit path records the event on
+ * `stream` right after layer1.0.conv1 of the last chunk has been launched, the fp32 path behind the whole encoder.
+ * BatchedHandTracker releases the NEXT step's source-box pull (at_crop_pull_source_boxes_u8 on its ingest stream) there:
+ * its one-warp CTAs then meet an SM array full of conv CTAs and spread over the registers those leave free, instead of
+ * piling up on whichever SMs are idle at a kernel boundary and pushing one CTA of the 148-CTA persistent conv grids into
+ * a second wave (measured: compute at half speed while the pull was in flight). */
+int at_encoder_forward_release(const float* blob, const void* bf16_blob, const void* crops, int crop_dtype,
+                               int c, float* features, void* workspace, int64_t workspace_bytes,
+                               int precision, int prepared_chunk, int32_t* status, void* release_stream, void* stream);
+
 /* Test/debug entry: ONE backbone conv layer (layer_id from at_model_layer_table, 1..28) through the
  * tcgen05 path on float32 NHWC tensors: in [n,H,W,cin] -> out [n,H/stride,W/stride,cout], optional
  * residual res [n,H/stride,W/stride,cout], optional ReLU.  mt = 128-pixel sub-tiles per CTA tile (0 = default). */

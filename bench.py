@@ -33,9 +33,10 @@ ENCODER_FLOP_PER_CROP = 969_228_288           # SURVEY.md 8(d), counted on the r
 TAIL_FLOP_PER_HAND = 19_150_000
 FK_BYTES_PER_HAND = 404                        # shared hand model
 CROP_SRC_BYTES = 32_160                        # mean source bounding box per crop
-# dram__bytes_read.sum + dram__bytes_write.sum over the 26 conv launches of ONE encoder pass, per crop: 7,939 MB for 2048
-# crops in the ncu --set full capture profiles/r1_conv_tc_ncu_full_summary.csv (= the activations read + written once)
-ENCODER_DRAM_BYTES_PER_CROP = 7_938_569_984 / 2048
+# dram__bytes_read.sum + dram__bytes_write.sum over the 25 conv_tc launches of ONE encoder pass for 2048 crops in the ncu --set full
+# capture profiles/r2_conv_tc_ncu_full_summary.csv (7614 MB = the activations read + written once) + the stem kernel's
+# algorithmic bytes (crops read, level-0 planes written: 334 MB; it was not part of that capture)
+ENCODER_DRAM_BYTES_PER_CROP = (7614045184 + 333578240) / 2048
 
 
 def load_peaks():
@@ -488,7 +489,7 @@ def main():
                          "achieved": enc_tflops, "peak": tf_peak, "unit": "TFLOP/s", "frac": enc_tflops / tf_peak,
                          "traffic": ENCODER_DRAM_BYTES_PER_CROP * c,
                          "traffic_source": "bytes per encoder pass (all conv launches), scaled per crop from the ncu --set full "
-                                           "capture in profiles/r1_conv_tc_ncu_full_summary.csv",
+                                           "capture in profiles/r2_conv_tc_ncu_full_summary.csv (+ the stem kernel's algorithmic bytes)",
                          "peak_source": peaks["src"] + " cuBLAS bf16 burst (MEASURED_PEAKS.json bf16_tflops)",
                          "frac_of_sustained_peak": enc_tflops / peaks["tf_sust"],
                          "launches_per_step": enc_launches // max(1, args.steps)},

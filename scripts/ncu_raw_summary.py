@@ -21,7 +21,7 @@ with open(sys.argv[2], "w", newline="") as f:
         for src, name in cols:
             v = r[idx[src]] if src in idx else ""
             if name == "kernel":
-                v = v.split("(")[0].replace("void at::tc::", "").replace("void at::", "").replace("void ", "")
+                v = v.split("(")[0].replace("void abt::tc::", "").replace("abt::", "").replace("<unnamed>::", "").replace("void at::", "").replace("void ", "")
             out.append(v)
         w.writerow(out)
 print("wrote", sys.argv[2])

@@ -55,12 +55,13 @@ def main():
     host_frames = [f.cpu().pin_memory() for f in dev_frames] if args.e2e else None
     # per (group, geometry phase): the small tensors of a step (crop records, camera matrices, ranges, memory slots) + GT landmarks
     small, gts = [], []
+    placeholder = torch.zeros(1, dtype=torch.uint8)
     for gi, seqs in enumerate(groups):
         row, grow = [], []
         for t in range(min(K, args.frames)):
-            hb = synthetic.make_batch(seqs, t)
+            hb = synthetic.make_batch(seqs, t, frames=placeholder)   # (without `frames` make_batch allocates a 625 MB dummy)
+            ja, wx = synthetic.gt_poses(seqs, t, hb)
             hb.memory_idx = hb.memory_idx + 2 * S * gi
-            ja, wx = synthetic.gt_poses(seqs, t, synthetic.make_batch(seqs, t))
             grow.append(skin_landmarks_cuda(tracker._hm_dev, ja.to(dev), wx.to(dev)))
             row.append(hb)
         small.append(row)

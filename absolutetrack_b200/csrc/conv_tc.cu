@@ -1393,20 +1393,30 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
     }
     Level phl[3];
     for (int l = 0; l < 3; ++l) phl[l] = make_level(P.lv[l + 1].H, P.lv[l + 1].W, P.lv[l].C, nc);
-    auto buf = [&](int l, int i) { return ws + P.off_lv[l] + i * P.buf_units[l] + P.lv[l].guard; };
+    // One span of the pass: the stem (l_begin == 0), levels [l_begin, l_end) and the projection (l_end == 4) over
+    // crops [cs, cs + n) of the chunk.  A span over part of the chunk addresses the same planes at a crop offset
+    // (the planes keep the chunk's stride, tiles are counted from the span's first pixel).
+    auto run_span = [&](int l_begin, int l_end, long long cs, long long n, bool release) -> int {
+    auto part = [&](const Level& L) { Level R = L; R.n_img = n; R.P = n * L.Hp * L.Wp; return R; };
+    auto buf = [&](int l, int i) { return ws + P.off_lv[l] + i * P.buf_units[l] + P.lv[l].guard + cs * P.lv[l].Hp * P.lv[l].Wp; };
+    auto ps_buf = [&](int l) { return ws + P.off_ps[l] + phl[l].guard + cs * phl[l].Hp * phl[l].Wp; };
+    Level phs[3];
+    for (int l = 0; l < 3; ++l) phs[l] = part(phl[l]);
+    const long long cg0 = c0 + cs;  // first crop of the span in the caller's arrays
     // stem.  Default: mma.sync kernel straight from the crops (registers, no TMEM read-back, no pack kernel).
     // AT_STEM_MMA=0: pack the crops into the 2x2-block plane S (first plane of the unused D buffer of level 0),
     // then the tcgen05 stem GEMM writes X of level 0 (A/B).
     static const bool stem_mma = getenv("AT_STEM_MMA") == nullptr || atoi(getenv("AT_STEM_MMA")) != 0;
-    if (stem_mma) {
-      const Level& L0 = P.lv[0];
+    if (l_begin > 0) {
+    } else if (stem_mma) {
+      const Level L0 = part(P.lv[0]);
       const uint2* wf = reinterpret_cast<const uint2*>(reinterpret_cast<const uint8_t*>(tc_blob) + tc_table()[L_STEM].offset + 8 * 1024);
       const float* bias = blob + layer_table()[L_STEM].bias_offset;
-      const int grid = (int)std::min<long long>(nc, 2 * kNumSMs);
+      const int grid = (int)std::min<long long>(n, 2 * kNumSMs);
 #define AT_STEM_LAUNCH(TIN, F)                                                                                        \
   do {                                                                                                              \
     AT_CARVEOUT_ONCE((stem_mma_kernel<TIN, F>));                                                                    \
-    stem_mma_kernel<TIN, F><<<grid, kStemThreads, 0, s>>>((const TIN*)crops + (size_t)c0 * 96 * 96, (int)nc, wf, bias, \
+    stem_mma_kernel<TIN, F><<<grid, kStemThreads, 0, s>>>((const TIN*)crops + (size_t)cg0 * 96 * 96, (int)n, wf, bias, \
                                                           buf(0, 0), L0, g_status);                                 \
   } while (0)
       if (crop_dtype == AT_U8) { if (fmt) AT_STEM_LAUNCH(uint8_t, 1); else AT_STEM_LAUNCH(uint8_t, 0); }
@@ -1414,14 +1424,14 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
 #undef AT_STEM_LAUNCH
       if ((rc = check_launch("stem_mma_kernel"))) return rc;
     } else {
-      const Level& L0 = P.lv[0];
+      const Level L0 = part(P.lv[0]);
       const unsigned blocks = (unsigned)((L0.P + 255) / 256);
       if (crop_dtype == AT_U8) {
         AT_CARVEOUT_ONCE(stem_pack_kernel<uint8_t>);
-        stem_pack_kernel<uint8_t><<<blocks, 256, 0, s>>>((const uint8_t*)crops + (size_t)c0 * 96 * 96, buf(0, 3), L0, fmt);
+        stem_pack_kernel<uint8_t><<<blocks, 256, 0, s>>>((const uint8_t*)crops + (size_t)cg0 * 96 * 96, buf(0, 3), L0, fmt);
       } else {
         AT_CARVEOUT_ONCE(stem_pack_kernel<float>);
-        stem_pack_kernel<float><<<blocks, 256, 0, s>>>((const float*)crops + (size_t)c0 * 96 * 96, buf(0, 3), L0, fmt);
+        stem_pack_kernel<float><<<blocks, 256, 0, s>>>((const float*)crops + (size_t)cg0 * 96 * 96, buf(0, 3), L0, fmt);
       }
       if ((rc = check_launch("stem_pack_kernel"))) return rc;
       ConvIo io;
@@ -1438,9 +1448,10 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
     // added in the epilogue (level bit mask; measured per level on B200: -0.04 / -0.02 / -0.05 / -0.005 ms)
     static const int fold_id = getenv("AT_TC_FOLD_ID") != nullptr ? atoi(getenv("AT_TC_FOLD_ID")) : 15;
     int id = L_LAYER1;
+    for (int l = 0; l < l_begin; ++l) id += 2 * nblocks[l] + (l > 0 ? 1 : 0);
     int cur = 0;  // index (0 = X, 2 = Y) of the buffer holding the current activation of the level
-    for (int l = 0; l < 4; ++l) {
-      const Level& LV = P.lv[l];
+    for (int l = l_begin; l < l_end; ++l) {
+      const Level LV = part(P.lv[l]);
       for (int b = 0; b < nblocks[l]; ++b) {
         const bool first = l > 0 && b == 0;
         const bool last = b == nblocks[l] - 1 && l < 3;
@@ -1450,7 +1461,7 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
         const uint4* resid;
         if (first) {
           // conv1 (3x3 stride 2) and the 1x1 stride-2 shortcut both read the phase-split output of level l-1
-          const uint4* src = ws + P.off_ps[l - 1] + phl[l - 1].guard;
+          const uint4* src = ps_buf(l - 1);
           io.a_base = src; io.a_plane_px = phl[l - 1].plane_px; io.a_phase_units = P.ps_units[l - 1];
           io.out = Tm; io.out_plane_px = LV.plane_px; io.out_mode = 0; io.relu = true;
           if ((rc = launch_conv_tc(id, blob, tc_blob, LV, nullptr, io, fmt, s))) return rc;
@@ -1466,7 +1477,7 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
           io.a_base = buf(l, cur); io.a_plane_px = LV.plane_px;
           io.out = Tm; io.out_plane_px = LV.plane_px; io.out_mode = 0; io.relu = true;
           if ((rc = launch_conv_tc(id, blob, tc_blob, LV, nullptr, io, fmt, s))) return rc;
-          if (release_stream != nullptr && l == 0 && b == 0 && c0 + kChunkCrops >= c &&   // last chunk: layer1.0.conv1 is launched
+          if (release && release_stream != nullptr && l == 0 && b == 0 &&   // last chunk: layer1.0.conv1 is launched
               (rc = release_after_launch(s, release_stream)))
             return rc;
           resid = buf(l, cur);
@@ -1480,13 +1491,13 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
         }
         if (first && fold) {
           io.sc_layer = id + 2;
-          io.sc_src = ws + P.off_ps[l - 1] + phl[l - 1].guard;  // phase (0,0) of the previous level's output
+          io.sc_src = ps_buf(l - 1);  // phase (0,0) of the previous level's output
           io.sc_plane_px = phl[l - 1].plane_px;
         }
         if (last) {
-          io.out = ws + P.off_ps[l] + phl[l].guard; io.out_plane_px = phl[l].plane_px; io.out_phase_units = P.ps_units[l];
+          io.out = ps_buf(l); io.out_plane_px = phl[l].plane_px; io.out_phase_units = P.ps_units[l];
           io.out_mode = 1;
-          if ((rc = launch_conv_tc(id + 1, blob, tc_blob, LV, &phl[l], io, fmt, s))) return rc;
+          if ((rc = launch_conv_tc(id + 1, blob, tc_blob, LV, &phs[l], io, fmt, s))) return rc;
         } else {
           cur = 2 - cur;
           io.out = buf(l, cur); io.out_plane_px = LV.plane_px; io.out_mode = 0;
@@ -1497,13 +1508,27 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
       cur = 0;
     }
     // proj 1x1 256->72, fp32 NHWC features.  The last block of level 3 wrote X or Y: recompute which.
-    {
+    if (l_end == 4) {
       // level 3 has 2 blocks: block 0 (first) writes X (cur: 2 -> 0), block 1 writes Y
       ConvIo io;
       memset(&io, 0, sizeof(io));
       io.a_base = buf(3, 2); io.a_plane_px = P.lv[3].plane_px;
-      io.out_mode = 2; io.out_f32 = features + (size_t)c0 * 36 * 72; io.relu = false;
-      if ((rc = launch_conv_tc(L_PROJ, blob, tc_blob, P.lv[3], nullptr, io, fmt, s))) return rc;
+      io.out_mode = 2; io.out_f32 = features + (size_t)cg0 * 36 * 72; io.relu = false;
+      if ((rc = launch_conv_tc(L_PROJ, blob, tc_blob, part(P.lv[3]), nullptr, io, fmt, s))) return rc;
+    }
+    return AT_OK;
+    };  // run_span
+    // AT_TC_SUB=<crops>: levels [0, AT_TC_SUB_LEVELS) run span by span so that a span's activations (layer 1: 154 KB per
+    // crop and tensor) stay in the 126 MB L2 between the convs of a block; the deeper levels run over the whole chunk.
+    static const int sub = getenv("AT_TC_SUB") != nullptr ? atoi(getenv("AT_TC_SUB")) : 0;
+    static const int sub_levels = getenv("AT_TC_SUB_LEVELS") != nullptr ? std::min(4, std::max(1, atoi(getenv("AT_TC_SUB_LEVELS")))) : 1;
+    const bool last_chunk = c0 + kChunkCrops >= c;
+    if (sub > 0 && sub < nc) {
+      for (long long cs = 0; cs < nc; cs += sub)
+        if ((rc = run_span(0, sub_levels, cs, std::min<long long>(sub, nc - cs), last_chunk && cs + sub >= nc))) return rc;
+      if (sub_levels < 4 && (rc = run_span(sub_levels, 4, 0, nc, false))) return rc;
+    } else if ((rc = run_span(0, 4, 0, nc, last_chunk))) {
+      return rc;
     }
   }
   (void)workspace_bytes;

@@ -186,6 +186,46 @@ WORKLOAD = ("synthetic 4-view fisheye frame stream (4x 636x480 u8 per frame, rec
             "known-skeleton head (BASELINE.json configs[3])")
 
 
+class PcieRxSampler:
+    """NVML's PCIe RX counter of one GPU (KB/s over the driver's 20 ms window), polled from a thread while the e2e
+    region runs; best effort - returns None where NVML does not expose it (some VMs)."""
+
+    def __init__(self, torch_index):
+        self.samples, self.stop_flag, self.t, self.h = [], False, None, None
+        try:
+            import pynvml
+            import torch
+
+            pynvml.nvmlInit()
+            uuid = str(torch.cuda.get_device_properties(torch_index).uuid)
+            self.h = pynvml.nvmlDeviceGetHandleByUUID(uuid if uuid.startswith("GPU-") else "GPU-" + uuid)
+            self.nv = pynvml
+        except Exception:
+            self.h = None
+
+    def _run(self):
+        while not self.stop_flag:
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetPcieThroughput(self.h, self.nv.NVML_PCIE_UTIL_RX_BYTES) * 1e3 / 1e9)
+            except Exception:
+                return
+
+    def __enter__(self):
+        if self.h is not None:
+            self.t = threading.Thread(target=self._run, daemon=True)
+            self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop_flag = True
+        if self.t is not None:
+            self.t.join(timeout=1)
+
+    def summary(self):
+        v = sorted(x for x in self.samples if x > 0)
+        return {"median": v[len(v) // 2], "max": v[-1], "samples": len(v)} if v else None
+
+
 def bind_to_gpu_numa_node(index):
     """One process per GPU: run (and therefore allocate the pinned frame buffers) on the CPU cores next to
     that GPU, so that the source-box pull crosses PCIe without also crossing the socket interconnect.
@@ -339,7 +379,8 @@ def main():
         out_host[0] = tracker.step(host[i % NB], out_host[0])
         issue[0] += time.perf_counter() - t0
 
-    ms_e2e, _ = timed(step_host, args.steps, args.warmup)
+    with PcieRxSampler(local_rank) as pcie:
+        ms_e2e, _ = timed(step_host, args.steps, args.warmup)
     issue_ms = issue[0] / (args.steps + args.warmup) * 1e3  # host time to enqueue one step (must stay below the GPU time)
     e2e_value = world * n / (ms_e2e / args.steps * 1e-3)
     small = host[0].nbytes() - host[0].frames.numel()
@@ -482,7 +523,10 @@ def main():
                        "host_numa_binding": numa},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "api": "BatchedHandTracker.step (pinned host buffers)", "ingest": ingest, "host_issue_ms_per_step": issue_ms,
-                    "host_frame_bytes_per_step": int(host[0].frames.numel())},
+                    "host_frame_bytes_per_step": int(host[0].frames.numel()),
+                    # the limiter of this arm at N = 8: bytes each GPU pulls over PCIe per second of the timed region
+                    # (counted by the pull kernel), and NVML's RX counter of rank 0's GPU over the same region
+                    "pcie_rx_gbs_per_gpu": h2d / (ms_e2e / args.steps * 1e-3) / 1e9, "pcie_rx_gbs_nvml": pcie.summary()},
             "e2e_from_poses": e2e_poses,
             "gpu_launches": int(launches),
             "roofline": {"bound": "tensor", "kernel": "per-view encoder (all conv launches of at_encoder_forward)",

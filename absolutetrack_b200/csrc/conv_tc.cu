@@ -63,6 +63,7 @@ struct ConvTcParams {
   long long out_plane_px;
   uint4* out_ph[4];
   long long out_ph_plane_px;
+  long long out_ph_stride;   // units between consecutive phase images (S2D epilogue)
   float* out_f32;
   // folded 1x1 stride-2 shortcut (first block of layers 2-4): sc_nk extra K chunks read phase image
   // (0,0) of the block input at shift 0 and accumulate W_sc x into the same accumulator
@@ -97,6 +98,7 @@ struct ConvTcParams {
   // 1 / n_split of a tile time instead of a whole one (layer 3: 9.13 -> 10 waves without it).  n_split = 1: plain tiles.
   int t_full, n_split, split_shift, n_items;
   // cta_group::2 (conv_tc2_kernel): each CTA of a pair holds n / 2 output channels of every weight block
+  int bias_wrap;          // > 0: bias index = channel % bias_wrap (S2D: both pixel parities share the layer's 32 biases)
   uint32_t w_src_bytes;   // bytes of a whole weight block in global memory (= block stride)
   uint32_t w_kg_bytes;    // bytes of one 8-channel K group of a whole block in global memory (n * 16)
 };
@@ -127,8 +129,15 @@ struct EpiCoord {
 // bias and an optional fp32 NHWC residual, applies ReLU, and writes fp32 NHWC and/or the split planes
 // of the next conv.
 // WRES: the layer's weights stay resident in shared memory (else they stream through a ring).
-template <int NTAPS, int KSTEPS, int MT, int WRES, int MODE>
+// S2D: layer 1 as a 64 -> 64 conv over the x-space-to-depth view of its 48 x 48 x 32 maps (rows of 24 pixel PAIRS,
+// channels [even pixel 0..31 | odd pixel 0..31] = planes 0-3 | 4-7): one accumulator row holds two output pixels
+// (TMEM columns [0,32) | [32,64)), so the A operand - what an N = 32 MMA spends its time reading - is read once
+// for both.  Tap (dy, di) of that view carries W[dy][dx = 2 di + pi - po]: the centre column is dense (K = 64,
+// N = 64), di = -1 only connects odd inputs to even outputs (K steps 2-3, N = columns 0-31) and di = +1 even inputs
+// to odd outputs (K steps 0-1, columns 32-63); the other halves are structural zeros and are not issued.
+template <int NTAPS, int KSTEPS, int MT, int WRES, int MODE, int S2D = 0>
 __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
+  static_assert(!S2D || (NTAPS == 9 && KSTEPS == 4 && WRES == 1 && (MODE == 0 || MODE == 5)), "S2D: 3x3, 64 -> 64, resident weights");
   extern __shared__ __align__(128) uint8_t smem[];
   using namespace ptx;
   const uint32_t sbase = smem_u32(smem);
@@ -155,7 +164,7 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
     tmem_relinquish();
   }
   for (int i = threadIdx.x; i < p.n; i += kThreads)
-    bias_s[i] = i < p.cout ? p.bias[i] + (p.bias2 != nullptr ? p.bias2[i] : 0.f) : 0.f;
+    bias_s[i] = i < p.cout ? p.bias[p.bias_wrap > 0 ? i % p.bias_wrap : i] + (p.bias2 != nullptr ? p.bias2[i] : 0.f) : 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -225,6 +234,8 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
     const bool prof = p.prof != nullptr && (p.dbg & 16);
     if (p.prof != nullptr && lane == 0) p.prof[blockIdx.x * 16 + 7] = (long long)globaltimer_ns();
     const uint32_t idesc_full = idesc, idesc_part = umma_idesc(kTileM, n_part, p.fmt);
+    const uint32_t idesc_half = umma_idesc(kTileM, 32, p.fmt);   // S2D side taps
+    (void)idesc_half;
     for (int it = 0; it < n_my; ++it) {
       int sp;
       item_tile(first_tile + it * (int)gridDim.x, sp);
@@ -250,15 +261,22 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
           if (elect_one()) {
             const uint32_t b_lo = b_lo0 + kci * NTAPS * w_blk16 + b_sp;
 #pragma unroll
-            for (int t = 0; t < NTAPS; ++t) {
+            for (int ti = 0; ti < NTAPS; ++ti) {
+              // S2D issues the dense centre tap of a row first, so that the first MMA of a tile initialises all 64 columns
+              const int t = S2D ? (ti % 3 == 0 ? ti + 1 : (ti % 3 == 1 ? ti - 1 : ti)) : ti;
+              const int di = S2D ? t % 3 - 1 : 0;
 #pragma unroll
               for (int j = 0; j < KSTEPS; ++j) {
-                const uint64_t bd = ((uint64_t)desc_hi << 32) | (b_lo + (t * KSTEPS + j) * b_kstep16);
+                if (S2D && ((di < 0 && j < 2) || (di > 0 && j >= 2))) continue;   // structural zeros
+                const uint32_t nsh = (S2D && di > 0) ? 32u : 0u;                     // output columns / B rows of this tap
+                const uint64_t bd = ((uint64_t)desc_hi << 32) | (b_lo + (t * KSTEPS + j) * b_kstep16 + nsh);
 #pragma unroll
                 for (int m = 0; m < MT; ++m) {
                   const uint64_t ad = ((uint64_t)desc_hi << 32) | (a_lo + tap_off[t] + j * a_kstep16 + m * kTileM);
                   if (kStem)
                     umma_f16(d_base + (t >> 1) * p.n, ad, bd, idesc, (uint32_t)(t & 1));
+                  else if (S2D)
+                    umma_f16(d_base + m * p.n + nsh, ad, bd, di != 0 ? idesc_half : idesc, (ti | j) != 0 ? 1u : acc0);
                   else
                     umma_f16(d_base + m * p.n, ad, bd, idesc, (t | j) != 0 ? 1u : acc0);
                 }
@@ -435,7 +453,10 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
               const uint32_t y = fast_div(rem, p.div_wp), x = rem - y * p.div_wp.d;
               valid = (long long)g < p.P && y < (uint32_t)p.H && x < (uint32_t)p.W;
               taddr = tmem_base + ((uint32_t)(qd * 32) << 16) + rc.slot * p.acc_cols + m * p.n;
-              if (out_mode == 1) {
+              if (out_mode == 1 && S2D) {   // x counts pixel pairs: the column parity is the channel half (below)
+                out_ph = p.out_ph[(y & 1) * 2];
+                o1 = (long long)img * (p.Hp2 * p.Wp2) + (y >> 1) * p.Wp2 + x;
+              } else if (out_mode == 1) {
                 out_ph = p.out_ph[(y & 1) * 2 + (x & 1)];
                 o1 = (long long)img * (p.Hp2 * p.Wp2) + (y >> 1) * p.Wp2 + (x >> 1);
               } else if (out_mode == 2) {
@@ -554,6 +575,8 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
                 if (cg < ncg && (wide || h < 2)) {
                   if (out_mode == 0)
                     p.out[(long long)cg * p.out_plane_px + g] = pk[h];
+                  else if (valid && S2D)   // planes 0-3 = even columns -> phase (y&1, 0), planes 4-7 -> phase (y&1, 1)
+                    (out_ph + (cg >> 2) * p.out_ph_stride)[(long long)(cg & 3) * p.out_ph_plane_px + o1] = pk[h];
                   else if (valid)
                     out_ph[(long long)cg * p.out_ph_plane_px + o1] = pk[h];
                 }
@@ -642,7 +665,12 @@ int zero_halo(uint4* base, long long n_planes, const Level& L, bool pads, cudaSt
 struct TcLayer {
   int64_t offset;  // bytes into the tc blob
   int n_pad, kc, nk;
+  int64_t s2d_offset;  // layer 1 only: the same conv as 64 -> 64 blocks over the x-space-to-depth view (-1: none)
 };
+constexpr int kS2dC = 64;                                  // channels of the x-space-to-depth view of layer 1
+constexpr int64_t kS2dMainBytes = 9 * kS2dC * kS2dC * 2;   // nine dense [8][64][8] blocks (structural zeros included)
+constexpr int64_t kS2dIdBytes = kS2dC * kS2dC * 2;
+bool is_s2d_layer_host(int i) { return i >= L_LAYER1 && i < L_LAYER1 + 4; }
 TcLayer g_tc[L_COUNT];
 int64_t g_tc_bytes = 0;
 std::once_flag g_tc_once;
@@ -678,6 +706,12 @@ void build_tc_table() {
     if (is_fold_host(i)) off += (int64_t)T[i + 1].cin * g_tc[i].n_pad * 2;  // copy of the shortcut's blocks (layer i + 1)
     if (is_identity_host(i)) off += (int64_t)T[i].cout * g_tc[i].n_pad * 2;    // identity blocks
     off = round_up(off, 128);
+    g_tc[i].s2d_offset = -1;
+    if (is_s2d_layer_host(i)) {
+      g_tc[i].s2d_offset = off;
+      off += kS2dMainBytes + (is_identity_host(i) ? kS2dIdBytes : 0);
+      off = round_up(off, 128);
+    }
   }
   g_tc_bytes = off + 128;
 }
@@ -696,6 +730,23 @@ __global__ void prepack_identity_kernel(uint16_t* __restrict__ out, int c, int n
   const int kk = (int)(r % (kc / 8));
   const int kci = (int)(r / (kc / 8));
   out[i] = ptx::pack1(kci * kc + kk * 8 + e == nn ? 1.0f : 0.0f, fmt);
+}
+
+// Layer-1 weights [9][32][coutP] -> nine [8][64][8] blocks of the x-space-to-depth view: input channel
+// ci' = pi * 32 + ci (pi = parity of the input column), output nn = po * 32 + co, tap (dy, di) carries
+// W[dy][dx] with dx = 2 di + pi - po when that is a tap of the 3x3 kernel and zero otherwise.
+__global__ void prepack_s2d_kernel(const float* __restrict__ w, uint16_t* __restrict__ out, int coutP, int fmt) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 9 * kS2dC * kS2dC) return;
+  const int e = i & 7;
+  int r = i >> 3;
+  const int nn = r % kS2dC; r /= kS2dC;
+  const int kk = r % (kS2dC / 8);
+  const int t = r / (kS2dC / 8);
+  const int cip = kk * 8 + e, pi = cip >> 5, ci = cip & 31, po = nn >> 5, co = nn & 31;
+  const int dy = t / 3, dx = 2 * (t % 3 - 1) + pi - po;
+  const float v = (dx >= -1 && dx <= 1) ? w[((long long)(dy * 3 + dx + 1) * 32 + ci) * coutP + co] : 0.f;
+  out[i] = ptx::pack1(v, fmt);
 }
 
 __global__ void prepack_kernel(const float* __restrict__ w /*[taps][cin][coutP]*/, uint16_t* __restrict__ out, int taps,
@@ -901,6 +952,7 @@ struct ConvIo {
   int sc_layer;              // > 0: fold this 1x1 stride-2 shortcut layer into the accumulator ...
   const uint4* sc_src;       // ... reading phase image (0,0) of the block input (plane 0 / pixel 0)
   long long sc_plane_px;
+  bool s2d;                  // layer 1 over its x-space-to-depth view (the Level passed is the 48 x 24 x 64 one)
 };
 
 // A convolution that is not a row of the backbone layer table (the pose-head convs of the tail).
@@ -1081,8 +1133,18 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
     L = layer_table()[layer_id];
     T = tc_table()[layer_id];
   }
+  if (io.s2d) {
+    if (desc != nullptr || T.s2d_offset < 0 || L.ksize != 3 || L.stride != 1 || L.cin != 32 || L.cout != 32 || io.res != nullptr ||
+        io.sc_layer > 0 || (io.out_mode != 0 && io.out_mode != 1)) {
+      set_error("conv_tc: layer %s has no space-to-depth form", L.name);
+      return AT_ERR_UNSUPPORTED;
+    }
+    L.cin = L.cout = kS2dC;
+    T.offset = T.s2d_offset; T.n_pad = kS2dC; T.kc = kS2dC; T.nk = 1;
+  }
   ConvTcParams p;
   memset(&p, 0, sizeof(p));
+  p.bias_wrap = io.s2d ? 32 : 0;
   const bool is_stem = desc == nullptr && layer_id == L_STEM;
   const int taps = is_stem ? 8 : L.ksize * L.ksize;
   p.n_taps = taps;
@@ -1133,6 +1195,7 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   if (g_prof != nullptr && g_prof_seq >= 0) p.prof = g_prof + (long long)(g_prof_seq++) * kNumSMs * 16;
   if (io.out_mode == 1) {
     for (int s = 0; s < 4; ++s) p.out_ph[s] = io.out + s * io.out_phase_units;
+    p.out_ph_stride = io.out_phase_units;
     p.out_ph_plane_px = io.out_plane_px;
     p.Hp2 = next->Hp; p.Wp2 = next->Wp;
   }
@@ -1153,7 +1216,7 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   if (taps == 1) mt = 1;
   while (mt > 1 && round_up(mt * p.n, 32) > 256) mt >>= 1;  // keep >= 2 accumulator stages
   if (io.sc_layer == -1) {  // identity shortcut: x accumulated through identity weight blocks
-    if (desc != nullptr || !is_identity_host(layer_id) || L.cin != L.cout) {
+    if (desc != nullptr || !is_identity_host(layer_id) || L.cin != L.cout) {  // (S2D: the 64 x 64 identity follows the nine blocks)
       set_error("conv_tc: layer %s has no identity blocks", L.name);
       return AT_ERR_UNSUPPORTED;
     }
@@ -1181,7 +1244,7 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
     // at best, layer 3 with resident weights): the relay / multicast-commit turnaround costs more than the halved B reads save.
     static const int cg2_mask = getenv("AT_TC_CG2") == nullptr ? 0 : atoi(getenv("AT_TC_CG2"));
     const bool use_cg2 = (cg2_mask & (p.n == 64 ? 1 : p.n == 128 ? 2 : 4)) != 0;
-    if (use_cg2 && desc == nullptr && !is_stem && taps == 9 && p.n >= 64 && p.n % 32 == 0 && io.res == nullptr &&
+    if (use_cg2 && desc == nullptr && !is_stem && !io.s2d && taps == 9 && p.n >= 64 && p.n % 32 == 0 && io.res == nullptr &&
         (io.out_mode == 0 || io.out_mode == 1) && p.cout == p.n)
       return launch_conv_tc2(p, L.name, OL, io.out_mode, mt, max_shift, stream);
   }
@@ -1231,7 +1294,7 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   {
     static const bool nsplit = getenv("AT_TC_NSPLIT") == nullptr || atoi(getenv("AT_TC_NSPLIT")) != 0;
     const int rest = (int)(p.n_tiles % kNumSMs);
-    if (nsplit && rest > 0 && !is_stem && io.res == nullptr && io.out_mode != 3 && io.out_mode != 2 && p.cout == p.n && p.n % 64 == 0) {
+    if (nsplit && rest > 0 && !is_stem && !io.s2d && io.res == nullptr && io.out_mode != 3 && io.out_mode != 2 && p.cout == p.n && p.n % 64 == 0) {
       int sh = 0;
       while ((p.n >> (sh + 1)) % 32 == 0 && (rest << (sh + 1)) <= kNumSMs) ++sh;   // slices of >= 32 channels, one wave
       if (sh > 0) { p.t_full = (int)p.n_tiles - rest; p.split_shift = sh; p.n_split = 1 << sh; }
@@ -1256,7 +1319,11 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   using Kernel = void (*)(const ConvTcParams);
   Kernel fn = nullptr;
 #define AT_TC_CASE(T, K, M, R, O) \
-  if (taps == T && ksteps == K && mt == M && p.w_resident == R && mode == O) fn = conv_tc_kernel<T, K, M, R, O>;
+  if (!io.s2d && taps == T && ksteps == K && mt == M && p.w_resident == R && mode == O) fn = conv_tc_kernel<T, K, M, R, O>;
+  if (io.s2d && p.w_resident == 1 && mode == 0 && mt == 2) fn = conv_tc_kernel<9, 4, 2, 1, 0, 1>;
+  if (io.s2d && p.w_resident == 1 && mode == 5 && mt == 2) fn = conv_tc_kernel<9, 4, 2, 1, 5, 1>;
+  if (io.s2d && p.w_resident == 1 && mode == 0 && mt == 1) fn = conv_tc_kernel<9, 4, 1, 1, 0, 1>;
+  if (io.s2d && p.w_resident == 1 && mode == 5 && mt == 1) fn = conv_tc_kernel<9, 4, 1, 1, 5, 1>;
 #define AT_TC_CASE3(T, K, M, R) \
   AT_TC_CASE(T, K, M, R, 0) AT_TC_CASE(T, K, M, R, 1) AT_TC_CASE(T, K, M, R, 2) AT_TC_CASE(T, K, M, R, 5)
   AT_TC_CASE(8, 1, 1, 1, 0)
@@ -1317,6 +1384,7 @@ constexpr int kChunkCrops = 2048;
 
 struct Plan {
   Level lv[4];   // activation geometry per resolution level (48, 24, 12, 6)
+  int ch[4];     // channels of the level (lv[0].C is 64 in the space-to-depth view of level 0)
   long long buf_units[4];   // one activation buffer per level (16-byte units)
   long long ps_units[3];    // one phase image set member (phase stride) for the outputs of levels 0..2
   long long off_lv[4];      // workspace offsets (units): 4 buffers per level (X, T, Y, D)
@@ -1324,12 +1392,20 @@ struct Plan {
   long long total_units;
 };
 
+// AT_TC_S2D=0: layer 1 as plain 32 -> 32 convs (the round-1 form) instead of the x-space-to-depth form (conv_tc_kernel S2D)
+bool s2d_enabled() {
+  static const bool on = (getenv("AT_TC_S2D") == nullptr || atoi(getenv("AT_TC_S2D")) != 0) &&
+                         (getenv("AT_STEM_MMA") == nullptr || atoi(getenv("AT_STEM_MMA")) != 0);
+  return on;
+}
+
 Plan make_plan(long long nc) {
   Plan P;
   const int HW[4] = {48, 24, 12, 6}, C[4] = {32, 64, 128, 256};
   long long off = 0;
   for (int l = 0; l < 4; ++l) {
-    P.lv[l] = make_level(HW[l], HW[l], C[l], nc);
+    P.lv[l] = l == 0 && s2d_enabled() ? make_level(48, 24, kS2dC, nc) : make_level(HW[l], HW[l], C[l], nc);
+    P.ch[l] = C[l];
     P.buf_units[l] = P.lv[l].buf_units();
     P.off_lv[l] = off;
     off += 4 * P.buf_units[l];
@@ -1364,7 +1440,7 @@ int encoder_prepare_workspace(void* workspace, long long nc, cudaStream_t s) {
   for (int l = 0; l < 4; ++l)
     if ((rc = zero_halo(ws + P.off_lv[l], 4 * P.lv[l].planes(), P.lv[l], false, s))) return rc;
   for (int l = 0; l < 3; ++l) {
-    Level ph = make_level(P.lv[l + 1].H, P.lv[l + 1].W, P.lv[l].C, nc);
+    Level ph = make_level(P.lv[l + 1].H, P.lv[l + 1].W, P.ch[l], nc);
     if ((rc = zero_halo(ws + P.off_ps[l], 4 * ph.planes(), ph, true, s))) return rc;
   }
   return AT_OK;
@@ -1392,7 +1468,7 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
       prepared_c = (int)nc;
     }
     Level phl[3];
-    for (int l = 0; l < 3; ++l) phl[l] = make_level(P.lv[l + 1].H, P.lv[l + 1].W, P.lv[l].C, nc);
+    for (int l = 0; l < 3; ++l) phl[l] = make_level(P.lv[l + 1].H, P.lv[l + 1].W, P.ch[l], nc);
     // One span of the pass: the stem (l_begin == 0), levels [l_begin, l_end) and the projection (l_end == 4) over
     // crops [cs, cs + n) of the chunk.  A span over part of the chunk addresses the same planes at a crop offset
     // (the planes keep the chunk's stride, tiles are counted from the span's first pixel).
@@ -1403,6 +1479,7 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
     Level phs[3];
     for (int l = 0; l < 3; ++l) phs[l] = part(phl[l]);
     const long long cg0 = c0 + cs;  // first crop of the span in the caller's arrays
+    const bool s2d = s2d_enabled();
     // stem.  Default: mma.sync kernel straight from the crops (registers, no TMEM read-back, no pack kernel).
     // AT_STEM_MMA=0: pack the crops into the 2x2-block plane S (first plane of the unused D buffer of level 0),
     // then the tcgen05 stem GEMM writes X of level 0 (A/B).
@@ -1417,7 +1494,7 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
   do {                                                                                                              \
     AT_CARVEOUT_ONCE((stem_mma_kernel<TIN, F>));                                                                    \
     stem_mma_kernel<TIN, F><<<grid, kStemThreads, 0, s>>>((const TIN*)crops + (size_t)cg0 * 96 * 96, (int)n, wf, bias, \
-                                                          buf(0, 0), L0, g_status);                                 \
+                                                          buf(0, 0), L0, g_status, s2d ? 1 : 0);                    \
   } while (0)
       if (crop_dtype == AT_U8) { if (fmt) AT_STEM_LAUNCH(uint8_t, 1); else AT_STEM_LAUNCH(uint8_t, 0); }
       else { if (fmt) AT_STEM_LAUNCH(float, 1); else AT_STEM_LAUNCH(float, 0); }
@@ -1457,6 +1534,7 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
         const bool last = b == nblocks[l] - 1 && l < 3;
         ConvIo io;
         memset(&io, 0, sizeof(io));
+        io.s2d = s2d && l == 0;
         uint4* Tm = buf(l, 1);
         const uint4* resid;
         if (first) {
@@ -1483,6 +1561,7 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
           resid = buf(l, cur);
         }
         memset(&io, 0, sizeof(io));
+        io.s2d = s2d && l == 0;
         io.a_base = Tm; io.a_plane_px = LV.plane_px;
         io.res = resid; io.res_plane_px = LV.plane_px; io.relu = true;
         if (!first && (fold_id >> l) & 1) {  // identity residual as a 10th tap
@@ -1693,6 +1772,17 @@ extern "C" int at_model_prepack_tc(const float* blob, void* tc_blob, int precisi
           reinterpret_cast<uint16_t*>(reinterpret_cast<uint8_t*>(tc_blob) + TT[i].offset + main_bytes), T[i].cout, TT[i].n_pad,
           TT[i].kc, precision == AT_PREC_BF16 ? 1 : 0);
       if ((rc = check_launch("prepack_identity_kernel"))) return rc;
+    }
+    if (TT[i].s2d_offset >= 0) {  // layer 1: the x-space-to-depth form (+ its 64 x 64 identity block)
+      uint16_t* dst = reinterpret_cast<uint16_t*>(reinterpret_cast<uint8_t*>(tc_blob) + TT[i].s2d_offset);
+      tc::prepack_s2d_kernel<<<(9 * tc::kS2dC * tc::kS2dC + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+          blob + T[i].weight_offset, dst, (int)round_up(T[i].cout, 4), precision == AT_PREC_BF16 ? 1 : 0);
+      if ((rc = check_launch("prepack_s2d_kernel"))) return rc;
+      if (tc::is_identity_host(i)) {
+        tc::prepack_identity_kernel<<<(tc::kS2dC * tc::kS2dC + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+            dst + tc::kS2dMainBytes / 2, tc::kS2dC, tc::kS2dC, tc::kS2dC, precision == AT_PREC_BF16 ? 1 : 0);
+        if ((rc = check_launch("prepack_identity_kernel"))) return rc;
+      }
     }
     if (tc::is_fold_host(i)) {  // second copy of the block's 1x1 shortcut weights, behind conv2's own blocks
       const ConvLayer& S = T[i + 1];

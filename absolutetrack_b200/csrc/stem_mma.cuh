@@ -7,7 +7,8 @@
 // pack kernel.  Here one m16n8k16 group covers 16 pooled pixels of a row: K = the 4x4 input patch around the
 // 2x2 block of a pooled pixel (exactly 16 values), N = 4 pooling phases x 32 channels.  The four phase
 // accumulators of a channel land in the same thread, so the pool is three FMNMX in registers; bias, ReLU,
-// 16-bit pack and the planar store follow.  The crop is staged once per CTA as 16-bit values (the /255
+// 16-bit pack and the planar store follow (s2d: into the x-space-to-depth view of level 0 - rows of 24 pixel
+// pairs, planes 0-3 = even columns, 4-7 = odd columns; L is then the 48 x 24 x 64 level).  The crop is staged once per CTA as 16-bit values (the /255
 // through a 256-entry table, bit-identical to the fp32 division the other paths use) in words
 // (col 2m-1, col 2m), so every A fragment register is one aligned LDS.32.  Writes the level-0 planar layout
 // including its zero pad cells.
@@ -46,7 +47,7 @@ __device__ __forceinline__ void mma_16816(float (&c)[4], const uint32_t (&a)[4],
 template <typename TIn, int FMT>
 __global__ void __launch_bounds__(kStemThreads, 2)
 stem_mma_kernel(const TIn* __restrict__ crops, int n_crops, const uint2* __restrict__ wfrag, const float* __restrict__ bias,
-                uint4* __restrict__ out /*plane 0, pixel 0*/, Level L, int32_t* __restrict__ status) {
+                uint4* __restrict__ out /*plane 0, pixel 0*/, Level L, int32_t* __restrict__ status, int s2d) {
   __shared__ __align__(16) uint32_t tile[kStemRows * kStemPW];
   __shared__ uint16_t lut[256];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -119,22 +120,26 @@ stem_mma_kernel(const TIn* __restrict__ crops, int n_crops, const uint2* __restr
             for (int e = 0; e < 4; ++e) best[cb][e] = q == 0 ? acc[e] : fmaxf(best[cb][e], acc[e]);
           }
         }
-        const long long g0 = img_base + (long long)py * L.Wp + px0 + r;
+        // pooled pixels px0 + r and px0 + r + 8 of row py
+        const long long g0 = s2d ? img_base + (long long)py * L.Wp + (px0 >> 1) + (r >> 1) : img_base + (long long)py * L.Wp + px0 + r;
+        const int pl0 = s2d ? (r & 1) * 4 : 0;
+        const int second = s2d ? 4 * 4 : 8 * 4;   // words to the second pixel (4 pairs / 8 pixels further)
 #pragma unroll
         for (int cb = 0; cb < 4; ++cb) {
           const uint32_t lo = ptx::pack2(fmaxf(best[cb][0] + bs[cb][0], 0.f), fmaxf(best[cb][1] + bs[cb][1], 0.f), FMT);
           const uint32_t hi = ptx::pack2(fmaxf(best[cb][2] + bs[cb][0], 0.f), fmaxf(best[cb][3] + bs[cb][1], 0.f), FMT);
           if (FMT == 0) ovf |= ptx::overflow_probe(lo) | ptx::overflow_probe(hi);
-          uint32_t* op = reinterpret_cast<uint32_t*>(out + (long long)cb * L.plane_px + g0) + j;
+          uint32_t* op = reinterpret_cast<uint32_t*>(out + (long long)(pl0 + cb) * L.plane_px + g0) + j;
           op[0] = lo;
-          op[8 * 4] = hi;   // pooled pixel + 8
+          op[second] = hi;   // pooled pixel + 8
         }
       }
-      if (lane < 16)  // the pad column x = W of this row
+      if (lane < (s2d ? 32 : 16))  // the pad column x = W of this row (all 4 / 8 planes)
         reinterpret_cast<uint32_t*>(out + (long long)(lane >> 2) * L.plane_px + img_base + (long long)py * L.Wp + L.W)[lane & 3] = 0u;
     }
-    for (int i = tid; i < L.Wp * 16; i += kStemThreads)  // the pad row y = H
-      reinterpret_cast<uint32_t*>(out + (long long)((i >> 2) & 3) * L.plane_px + img_base + (long long)L.H * L.Wp + (i >> 4))[i & 3] = 0u;
+    const int npl = s2d ? 8 : 4;
+    for (int i = tid; i < L.Wp * npl * 4; i += kStemThreads)  // the pad row y = H
+      reinterpret_cast<uint32_t*>(out + (long long)((i >> 2) % npl) * L.plane_px + img_base + (long long)L.H * L.Wp + i / (npl * 4))[i & 3] = 0u;
   }
   if (status != nullptr && (ovf & ptx::kOverflowProbeMask) != 0u) atomicOr(status, 2);
 }

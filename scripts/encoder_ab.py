@@ -32,6 +32,12 @@ def main():
         f = model.encode(crops[i & 1])
     torch.cuda.synchronize()
     sha = hashlib.sha1(model.encode(crops[0]).float().cpu().numpy().tobytes()).hexdigest()
+    # accuracy of the 16-bit features against the fp32 CUDA-core encoder on the first 64 crops
+    ref_model = model_from_state_dict(make_random_state_dict(0), precision="fp32").cuda()
+    fr = ref_model.encode(crops[0][:64]).float()
+    ft = model.encode(crops[0][:64]).float()
+    err = (ft - fr).abs()
+    err_vs_fp32 = {"max": float(err.max()), "mean": float(err.mean()), "ref_abs_mean": float(fr.abs().mean())}
     ms = []
     for i in range(args.iters):
         flush.zero_()          # L2 holds nothing of the previous pass
@@ -44,7 +50,8 @@ def main():
     ms.sort()
     med = ms[len(ms) // 2]
     print(json.dumps({"env": {k: v for k, v in os.environ.items() if k.startswith("AT_")}, "crops": args.crops, "ms": med,
-                      "ms_min": ms[0], "tflops": 969228288 * args.crops / (med * 1e-3) / 1e12, "features_sha1": sha}))
+                      "ms_min": ms[0], "tflops": 969228288 * args.crops / (med * 1e-3) / 1e12, "features_sha1": sha,
+                      "err_vs_fp32_encoder": err_vs_fp32}))
 
 
 if __name__ == "__main__":

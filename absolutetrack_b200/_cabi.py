@@ -202,6 +202,7 @@ SIGNATURES = {
     "at_encoder_forward_prepared": (_I, [_VP, _VP, _VP, _I, _I, _VP, _VP, _I64, _I, _I, _VP]),
     "at_encoder_forward_status": (_I, [_VP, _VP, _VP, _I, _I, _VP, _VP, _I64, _I, _I, _VP, _VP]),
     "at_encoder_forward_release": (_I, [_VP, _VP, _VP, _I, _I, _VP, _VP, _I64, _I, _I, _VP, _VP, _VP]),
+    "at_encoder_forward_front": (_I, [_VP, _VP, _VP, _I, _I, _VP, _VP, _I64, _I, _I, _VP, _VP, _VP, _VP]),
     "at_tail_workspace_bytes": (_I64, [_I]),
     "at_tail_forward": (
         _I,

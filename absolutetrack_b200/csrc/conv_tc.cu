@@ -983,26 +983,29 @@ thread_local int32_t* g_status = nullptr;  // status word of the encoder call in
 // `release_stream` is made to wait for it.  Side-stream work released at that point (the source-box pull of the NEXT step)
 // meets an SM array that is full of conv CTAs and spreads over their leftover registers, instead of piling up on
 // the SMs that happen to be free at a kernel boundary and pushing a CTA of the 148-CTA persistent conv grids into a second wave.
-int release_after_launch(cudaStream_t s, cudaStream_t release_stream) {
+// `which`: one event per device and purpose (0 = release point, 1 = front stream -> encoder stream)
+int order_streams(cudaStream_t from, cudaStream_t to, int which) {
   static std::mutex mu;
-  static cudaEvent_t ev[64] = {};
+  static cudaEvent_t ev[2][64] = {};
   int dev = 0;
   cudaGetDevice(&dev);
   cudaEvent_t e;
   {
     std::lock_guard<std::mutex> lock(mu);
-    if (ev[dev & 63] == nullptr && cudaEventCreateWithFlags(&ev[dev & 63], cudaEventDisableTiming) != cudaSuccess) {
+    cudaEvent_t& slot = ev[which & 1][dev & 63];
+    if (slot == nullptr && cudaEventCreateWithFlags(&slot, cudaEventDisableTiming) != cudaSuccess) {
       set_error("at_encoder_forward: cudaEventCreate: %s", cudaGetErrorString(cudaGetLastError()));
       return AT_ERR_CUDA;
     }
-    e = ev[dev & 63];
+    e = slot;
   }
-  if (cudaEventRecord(e, s) != cudaSuccess || cudaStreamWaitEvent(release_stream, e, 0) != cudaSuccess) {
-    set_error("at_encoder_forward: release event: %s", cudaGetErrorString(cudaGetLastError()));
+  if (cudaEventRecord(e, from) != cudaSuccess || cudaStreamWaitEvent(to, e, 0) != cudaSuccess) {
+    set_error("at_encoder_forward: stream ordering event: %s", cudaGetErrorString(cudaGetLastError()));
     return AT_ERR_CUDA;
   }
   return AT_OK;
 }
+int release_after_launch(cudaStream_t s, cudaStream_t release_stream) { return order_streams(s, release_stream, 0); }
 
 
 // conv_tc2_kernel (CTA pairs): ring / residency configuration and launch.  `p` arrives with the layer, tap, source
@@ -1450,7 +1453,7 @@ int encoder_prepare_workspace(void* workspace, long long nc, cudaStream_t s) {
 // chunk (encoder_prepare_workspace) and only written by this function since.
 int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* crops, int crop_dtype, int c, float* features,
                          void* workspace, int64_t workspace_bytes, int fmt, int prepared_c, int32_t* status,
-                         cudaStream_t release_stream, cudaStream_t s) {
+                         cudaStream_t front_stream, cudaStream_t release_stream, cudaStream_t s) {
   using namespace tc;
   struct StatusScope {  // every conv launch of this call reports fp16 saturation into `status`
     explicit StatusScope(int32_t* p) { g_status = p; }
@@ -1463,10 +1466,18 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
     const long long nc = std::min(c - c0, kChunkCrops);
     const Plan P = make_plan(nc);
     int rc;
+    bool prepared_now = false;
     if (nc != prepared_c) {
       if ((rc = encoder_prepare_workspace(workspace, nc, s))) return rc;
       prepared_c = (int)nc;
+      prepared_now = true;
     }
+    // Front stream: the caller produced the crops there and the stem of the first chunk may run there too, next to whatever
+    // `s` still has queued in front of this call (BatchedHandTracker: the previous step's tail); `s` joins before layer 1.
+    // Not when this call had to prepare the workspace on `s` (the stem writes it), and not for later chunks (their stem
+    // overwrites planes the previous chunk's convs on `s` still read): then `s` simply waits for the front stream first.
+    const bool stem_on_front = front_stream != nullptr && front_stream != s && c0 == 0 && !prepared_now;
+    if (front_stream != nullptr && front_stream != s && c0 == 0 && !stem_on_front && (rc = order_streams(front_stream, s, 1))) return rc;
     Level phl[3];
     for (int l = 0; l < 3; ++l) phl[l] = make_level(P.lv[l + 1].H, P.lv[l + 1].W, P.ch[l], nc);
     // One span of the pass: the stem (l_begin == 0), levels [l_begin, l_end) and the projection (l_end == 4) over
@@ -1484,6 +1495,11 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
     // AT_STEM_MMA=0: pack the crops into the 2x2-block plane S (first plane of the unused D buffer of level 0),
     // then the tcgen05 stem GEMM writes X of level 0 (A/B).
     static const bool stem_mma = getenv("AT_STEM_MMA") == nullptr || atoi(getenv("AT_STEM_MMA")) != 0;
+    cudaStream_t ss = s;   // stream of the stem launch
+    if (l_begin == 0 && stem_on_front && cs == 0) {
+      if (stem_mma) ss = front_stream;
+      else if ((rc = order_streams(front_stream, s, 1))) return rc;
+    }
     if (l_begin > 0) {
     } else if (stem_mma) {
       const Level L0 = part(P.lv[0]);
@@ -1493,13 +1509,14 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
 #define AT_STEM_LAUNCH(TIN, F)                                                                                        \
   do {                                                                                                              \
     AT_CARVEOUT_ONCE((stem_mma_kernel<TIN, F>));                                                                    \
-    stem_mma_kernel<TIN, F><<<grid, kStemThreads, 0, s>>>((const TIN*)crops + (size_t)cg0 * 96 * 96, (int)n, wf, bias, \
+    stem_mma_kernel<TIN, F><<<grid, kStemThreads, 0, ss>>>((const TIN*)crops + (size_t)cg0 * 96 * 96, (int)n, wf, bias, \
                                                           buf(0, 0), L0, g_status, s2d ? 1 : 0);                    \
   } while (0)
       if (crop_dtype == AT_U8) { if (fmt) AT_STEM_LAUNCH(uint8_t, 1); else AT_STEM_LAUNCH(uint8_t, 0); }
       else { if (fmt) AT_STEM_LAUNCH(float, 1); else AT_STEM_LAUNCH(float, 0); }
 #undef AT_STEM_LAUNCH
       if ((rc = check_launch("stem_mma_kernel"))) return rc;
+      if (ss != s && (rc = order_streams(ss, s, 1))) return rc;
     } else {
       const Level L0 = part(P.lv[0]);
       const unsigned blocks = (unsigned)((L0.P + 255) / 256);

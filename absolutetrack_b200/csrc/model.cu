@@ -160,7 +160,7 @@ namespace abt {
 // tcgen05 path (conv_tc.cu)
 int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* crops, int crop_dtype, int c,
                          float* features, void* workspace, int64_t workspace_bytes, int fmt, int prepared_c,
-                         int32_t* status, cudaStream_t release_stream, cudaStream_t s);
+                         int32_t* status, cudaStream_t front_stream, cudaStream_t release_stream, cudaStream_t s);
 int64_t encoder_workspace_bytes_bf16(int c);
 int encoder_chunk_crops();
 }  // namespace abt
@@ -192,8 +192,17 @@ extern "C" int at_encoder_forward_release(const float* blob, const void* bf16_bl
                                           int c, float* features, void* workspace, int64_t workspace_bytes,
                                           int precision, int prepared_chunk, int32_t* status, void* release_stream,
                                           void* stream) {
+  return at_encoder_forward_front(blob, bf16_blob, crops, crop_dtype, c, features, workspace, workspace_bytes, precision,
+                                  prepared_chunk, status, nullptr, release_stream, stream);
+}
+
+extern "C" int at_encoder_forward_front(const float* blob, const void* bf16_blob, const void* crops, int crop_dtype,
+                                        int c, float* features, void* workspace, int64_t workspace_bytes,
+                                        int precision, int prepared_chunk, int32_t* status, void* front_stream,
+                                        void* release_stream, void* stream) {
   AT_REQUIRE(c >= 0, "at_encoder_forward: c < 0");
   if (c == 0) return AT_OK;
+  if (front_stream == stream) front_stream = nullptr;
   AT_REQUIRE(blob && crops && features && workspace, "at_encoder_forward: NULL pointer");
   AT_REQUIRE(crop_dtype == AT_U8 || crop_dtype == AT_F32, "at_encoder_forward: crops must be AT_U8 or AT_F32");
   AT_REQUIRE(c <= 200000, "at_encoder_forward: at most 200000 crops per call");
@@ -203,6 +212,14 @@ extern "C" int at_encoder_forward_release(const float* blob, const void* bf16_bl
     return AT_ERR_WORKSPACE_TOO_SMALL;
   }
   if (precision == AT_PREC_FP32) {
+    if (front_stream != nullptr) {  // no split on this path: the encoder stream waits for the crops' producer
+      cudaEvent_t e;
+      if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess || cudaEventRecord(e, (cudaStream_t)front_stream) != cudaSuccess ||
+          cudaStreamWaitEvent((cudaStream_t)stream, e, 0) != cudaSuccess || cudaEventDestroy(e) != cudaSuccess) {
+        abt::set_error("at_encoder_forward_front: %s", cudaGetErrorString(cudaGetLastError()));
+        return AT_ERR_CUDA;
+      }
+    }
     const int rc = abt::encoder_forward_f32(blob, crops, crop_dtype, c, features, workspace, (cudaStream_t)stream);
     if (rc == AT_OK && release_stream != nullptr) {  // no mid-encoder point on this path: release behind the whole encoder
       cudaEvent_t e;
@@ -217,8 +234,8 @@ extern "C" int at_encoder_forward_release(const float* blob, const void* bf16_bl
   if (precision == AT_PREC_BF16 || precision == AT_PREC_FP16) {
     AT_REQUIRE(bf16_blob != nullptr, "at_encoder_forward: the prepacked 16-bit blob is required for AT_PREC_BF16/FP16");
     return abt::encoder_forward_bf16(blob, bf16_blob, crops, crop_dtype, c, features, workspace, workspace_bytes,
-                                    precision == AT_PREC_BF16 ? 1 : 0, prepared_chunk, status, (cudaStream_t)release_stream,
-                                    (cudaStream_t)stream);
+                                    precision == AT_PREC_BF16 ? 1 : 0, prepared_chunk, status, (cudaStream_t)front_stream,
+                                    (cudaStream_t)release_stream, (cudaStream_t)stream);
   }
   abt::set_error("at_encoder_forward: bad precision %d", precision);
   return AT_ERR_INVALID_ARGUMENT;

@@ -83,6 +83,7 @@ class UmeTrackModel(nn.Module):
         self._status: Optional[torch.Tensor] = None
         self.memory_capacity_hint: Optional[int] = None  # callers that know max(memory_idx)+1 avoid a sync
         self.release_stream = None  # torch.cuda.Stream made to wait until each encoder call is under way (at_encoder_forward_release)
+        self.front_stream = None    # torch.cuda.Stream the crops of the NEXT encode() call were produced on (at_encoder_forward_front)
         self.strict = True  # read the device status flag after every call (one sync, like the reference's .cpu())
         self.eval()
 
@@ -185,11 +186,12 @@ class UmeTrackModel(nn.Module):
         self._enc_prepared = None
         with torch.cuda.device(dev):
             rel = self.release_stream.cuda_stream if self.release_stream is not None else None
-            rc = lib.at_encoder_forward_release(
+            front = self.front_stream.cuda_stream if self.front_stream is not None else None
+            rc = lib.at_encoder_forward_front(
                 self._blob.data_ptr(), _cabi.ptr(bf), crops.data_ptr(), dt, c, feats.data_ptr(), ws.data_ptr(),
-                ws.numel(), prec, prepared, self._status_word(dev).data_ptr(), rel, _cabi.stream_ptr(dev),
+                ws.numel(), prec, prepared, self._status_word(dev).data_ptr(), front, rel, _cabi.stream_ptr(dev),
             )
-        _cabi.check(rc, "at_encoder_forward_release")
+        _cabi.check(rc, "at_encoder_forward_front")
         if c > 0:
             chunk = lib.at_encoder_chunk_crops()
             self._enc_prepared = (key, c % chunk if c % chunk else min(c, chunk))

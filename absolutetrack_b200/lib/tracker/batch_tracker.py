@@ -149,28 +149,57 @@ class BatchedHandTracker:
         self._stage_free = [None, None]
         self._slot = 0
         self._crops_done = None
+        # Front stream: the resampler and the encoder's stem of step i+1 (ordinary grids, 8 % of a step) run there, NEXT TO
+        # the tail of step i on the main stream (18 small latency-bound launches, 14 % of a step) instead of behind it;
+        # the main stream joins before layer 1 (at_encoder_forward_front).  Opt-in (AT_FRONT_OVERLAP=1): measured on B200 the
+        # overlap happens but buys nothing - the tail stretches from 0.34 to 0.54 ms while the resampler and the stem share
+        # the SMs with it (profiles/r2_front_stream_overlap_trace.txt), so the default keeps everything on one stream.
+        self._front = torch.cuda.Stream(device=self._device) if os.environ.get("AT_FRONT_OVERLAP", "0") == "1" else None
+        self._enc_done = None   # main-stream event behind the previous step's encoder (its level-0 planes and crops are free)
 
     @property
     def device(self):
         return self._device
 
-    def step_device(self, b: FrameBatch) -> BatchResult:
-        """All inputs already on the device."""
+    def step_device(self, b: FrameBatch, inputs_ready="current") -> BatchResult:
+        """All inputs already on the device.  `inputs_ready` says when `b.frames` / `b.crop_params` are complete, for the
+        front stream (the resampler runs there): "current" (default) = produced by work queued on the current stream
+        up to this call (safe, but the resampler then also waits for the previous step's tail: no overlap); a
+        torch.cuda.Event = after that event; None = already complete (resident inputs, e.g. a replayed recording)."""
         S, H, V, W = b.frames.shape
-        crops = crop_resample_cuda(
-            b.frames, H * V * W, W, V * W, b.crop_params, (96, 96), self._crop_dtype, self._map_mode,
-            staged_bytes=None if b.frames.is_cuda else self.pulled_bytes,
-        )
-        # the next step's ingest kernel is released after this point: the resampler runs with its own
-        # (L1-heavy) shared-memory configuration and must not meet resident ingest CTAs
-        if not self._release_in_encoder:
-            self._crops_done = torch.cuda.Event()
-            self._crops_done.record()
-        out = self._model.regress_pose_use_skeleton(
-            InputFrameData(crops, b.intrinsics, b.extrinsics),
-            InputFrameDesc(b.sample_range, b.memory_idx, b.use_memory, b.hand_idx),
-            self._skel,
-        )
+        cur = torch.cuda.current_stream(self._device)
+        front = self._front
+        if front is not None:
+            if isinstance(inputs_ready, str):
+                front.wait_stream(cur)
+            else:
+                if inputs_ready is not None:
+                    front.wait_event(inputs_ready)
+                if self._enc_done is not None:
+                    front.wait_event(self._enc_done)
+                else:
+                    front.wait_stream(cur)
+        with torch.cuda.stream(front if front is not None else cur):
+            crops = crop_resample_cuda(
+                b.frames, H * V * W, W, V * W, b.crop_params, (96, 96), self._crop_dtype, self._map_mode,
+                staged_bytes=None if b.frames.is_cuda else self.pulled_bytes,
+            )
+            # the next step's ingest kernel is released after this point: the resampler runs with its own
+            # (L1-heavy) shared-memory configuration and must not meet resident ingest CTAs
+            if not self._release_in_encoder:
+                self._crops_done = torch.cuda.Event()
+                self._crops_done.record()
+        self._model.front_stream = front
+        try:
+            feats = self._model.encode(crops)
+        finally:
+            self._model.front_stream = None
+        if front is not None:
+            self._enc_done = torch.cuda.Event()
+            self._enc_done.record(cur)
+        out = self._model.tail(
+            feats, InputFrameData(None, b.intrinsics, b.extrinsics),
+            InputFrameDesc(b.sample_range, b.memory_idx, b.use_memory, b.hand_idx), self._skel, _cabi.AT_HEAD_KNOWN_SKELETON)
         # metres -> millimetres on the wrist translations (tracker.py:379) inside the FK launch.
         # The model already mirrored right hands (umetrack_model.py:88-89); landmarks_from_hand_pose
         # mirrors them back before FK (perspective_crop.py:46-48) -> hand_idx does that in-kernel
@@ -220,7 +249,7 @@ class BatchedHandTracker:
             ready.record(cs)
         cur.wait_event(ready)
         if ev: ev[2].record(cur)
-        r = self.step_device(st)
+        r = self.step_device(st, inputs_ready=ready)
         return self._finish(slot, r, ev, out_host)
 
     def _finish(self, slot, r: BatchResult, ev, out_host):
@@ -312,7 +341,7 @@ class BatchedHandTracker:
         cur.wait_event(ready)
         if ev: ev[2].record(cur)
         r = self.step_device(FrameBatch(st["frames"], ci.crop_params, ci.intrinsics, ci.extrinsics, ci.sample_range,
-                                        ci.hand_idx, ci.memory_idx, ci.use_memory))
+                                        ci.hand_idx, ci.memory_idx, ci.use_memory), inputs_ready=ready)
         r.memory_idx = ci.memory_idx
         if out_host is None:
             out_host = {

@@ -349,6 +349,19 @@ int at_encoder_forward_release(const float* blob, const void* bf16_blob, const v
                                int c, float* features, void* workspace, int64_t workspace_bytes,
                                int precision, int prepared_chunk, int32_t* status, void* release_stream, void* stream);
 
+/* Same call, plus a FRONT stream (may be NULL): the stream on which the caller produced `crops` (at_crop_resample_* of
+ * this step).  The 16-bit path launches the stem of the first chunk there as well and makes `stream` wait for it before
+ * layer1.0.conv1, so that the resampler and the stem - ordinary grids, 8 % of a step - run NEXT TO whatever `stream`
+ * still has queued ahead of this call instead of behind it.  BatchedHandTracker queues the previous step's tail (18 small
+ * latency-bound launches, 14 % of a step) on `stream` and the next step's resampler + stem on the front stream.  The caller
+ * orders the front stream after the previous encoder call (the stem overwrites the level-0 planes) and after the
+ * producer of the frames; a call that has to prepare the workspace, later chunks, and the fp32 path do not split:
+ * there `stream` simply waits for the front stream.  No counterpart in the reference (tracker.py:315-368 runs serially). */
+int at_encoder_forward_front(const float* blob, const void* bf16_blob, const void* crops, int crop_dtype,
+                             int c, float* features, void* workspace, int64_t workspace_bytes,
+                             int precision, int prepared_chunk, int32_t* status, void* front_stream,
+                             void* release_stream, void* stream);
+
 /* Test/debug entry: ONE backbone conv layer (layer_id from at_model_layer_table, 1..28) through the
  * tcgen05 path on float32 NHWC tensors: in [n,H,W,cin] -> out [n,H/stride,W/stride,cout], optional
  * residual res [n,H/stride,W/stride,cout], optional ReLU.  mt = 128-pixel sub-tiles per CTA tile (0 = default). */

@@ -3,7 +3,6 @@
 mkdir -p gpurun_out; out=gpurun_out/sub_experiments.log; : > $out
 run() { echo "== $*" >> $out; env "$@" timeout 300 python scripts/encoder_ab.py >> $out 2>gpurun_out/sub.err || { echo "FAILED" >> $out; tail -3 gpurun_out/sub.err >> $out; }; }
 run AT_TC_SUB=0
-for lv in 1 2; do for sub in 128 256 512 1024; do run AT_TC_SUB=$sub AT_TC_SUB_LEVELS=$lv; done; done
-run AT_TC_SUB=256 AT_TC_SUB_LEVELS=3
+for sub in 256 512 1024; do run AT_TC_SUB=$sub AT_TC_SUB_LEVELS=1; done
 run AT_TC_SUB=0
 cat $out

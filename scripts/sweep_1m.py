@@ -102,7 +102,7 @@ def main():
                 if t == 0:  # first frame of every sequence: no temporal memory (temporal.py:59-63)
                     b = FrameBatch(b.frames, b.crop_params, b.intrinsics, b.extrinsics, b.sample_range, b.hand_idx, b.memory_idx, firsts[gi])
                 if on_device:
-                    r = tracker.step_device(b)
+                    r = tracker.step_device(b, inputs_ready=None)
                     accumulate_metric_sums_cuda(r.landmarks, gts[gi][t % K], sums)
                 else:
                     out_host[gi] = tracker.step(b, out_host[gi])

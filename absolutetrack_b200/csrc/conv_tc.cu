@@ -46,6 +46,14 @@ constexpr int kThreads = 384;
 constexpr int kMaxRegs = 160;
 constexpr int kMaxTaps = 9;
 constexpr int kSmemBudget = 220 * 1024;
+constexpr int kS2dC = 64;                                  // channels of the x-space-to-depth view of layer 1
+// S2D weight blocks, compact: the centre taps (di = 0) as [8][64][8] (8 KB), the side taps only with the four K groups
+// they use ([4][64][8], 4 KB: K groups 4-7 for di = -1, 0-3 for di = +1) - in 4 KB units tap t starts at kS2dUnit[t]
+constexpr int64_t kS2dUnitBytes = 4096;
+constexpr int kS2dUnits = 12;
+constexpr int64_t kS2dMainBytes = kS2dUnits * kS2dUnitBytes;
+constexpr int64_t kS2dIdBytes = kS2dC * kS2dC * 2;
+
 
 // q = n / d for the bounded n of this kernel: q = umulhi(n, magic) >> shift (host: make_divider)
 struct Divider {
@@ -193,7 +201,14 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
       const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(p.w);
       const int nmain = nk * NTAPS;
       const int nblocks = nmain + p.sc_nk;  // the shortcut blocks follow the main ones at the same stride
-      if (WRES) {
+      if (S2D) {  // compact blocks, loaded as 4 KB units (12 + 2 for the identity)
+        if (n_my > 0)
+          for (int u = 0; u < kS2dUnits + 2 * p.sc_nk; ++u) {
+            mbar_expect_tx(w_full + 8 * u, (uint32_t)kS2dUnitBytes);
+            bulk_g2s(sbase + p.smem_w_off + u * (uint32_t)kS2dUnitBytes, wsrc + (size_t)u * kS2dUnitBytes, (uint32_t)kS2dUnitBytes,
+                     w_full + 8 * u);
+          }
+      } else if (WRES) {
         if (n_my > 0)
           for (int b = 0; b < nblocks; ++b) {
             const uint32_t bytes = b < nmain ? p.w_block_bytes : p.sc_w_bytes;
@@ -255,7 +270,7 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
         const uint32_t acc0 = kci != 0;
         if (WRES) {
           if (it == 0) {
-            for (int t = 0; t < NTAPS; ++t) mbar_wait(w_full + 8 * (kci * NTAPS + t), 0);
+            for (int t = 0; t < (S2D ? kS2dUnits : NTAPS); ++t) mbar_wait(w_full + 8 * (kci * NTAPS + t), 0);
             tc_fence_after();
           }
           if (elect_one()) {
@@ -269,7 +284,11 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
               for (int j = 0; j < KSTEPS; ++j) {
                 if (S2D && ((di < 0 && j < 2) || (di > 0 && j >= 2))) continue;   // structural zeros
                 const uint32_t nsh = (S2D && di > 0) ? 32u : 0u;                     // output columns / B rows of this tap
-                const uint64_t bd = ((uint64_t)desc_hi << 32) | (b_lo + (t * KSTEPS + j) * b_kstep16 + nsh);
+                // B block of (tap, K step): dense blocks at a uniform stride, or the compact S2D units
+                const uint32_t boff = S2D ? (uint32_t)((t / 3 * 4 + (di < 0 ? 0 : (di > 0 ? 3 : 1))) * (kS2dUnitBytes / 16)) +
+                                                (uint32_t)(j - (di < 0 ? 2 : 0)) * b_kstep16
+                                          : (uint32_t)(t * KSTEPS + j) * b_kstep16;
+                const uint64_t bd = ((uint64_t)desc_hi << 32) | (b_lo + boff + nsh);
 #pragma unroll
                 for (int m = 0; m < MT; ++m) {
                   const uint64_t ad = ((uint64_t)desc_hi << 32) | (a_lo + tap_off[t] + j * a_kstep16 + m * kTileM);
@@ -318,7 +337,14 @@ __global__ void __maxnreg__(kMaxRegs) conv_tc_kernel(const __grid_constant__ Con
         tc_fence_after();
         const uint32_t a_lo = a_lo0 + ra.slot * a_slot16 + (uint32_t)(-p.min_shift);
         uint32_t b_lo;
-        if (WRES) {
+        if (S2D) {
+          if (it == 0) {
+            mbar_wait(w_full + 8 * kS2dUnits, 0);
+            mbar_wait(w_full + 8 * (kS2dUnits + 1), 0);
+            tc_fence_after();
+          }
+          b_lo = b_lo0 + (uint32_t)(kS2dMainBytes / 16);
+        } else if (WRES) {
           if (it == 0) {
             mbar_wait(w_full + 8 * (nk * NTAPS + sc), 0);
             tc_fence_after();
@@ -667,9 +693,6 @@ struct TcLayer {
   int n_pad, kc, nk;
   int64_t s2d_offset;  // layer 1 only: the same conv as 64 -> 64 blocks over the x-space-to-depth view (-1: none)
 };
-constexpr int kS2dC = 64;                                  // channels of the x-space-to-depth view of layer 1
-constexpr int64_t kS2dMainBytes = 9 * kS2dC * kS2dC * 2;   // nine dense [8][64][8] blocks (structural zeros included)
-constexpr int64_t kS2dIdBytes = kS2dC * kS2dC * 2;
 bool is_s2d_layer_host(int i) { return i >= L_LAYER1 && i < L_LAYER1 + 4; }
 TcLayer g_tc[L_COUNT];
 int64_t g_tc_bytes = 0;
@@ -737,12 +760,13 @@ __global__ void prepack_identity_kernel(uint16_t* __restrict__ out, int c, int n
 // W[dy][dx] with dx = 2 di + pi - po when that is a tap of the 3x3 kernel and zero otherwise.
 __global__ void prepack_s2d_kernel(const float* __restrict__ w, uint16_t* __restrict__ out, int coutP, int fmt) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= 9 * kS2dC * kS2dC) return;
-  const int e = i & 7;
-  int r = i >> 3;
-  const int nn = r % kS2dC; r /= kS2dC;
-  const int kk = r % (kS2dC / 8);
-  const int t = r / (kS2dC / 8);
+  if (i >= (int)(kS2dMainBytes / 2)) return;
+  const int unit = i / 2048;                       // 2048 elements per 4 KB unit
+  const int row3 = unit / 4, u3 = unit % 4;        // a kernel row (dy) is 4 units: di = -1 | di = 0 (two) | di = +1
+  const int t = row3 * 3 + (u3 == 0 ? 0 : (u3 == 3 ? 2 : 1));
+  const int loc = i - (row3 * 4 + (u3 == 0 ? 0 : (u3 == 3 ? 3 : 1))) * 2048;   // element inside the tap's block
+  const int e = loc & 7, nn = (loc >> 3) % kS2dC;
+  const int kk = loc / (kS2dC * 8) + (t % 3 == 0 ? 4 : 0);   // di = -1 stores K groups 4-7
   const int cip = kk * 8 + e, pi = cip >> 5, ci = cip & 31, po = nn >> 5, co = nn & 31;
   const int dy = t / 3, dx = 2 * (t % 3 - 1) + pi - po;
   const float v = (dx >= -1 && dx <= 1) ? w[((long long)(dy * 3 + dx + 1) * 32 + ci) * coutP + co] : 0.f;
@@ -1251,7 +1275,8 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
         (io.out_mode == 0 || io.out_mode == 1) && p.cout == p.n)
       return launch_conv_tc2(p, L.name, OL, io.out_mode, mt, max_shift, stream);
   }
-  const int nblocks = p.n_kchunks * taps + p.sc_nk;
+  // resident weight blocks (S2D: 4 KB units, 12 for the nine compact tap blocks + 2 for the identity)
+  const int nblocks = io.s2d ? kS2dUnits + 2 * p.sc_nk : p.n_kchunks * taps + p.sc_nk;
   const int64_t misc = 4096;
   int64_t w_bytes = 0, ra = 0;
   for (;; mt >>= 1) {
@@ -1259,7 +1284,7 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
     p.npix = (int)round_up(kTileM * mt + max_shift - p.min_shift, 8);
     p.a_plane_bytes = (uint32_t)p.npix * 16u;
     p.a_slot_bytes = (uint32_t)(is_stem ? 1 : p.n_src * (p.kc / 8)) * p.a_plane_bytes;
-    p.w_block_bytes = (uint32_t)(p.kc * p.n * 2);
+    p.w_block_bytes = io.s2d ? (uint32_t)kS2dUnitBytes : (uint32_t)(p.kc * p.n * 2);
     p.sc_a_bytes = (uint32_t)p.sc_planes * p.a_plane_bytes;
     p.w_resident = (int64_t)nblocks * p.w_block_bytes <= 100 * 1024;
     p.ws = p.w_resident ? nblocks : 4;
@@ -1280,6 +1305,10 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
   while (cols < p.as * p.acc_cols) cols <<= 1;
   p.tmem_cols = cols;
   if (ra > 8) ra = 8;
+  {
+    static const int ra_max = getenv("AT_TC_RA_MAX") != nullptr ? atoi(getenv("AT_TC_RA_MAX")) : 8;   // A/B knob: ring depth cap
+    if (ra > ra_max && ra_max >= 2) ra = ra_max;
+  }
   if (ra < 2) {
     set_error("conv_tc: layer %s does not fit shared memory (a_slot %u B, weights %lld B)", L.name, p.a_slot_bytes,
               (long long)w_bytes);
@@ -1792,7 +1821,7 @@ extern "C" int at_model_prepack_tc(const float* blob, void* tc_blob, int precisi
     }
     if (TT[i].s2d_offset >= 0) {  // layer 1: the x-space-to-depth form (+ its 64 x 64 identity block)
       uint16_t* dst = reinterpret_cast<uint16_t*>(reinterpret_cast<uint8_t*>(tc_blob) + TT[i].s2d_offset);
-      tc::prepack_s2d_kernel<<<(9 * tc::kS2dC * tc::kS2dC + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+      tc::prepack_s2d_kernel<<<(unsigned)((tc::kS2dMainBytes / 2 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
           blob + T[i].weight_offset, dst, (int)round_up(T[i].cout, 4), precision == AT_PREC_BF16 ? 1 : 0);
       if ((rc = check_launch("prepack_s2d_kernel"))) return rc;
       if (tc::is_identity_host(i)) {

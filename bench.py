@@ -36,7 +36,7 @@ CROP_SRC_BYTES = 32_160                        # mean source bounding box per cr
 # dram__bytes_read.sum + dram__bytes_write.sum over the 25 conv_tc launches of ONE encoder pass for 2048 crops in the ncu --set full
 # capture profiles/r2_conv_tc_ncu_full_summary.csv (7614 MB = the activations read + written once) + the stem kernel's
 # algorithmic bytes (crops read, level-0 planes written: 334 MB; it was not part of that capture)
-ENCODER_DRAM_BYTES_PER_CROP = (7614045184 + 333578240) / 2048
+ENCODER_DRAM_BYTES_PER_CROP = 7961068032 / 2048   # dram read + write of the stem + 25 conv launches of one 2048-crop pass
 
 
 def load_peaks():
@@ -533,7 +533,7 @@ def main():
                          "achieved": enc_tflops, "peak": tf_peak, "unit": "TFLOP/s", "frac": enc_tflops / tf_peak,
                          "traffic": ENCODER_DRAM_BYTES_PER_CROP * c,
                          "traffic_source": "bytes per encoder pass (all conv launches), scaled per crop from the ncu --set full "
-                                           "capture in profiles/r2_conv_tc_ncu_full_summary.csv (+ the stem kernel's algorithmic bytes)",
+                                           "capture in profiles/r2_conv_tc_s2d_ncu_full_summary.csv (stem_mma + the 25 backbone conv launches)",
                          "peak_source": peaks["src"] + " cuBLAS bf16 burst (MEASURED_PEAKS.json bf16_tflops)",
                          "frac_of_sustained_peak": enc_tflops / peaks["tf_sust"],
                          "launches_per_step": enc_launches // max(1, args.steps)},

@@ -5,6 +5,8 @@
 #   scripts/gpu_run.sh launches              ncu launch list of a short bench run -> gpurun_out/launches.csv
 #   scripts/gpu_run.sh ncu <regex> <n>       ncu --set full of kernels matching <regex> (n launches) during a short bench
 #   scripts/gpu_run.sh py <script> ...       python <script> ...    -> gpurun_out/<script>.log
+#   scripts/gpu_run.sh ab <name> "<cmd>" "<ENV=..>" ...   the same command once per environment setting, back to back on
+#                                            one box -> gpurun_out/<name>.log  (A/B experiments; "" = default environment)
 # Everything it writes goes to gpurun_out/ (merged back by gpurun).
 set -u
 cd "$(dirname "$0")/.."
@@ -27,5 +29,14 @@ case "$what" in
   py)
     script=$1; shift
     python "$script" "$@" > "gpurun_out/$(basename "$script" .py).log" 2>&1; echo "exit $?"; tail -n 40 "gpurun_out/$(basename "$script" .py).log" ;;
+  ab)
+    name=$1; cmd=$2; shift 2
+    out=gpurun_out/$name.log; : > "$out"
+    for setting in "$@"; do
+      echo "== ${setting:-(default)}" >> "$out"
+      # shellcheck disable=SC2086
+      env $setting timeout 600 $cmd >> "$out" 2> gpurun_out/$name.err || { echo "FAILED" >> "$out"; tail -n 5 gpurun_out/$name.err >> "$out"; }
+    done
+    cut -c1-400 "$out" ;;
   *) echo "unknown mode $what"; exit 2 ;;
 esac

@@ -7,7 +7,7 @@ absolutetrack_b200/lib, the un-mirrored plumbing (`lib.data_utils.fs`, ...) to t
 
 usage: script_driver.py known   <rec.mp4> <out.npy> <ckpt>
        script_driver.py unknown <rec.mp4> <out.npy> <ckpt> <generic_hand_model.json> <n_calibration_samples>
-       script_driver.py evalbatch <torchdata dir> <out.npz> <ckpt> <batch>
+       script_driver.py evalbatch <torchdata dir> <out.npz> <ckpt> <batch> [time]
 """
 import os
 import sys
@@ -66,6 +66,31 @@ def main():
                 err = R._eval_batch(model, model_input, model_target, "multiv", use_skel=use_skel, device="cuda")
                 out[name] = err.cpu().numpy()
         np.savez(sys.argv[3], **out)
+        if len(sys.argv) > 6 and sys.argv[6] == "time":   # scripts/config3_throughput.py: the same calls, timed
+            import json
+            import time
+
+            T = int(model_input.left_images.shape[1])   # [batch, frames, views, 96, 96]
+            reps = 5
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                batch = [preprocess(batch_sample(mono, labels, i), (96, 96)) for i in range(bs)]
+                model_input, model_target = bundles.collate(batch)
+            torch.cuda.synchronize()
+            t_pre = (time.perf_counter() - t0) / reps
+            times = {}
+            with torch.inference_mode():
+                for name, use_skel in (("known_skeleton", True), ("predict_scale", False)):
+                    R._eval_batch(model, model_input, model_target, "multiv", use_skel=use_skel, device="cuda")
+                    torch.cuda.synchronize()
+                    t0 = time.perf_counter()
+                    for _ in range(reps):
+                        R._eval_batch(model, model_input, model_target, "multiv", use_skel=use_skel, device="cuda")
+                    torch.cuda.synchronize()
+                    times[name] = (time.perf_counter() - t0) / reps
+            shapes = {k: list(v.shape) for k, v in vars(model_input).items() if hasattr(v, "shape")} if hasattr(model_input, "__dict__") else {}
+            print("timing " + json.dumps({"batch": bs, "frames_per_sequence": T, "preprocess_collate_s": t_pre,
+                                          "eval_batch_s": times, "input_shapes": shapes}))
     else:
         raise SystemExit(f"unknown mode {mode}")
     from absolutetrack_b200 import _cabi

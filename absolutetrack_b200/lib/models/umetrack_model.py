@@ -28,7 +28,8 @@ class InputFrameData:
 
 @dataclass
 class InputFrameDesc:
-    """sample_range [bs,2], memory_idx [bs], use_memory [bs] bool, hand_idx [bs]."""
+    """sample_range [bs,2], memory_idx [bs], use_memory [bs] bool, hand_idx [bs].  memory_idx values must be
+    distinct within a batch (samples sharing a temporal-memory slot race on it; the reference is last-write-wins)."""
 
     sample_range: torch.Tensor
     memory_idx: torch.Tensor

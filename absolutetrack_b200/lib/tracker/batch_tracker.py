@@ -134,6 +134,7 @@ class BatchedHandTracker:
         self.pulled_bytes = torch.zeros(1, dtype=torch.int64, device=self._device)  # bytes the resampler pulled from host frames
         self.pull_ctas = 0  # CTAs of the pull kernel (0 = one per SM)
         self.trace = None   # debug: a list -> step() appends (ingest start, ingest end, compute start, compute end) events
+        self.encoder_events = None   # measurement: a list -> step_device() appends (start, end) timing events around the encoder
         # high priority: the ingest kernels are tiny and must not queue behind the encoder's CTAs
         # The ingest stream is released from INSIDE the encoder (at_encoder_forward_release: the copy stream waits until
         # layer1.0.conv1 of the current step has been launched and finished).  Released at a kernel boundary (behind the
@@ -190,10 +191,17 @@ class BatchedHandTracker:
                 self._crops_done = torch.cuda.Event()
                 self._crops_done.record()
         self._model.front_stream = front
+        enc_ev = None
+        if self.encoder_events is not None and front is None:
+            enc_ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            enc_ev[0].record(cur)
         try:
             feats = self._model.encode(crops)
         finally:
             self._model.front_stream = None
+        if enc_ev is not None:
+            enc_ev[1].record(cur)
+            self.encoder_events.append(enc_ev)
         if front is not None:
             self._enc_done = torch.cuda.Event()
             self._enc_done.record(cur)

@@ -385,7 +385,8 @@ typedef struct AtTailInputs {
   const float* intrinsics;     /* [c,3,3] */
   const float* extrinsics;     /* [c,4,4] world->crop-eye, metres */
   const int64_t* sample_range; /* [n,2] (start,end) into the c crops; end-start in {1,2} */
-  const int64_t* memory_idx;   /* [n] */
+  const int64_t* memory_idx;   /* [n]; values must be distinct within a call: two samples sharing a slot race on it
+                                * (the reference, temporal.py:77,134, is last-write-wins; trackers give every (sequence, hand) its own slot) */
   const uint8_t* use_memory;   /* [n] bool */
   const int64_t* hand_idx;     /* [n] */
   const float* skel_axes;      /* [1 or n,22,3]  (NULL for AT_HEAD_PREDICT_SCALE) */

@@ -121,6 +121,116 @@ __global__ void __launch_bounds__(kBlock) fk_skin_kernel(const float* __restrict
 
 
 // ------------------------------------------------------------------------------------------
+// Per-sample hand models (config 3: every sample brings its own skeleton, 1,284 B of model per hand next to 404 B
+// of pose in / landmarks out): one WARP per hand.  With one thread per hand (fk_skin_kernel) each thread walks its
+// own 1.3 KB of model with 4-byte loads 1.3 KB apart from its neighbour's - 0.11 of HBM.  Here lane j < 20 loads
+// joint j (axis, rest position, angle: the warp's loads are contiguous) and builds its local transform (MUFU rsqrt /
+// sin / cos as in the shared-model path), so the 20 Rodrigues formulas of a hand run in parallel; the chain products
+// T_0 ... T_i of every finger are a two-round prefix scan over its four lanes (shuffles), then one product with the
+// wrist; lane l < 21 skins landmark l, fetching the frames of its bones from the lanes that hold them, and stores its
+// three coordinates (252 contiguous bytes per warp).  No shared memory.  (Products are associated differently from
+// hand_skinning.py:35-53's left-to-right loop: ~1e-4 mm at most, tests/test_gpu_kernels.py bounds it at 1e-3 mm.)
+constexpr int kWarpFkThreads = 256;
+
+__device__ __forceinline__ void shfl_xf(const Xf& v, int src, Xf& o) {
+#pragma unroll
+  for (int e = 0; e < 9; ++e) o.r[e] = __shfl_sync(0xffffffffu, v.r[e], src);
+#pragma unroll
+  for (int e = 0; e < 3; ++e) o.t[e] = __shfl_sync(0xffffffffu, v.t[e], src);
+}
+
+template <int KMAX>   // upper bound of n_weights the loops are unrolled for (4: the usual 3-weight models; 8: the maximum)
+__global__ void __launch_bounds__(kWarpFkThreads, 4) fk_skin_warp_kernel(const float* __restrict__ joint_angles,
+                                                                         const float* __restrict__ wrist,
+                                                                         const int64_t* __restrict__ hand_idx, AtHandModel m,
+                                                                         int64_t n, float* __restrict__ landmarks, float tscale,
+                                                                         float* __restrict__ wrist_out) {
+  const int lane = threadIdx.x & 31;
+  const int64_t nwarps = (int64_t)gridDim.x * (kWarpFkThreads / 32);
+  const int K = m.n_weights;
+  const int pos = lane & 3;  // position of joint `lane` in its finger chain
+  for (int64_t h = (int64_t)blockIdx.x * (kWarpFkThreads / 32) + (threadIdx.x >> 5); h < n; h += nwarps) {
+    const int64_t hm = m.per_sample ? h : 0;
+    const float* wp = wrist + h * 16;
+    Xf W;
+    const float sgn = (hand_idx != nullptr && hand_idx[h] == 1) ? -1.0f : 1.0f;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      W.r[i * 3 + 0] = sgn * wp[i * 4 + 0];
+      W.r[i * 3 + 1] = wp[i * 4 + 1];
+      W.r[i * 3 + 2] = wp[i * 4 + 2];
+      W.t[i] = wp[i * 4 + 3] * tscale;
+    }
+    if (wrist_out != nullptr && lane < 16)
+      wrist_out[h * 16 + lane] = (lane < 12 && (lane & 3) == 3) ? wp[lane] * tscale : wp[lane];
+    // everything this lane reads from global memory is requested up front (one exposed latency per hand)
+    const int l = lane < 21 ? lane : 0;
+    const float* lm = m.landmark_rest_positions + hm * 63 + 3 * l;
+    const float px = lm[0], py = lm[1], pz = lm[2];
+    const float* bw = m.landmark_rest_bone_weights + (hm * 21 + l) * K;
+    const int32_t* bi = m.landmark_rest_bone_indices + (hm * 21 + l) * K;
+    float wk[KMAX];
+    int bk[KMAX];
+#pragma unroll
+    for (int k = 0; k < KMAX; ++k) {
+      wk[k] = k < K ? bw[k] : 0.0f;
+      bk[k] = k < K ? bi[k] : 0;
+    }
+    const int j = lane < 20 ? lane : 0;
+    Xf T;
+    {
+      const float* axis = m.joint_rotation_axes + hm * 66 + 3 * j;
+      const float* rest = m.joint_rest_positions + hm * 66 + 3 * j;
+      const float angle = joint_angles[h * 22 + j];
+      const float wx = axis[0] * angle, wy = axis[1] * angle, wz = axis[2] * angle;
+      const float th2 = fmaxf(wx * wx + wy * wy + wz * wz, 1e-4f);   // so3_exp_map's clamp (hand_skinning.py:46)
+      const float inv = rsqrtf(th2);
+      float sn, cs;
+      __sincosf(th2 * inv, &sn, &cs);
+      const float f1 = inv * sn, f2 = inv * inv * (1.0f - cs);
+      T.r[0] = 1.0f - f2 * (wy * wy + wz * wz); T.r[1] = f2 * (wx * wy) - f1 * wz;        T.r[2] = f2 * (wx * wz) + f1 * wy;
+      T.r[3] = f2 * (wx * wy) + f1 * wz;        T.r[4] = 1.0f - f2 * (wx * wx + wz * wz); T.r[5] = f2 * (wy * wz) - f1 * wx;
+      T.r[6] = f2 * (wx * wz) - f1 * wy;        T.r[7] = f2 * (wy * wz) + f1 * wx;        T.r[8] = 1.0f - f2 * (wx * wx + wy * wy);
+      const float px = rest[0], py = rest[1], pz = rest[2];
+      T.t[0] = px - (T.r[0] * px + T.r[1] * py + T.r[2] * pz);
+      T.t[1] = py - (T.r[3] * px + T.r[4] * py + T.r[5] * pz);
+      T.t[2] = pz - (T.r[6] * px + T.r[7] * py + T.r[8] * pz);
+    }
+    // chains: inclusive prefix products over the four lanes of a finger, then the wrist in front
+    Xf cur, up;
+    shfl_xf(T, (lane + 31) & 31, up);
+    if (pos >= 1) compose(up, T, cur); else cur = T;
+    shfl_xf(cur, (lane + 30) & 31, up);
+    if (pos >= 2) { Xf t2; compose(up, cur, t2); cur = t2; }
+    { Xf t3; compose(W, cur, t3); cur = t3; }
+    // skinning: sum_k F[idx_k] * (w_k * [p,1])  (zero weights dropped, hand_skinning.py:92-94)
+    float ax = 0.f, ay = 0.f, az = 0.f;
+#pragma unroll
+    for (int k = 0; k < KMAX; ++k) {
+      if (k >= K) break;
+      const float w = wk[k];
+      const int b = min(max(bk[k], 0), kNumFrames - 1);
+      // frames 0, 1 = the wrist; frame 2 + 3 f + (i - 1), i = 1..3, is held by lane 4 f + i
+      const int fq = ((b - 2) * 11) >> 5;   // (b - 2) / 3 for b - 2 in [0, 14]
+      const int src = b < 2 ? lane : 4 * fq + (b - 2 - 3 * fq) + 1;
+      Xf F;
+      shfl_xf(cur, src, F);
+      if (b < 2) F = W;
+      if (w != 0.0f) {
+        const float qx = px * w, qy = py * w, qz = pz * w;
+        ax += F.r[0] * qx + F.r[1] * qy + F.r[2] * qz + F.t[0] * w;
+        ay += F.r[3] * qx + F.r[4] * qy + F.r[5] * qz + F.t[1] * w;
+        az += F.r[6] * qx + F.r[7] * qy + F.r[8] * qz + F.t[2] * w;
+      }
+    }
+    if (lane < 21) {
+      float* o = landmarks + h * 63 + 3 * lane;
+      o[0] = ax; o[1] = ay; o[2] = az;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // Shared-hand-model fast path (eval scripts, frame-stream tracker): the model is uniform across the
 // CTA, so per joint the constant parts of the Rodrigues formula are computed once per CTA:
 //   R = I + s1*K + s2*K^2,  t = p - R p = -(s1*K p + s2*K^2 p),  K = skew(axis),
@@ -556,6 +666,18 @@ extern "C" int at_fk_skin_scaled_f32(const float* joint_angles, const float* wri
     fk_skin_shared_kernel<<<(unsigned)fb, kFast, fast_smem, (cudaStream_t)stream>>>(
         joint_angles, wrist_xforms, hand_idx, *model, n, landmarks, translation_scale, wrist_out);
     return abt::check_launch("fk_skin_shared_kernel");
+  }
+  // per-sample models: one warp per hand (AT_FK_WARP=0: the one-thread-per-hand kernel, for A/B)
+  static const bool warp_fk = getenv("AT_FK_WARP") == nullptr || atoi(getenv("AT_FK_WARP")) != 0;
+  if (model->per_sample && warp_fk) {
+    const int64_t wb = std::min<int64_t>((n + kWarpFkThreads / 32 - 1) / (kWarpFkThreads / 32), 24LL * abt::kNumSMs);
+    if (model->n_weights <= 4)
+      fk_skin_warp_kernel<4><<<(unsigned)wb, kWarpFkThreads, 0, (cudaStream_t)stream>>>(joint_angles, wrist_xforms, hand_idx, *model, n,
+                                                                                      landmarks, translation_scale, wrist_out);
+    else
+      fk_skin_warp_kernel<8><<<(unsigned)wb, kWarpFkThreads, 0, (cudaStream_t)stream>>>(joint_angles, wrist_xforms, hand_idx, *model, n,
+                                                                                      landmarks, translation_scale, wrist_out);
+    return abt::check_launch("fk_skin_warp_kernel");
   }
   const int64_t blocks = (n + kBlock - 1) / kBlock;
   AT_REQUIRE(blocks <= 0x7fffffffLL, "at_fk_skin_f32: n too large");

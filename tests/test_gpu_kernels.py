@@ -541,3 +541,46 @@ def test_config3_preprocess_from_torch_idx_files_matches_reference(cuda_lib, gol
         assert np.array_equal(np.asarray(mt.gt_skel_targets.skel_scales), G[p + "gt_skel_scales"])
         assert np.array_equal(mt.preds_targets.pinch_prediction.numpy(), G[p + "pinch"])
         assert mt.intrinsics is mi.intrinsics and mt.extrinsics_xf is mi.extrinsics_xf
+
+
+@pytest.mark.gpu
+def test_fk_per_sample_models_warp_kernel_five_weights(cuda_lib, gold):
+    """Per-sample hand models run one warp per hand (fk_skin_warp_kernel).  Five skinning weights per landmark
+    (the KMAX = 8 instantiation; the recordings use three) with per-sample skeleton scales, right and left hands,
+    against the numpy oracle (hand_skinning.py:56-127), and against the shared-model path for the unscaled model."""
+    from absolutetrack_b200.lib.common.hand_skinning import skin_landmarks_cuda
+
+    hm = _hand_model_tuple(gold["geometry"], "hm_")
+    rng = np.random.default_rng(21)
+    n = 777
+    w3 = hm.landmark_rest_bone_weights.numpy()
+    i3 = hm.landmark_rest_bone_indices.numpy()
+    w5 = np.zeros((21, 5), np.float32)
+    i5 = np.zeros((21, 5), i3.dtype)
+    w5[:, :3], i5[:, :3] = w3, i3
+    w5[:, 3] = 0.25 * w5[:, 0]; w5[:, 0] *= 0.75; i5[:, 3] = rng.integers(0, 17, 21)     # a fourth bone takes a share
+    w5[::2, 4] = 0.5 * w5[::2, 1]; w5[::2, 1] *= 0.5; i5[:, 4] = rng.integers(0, 17, 21)  # a fifth on every other landmark
+    scale = np.linspace(0.8, 1.25, n).astype(np.float32).reshape(n, 1, 1)
+    md = {
+        "joint_rotation_axes": np.broadcast_to(hm.joint_rotation_axes.numpy(), (n, 22, 3)).copy(),
+        "joint_rest_positions": hm.joint_rest_positions.numpy()[None] * scale,
+        "landmark_rest_positions": hm.landmark_rest_positions.numpy()[None] * scale,
+        "landmark_rest_bone_weights": np.broadcast_to(w5, (n, 21, 5)).copy(),
+        "landmark_rest_bone_indices": np.broadcast_to(i5, (n, 21, 5)).copy(),
+    }
+    ja = rng.uniform(-1.3, 1.3, (n, 22)).astype(np.float32)
+    wx = np.tile(np.eye(4, dtype=np.float32), (n, 1, 1))
+    wx[:, :3, :3] = O.so3_exp_map_f32(rng.normal(0, 1, (n, 3)).astype(np.float32))
+    wx[:, :3, 3] = rng.normal(0, 300, (n, 3))
+    ref = O.skin_landmarks(md, ja, wx)
+    per = hm._replace(**{k: torch.from_numpy(v) for k, v in md.items()})
+    out = skin_landmarks_cuda(per, torch.from_numpy(ja), torch.from_numpy(wx)).cpu().numpy()
+    assert np.abs(out - ref).max() < 1e-3
+    # three weights, unscaled, mirrored hands: the warp kernel against the shared-model kernel
+    hidx = torch.from_numpy(rng.integers(0, 2, n))
+    same = hm._replace(**{k: getattr(hm, k).expand((n,) + tuple(getattr(hm, k).shape)).contiguous() for k in
+                          ("joint_rotation_axes", "joint_rest_positions", "landmark_rest_positions",
+                           "landmark_rest_bone_weights", "landmark_rest_bone_indices")})
+    a = skin_landmarks_cuda(same, torch.from_numpy(ja), torch.from_numpy(wx), hand_idx=hidx)
+    b = skin_landmarks_cuda(hm, torch.from_numpy(ja), torch.from_numpy(wx), hand_idx=hidx)
+    assert float((a - b).abs().max()) < 5e-4

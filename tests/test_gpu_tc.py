@@ -183,3 +183,30 @@ def test_fp16_overflow_is_reported_not_silently_clamped(state_dict):
         m2 = model_from_state_dict(big, precision=prec).cuda()
         m2.encode(crops)
         m2.check_status()
+
+
+@pytest.mark.gpu
+def test_layer1_forms_agree():
+    """Layer 1 runs in its x-space-to-depth form by default (conv_tc_kernel S2D: two output pixels per accumulator
+    row); AT_TC_S2D=0 keeps the plain 32 -> 32 form.  The switch is read once per process, so each form gets its own:
+    both must sit at the same distance from the fp32 encoder (they differ by fp32 summation order only) and - being
+    different kernels over different layouts - must not be bit-identical by accident of running the same code."""
+    import json
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = {}
+    for form in ("0", "1"):
+        env = dict(os.environ, AT_TC_S2D=form)
+        r = subprocess.run([sys.executable, os.path.join(root, "scripts", "encoder_ab.py"), "--crops", "192", "--iters", "1"],
+                           env=env, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-3000:]
+        out[form] = json.loads(r.stdout.strip().splitlines()[-1])
+    e0, e1 = out["0"]["err_vs_fp32_encoder"], out["1"]["err_vs_fp32_encoder"]
+    print("plain form:", e0, " space-to-depth form:", e1)
+    assert out["0"]["features_sha1"] != out["1"]["features_sha1"]
+    for e in (e0, e1):
+        assert e["mean"] < 2.5e-4 and e["max"] < 3e-3, e      # features are O(0.2): fp16 operands, fp32 accumulation
+    assert abs(e0["mean"] - e1["mean"]) < 2e-5

@@ -10,6 +10,7 @@
 #include <stdlib.h>
 
 #include "at_common.cuh"
+#include "tc_ptx.cuh"
 
 namespace {
 
@@ -823,6 +824,122 @@ __device__ __forceinline__ uint32_t pull_word_offset(int i, int total, int wpr, 
   return (addr < row0 + bw && addr + 16u <= tb) ? addr : 0xFFFFFFFFu;
 }
 
+// Bulk-TMA variant of the pull (AT_PULL_TMA=1, A/B): the same boxes, moved as chunks of <= 256 bytes of a row by the
+// copy engine of the SM - cp.async.bulk from the pinned frames into a 6-slot shared-memory ring (mbarrier completion),
+// cp.async.bulk back out to the device buffer - issued by ONE thread; no LSU traffic, no registers holding data.
+// Up to kTmaAhead loads in flight per CTA.  The other lanes only help with the box bounds.
+constexpr int kTmaSlots = 6, kTmaAhead = 4, kTmaChunk = 256;
+
+__device__ __forceinline__ void bulk_s2g(void* dst, uint32_t src_smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src_smem), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+__global__ void __launch_bounds__(32)
+crop_pull_boxes_tma_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int64_t total_bytes,
+                           int64_t frame_stride, int64_t view_stride, int64_t row_stride,
+                           const AtCropParams* __restrict__ params, int n_crops, int dst_w, int dst_h,
+                           unsigned long long* __restrict__ pulled_bytes) {
+  __shared__ __align__(128) uint8_t ring[kTmaSlots * kTmaChunk];
+  __shared__ __align__(8) uint64_t bars[kTmaSlots];
+  __shared__ uint32_t c_addr[kTmaSlots], c_bytes[kTmaSlots];
+  __shared__ FastParams P;
+  using namespace abt::ptx;
+  const int lane = threadIdx.x;
+  const uint32_t ring_s = smem_u32(ring), bar_s = smem_u32(bars);
+  if (lane == 0) {
+    for (int i = 0; i < kTmaSlots; ++i) mbar_init(bar_s + 8 * i, 1);
+    fence_barrier_init();
+  }
+  __syncwarp();
+  uint32_t produced = 0, consumed = 0;   // chunk counters of lane 0 (slot = counter % kTmaSlots, parity = counter / kTmaSlots & 1)
+  unsigned long long my_bytes = 0ull;
+  for (int crop = blockIdx.x; crop < n_crops; crop += gridDim.x) {
+    const AtCropParams& g = params[crop];
+    __syncwarp();
+    if (lane < 9) P.M[lane] = (float)g.M[lane];
+    if (lane < 3) P.d[lane] = (float)g.d[lane];
+    if (lane == 31) {
+      P.ifdx = 1.0f / (float)g.f_dst[0]; P.ifdy = 1.0f / (float)g.f_dst[1];
+      P.qx0 = -(float)g.c_dst[0] * P.ifdx; P.qy0 = -(float)g.c_dst[1] * P.ifdy;
+      P.fsx = (float)g.f_src[0]; P.fsy = (float)g.f_src[1]; P.csx = (float)g.c_src[0]; P.csy = (float)g.c_src[1];
+      P.k1 = (float)g.k[0]; P.k2 = (float)g.k[1]; P.k3 = (float)g.k[2]; P.k4 = (float)g.k[3];
+      P.p1 = (float)g.k[4]; P.p2 = (float)g.k[5]; P.k5 = (float)g.k[6]; P.k6 = (float)g.k[7];
+    }
+    __syncwarp();
+    const int W = g.src_w, H = g.src_h;
+    float mnx = 3.0e38f, mny = 3.0e38f, mxx = -3.0e38f, mxy = -3.0e38f;
+    bool behind = false;
+    const int nb = 2 * (dst_w + dst_h);
+    for (int i = lane; i < nb; i += 32) {
+      int x, y;
+      if (i < dst_w) { x = i; y = 0; }
+      else if (i < 2 * dst_w) { x = i - dst_w; y = dst_h - 1; }
+      else if (i < 2 * dst_w + dst_h) { x = 0; y = i - 2 * dst_w; }
+      else { x = dst_w - 1; y = i - 2 * dst_w - dst_h; }
+      float wx, wy;
+      map_pixel_fast(P, fmaf((float)x, P.ifdx, P.qx0), fmaf((float)y, P.ifdy, P.qy0), wx, wy);
+      behind |= (wx == -1.0f && wy == -1.0f);
+      mnx = fminf(mnx, wx); mxx = fmaxf(mxx, wx);
+      mny = fminf(mny, wy); mxy = fmaxf(mxy, wy);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      mnx = fminf(mnx, __shfl_xor_sync(0xffffffffu, mnx, o)); mxx = fmaxf(mxx, __shfl_xor_sync(0xffffffffu, mxx, o));
+      mny = fminf(mny, __shfl_xor_sync(0xffffffffu, mny, o)); mxy = fmaxf(mxy, __shfl_xor_sync(0xffffffffu, mxy, o));
+    }
+    behind = __any_sync(0xffffffffu, behind);
+    const float lim = 1.0e6f;
+    mnx = fminf(fmaxf(mnx, -lim), lim); mxx = fminf(fmaxf(mxx, -lim), lim);
+    mny = fminf(fmaxf(mny, -lim), lim); mxy = fminf(fmaxf(mxy, -lim), lim);
+    int x0 = max(0, (int)floorf(mnx) - 2), x1 = min(W - 1, (int)floorf(mxx) + 3);   // the same box as crop_pull_boxes_kernel
+    int y0 = max(0, (int)floorf(mny) - 2), y1 = min(H - 1, (int)floorf(mxy) + 3);
+    if (behind) { x0 = 0; y0 = 0; x1 = W - 1; y1 = H - 1; }
+    const int bw = x1 - x0 + 1, bh = y1 - y0 + 1;
+    if (bw <= 0 || bh <= 0 || lane != 0) continue;
+    const uint32_t base = (uint32_t)((int64_t)g.frame * frame_stride + (int64_t)g.view * view_stride +
+                                     (int64_t)y0 * row_stride + x0);
+    const uint32_t tb = (uint32_t)total_bytes & ~15u, rs = (uint32_t)row_stride;
+    // chunk generator: rows top to bottom, each row's 16-byte-aligned span [s, e) in pieces of kTmaChunk bytes
+    int r = 0;
+    uint32_t s = base & ~15u, e = min((base + (uint32_t)bw + 15u) & ~15u, tb);
+    auto drain_one = [&]() {
+      const uint32_t slot = consumed % kTmaSlots;
+      mbar_wait(bar_s + 8 * slot, (consumed / kTmaSlots) & 1u);
+      bulk_s2g(dst + c_addr[slot], ring_s + slot * kTmaChunk, c_bytes[slot]);
+      bulk_commit();
+      ++consumed;
+    };
+    while (r < bh) {
+      if (s >= e) {   // next row
+        if (++r >= bh) break;
+        const uint32_t a = base + (uint32_t)r * rs;
+        s = a & ~15u; e = min((a + (uint32_t)bw + 15u) & ~15u, tb);
+        continue;
+      }
+      const uint32_t n = min(e - s, (uint32_t)kTmaChunk);
+      if (produced - consumed >= (uint32_t)kTmaAhead) drain_one();
+      // the slot about to be refilled was stored kTmaSlots - kTmaAhead >= 2 commits ago: all but the newest group have read it
+      bulk_wait_read<1>();
+      const uint32_t slot = produced % kTmaSlots;
+      c_addr[slot] = s; c_bytes[slot] = n;
+      mbar_expect_tx(bar_s + 8 * slot, n);
+      bulk_g2s(ring_s + slot * kTmaChunk, src + s, n, bar_s + 8 * slot);
+      ++produced;
+      my_bytes += n;
+      s += n;
+    }
+    while (consumed < produced) drain_one();
+  }
+  if (lane == 0) {
+    bulk_wait_all();
+    if (pulled_bytes != nullptr && my_bytes) atomicAdd(pulled_bytes, my_bytes);
+  }
+}
+
 template <int kPullPerLane>  // 16-byte slots per lane per stage: ring = 2 x kPullPerLane x 512 B
 __global__ void __maxnreg__(32)
 crop_pull_boxes_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int64_t total_bytes,
@@ -1050,6 +1167,13 @@ extern "C" int at_crop_pull_source_boxes_u8(const uint8_t* src, uint8_t* dst, in
   // also slows the co-running encoder a little (scripts/overlap_probe.cu), and more requests in
   // flight only make that worse -> one warp per SM, 1 KB each.  AT_PULL_DEPTH (1, 2, 4, 8) to tune.
   static const int depth = getenv("AT_PULL_DEPTH") ? atoi(getenv("AT_PULL_DEPTH")) : 1;
+  static const bool pull_tma = getenv("AT_PULL_TMA") != nullptr && atoi(getenv("AT_PULL_TMA")) != 0;
+  if (pull_tma) {
+    AT_CARVEOUT_ONCE(crop_pull_boxes_tma_kernel);
+    crop_pull_boxes_tma_kernel<<<grid, 32, 0, (cudaStream_t)stream>>>(src, dst, n_frames * frame_stride, frame_stride, view_stride,
+                                                                      row_stride, params, n_crops, dst_w, dst_h, pulled_bytes);
+    return abt::check_launch("crop_pull_boxes_tma_kernel");
+  }
 #define AT_PULL_LAUNCH(D)                                                                                         \
   do {                                                                                                            \
     AT_CARVEOUT_ONCE(crop_pull_boxes_kernel<D>);                                                                  \

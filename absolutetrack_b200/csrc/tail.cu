@@ -185,43 +185,47 @@ __global__ void __launch_bounds__(128) tail_prepare_kernel(PrepArgs a) {
   __shared__ float Xm[12];
   __shared__ int s_info[4];   // r0, nv, mem slot, use_memory
   const int i = blockIdx.x;
-  if (threadIdx.x == 0) {
-    const int64_t r0 = a.in.sample_range[2 * i], r1 = a.in.sample_range[2 * i + 1];
-    const int64_t m = a.in.memory_idx[i];
-    int nv = (int)(r1 - r0);
-    bool bad = r0 < 0 || r1 > a.in.c || nv < 1 || nv > 2 || m < 0 || m >= a.st.capacity;
-    if (bad) {
-      atomicOr(a.status, 1);  // AT_STATUS_BAD_SAMPLE_RANGE (the encoder ORs its own bit into the same word)
-      nv = 0;
-    }
-    s_info[0] = (int)r0; s_info[1] = nv; s_info[2] = (int)m; s_info[3] = bad ? 0 : (int)a.in.use_memory[i];
-    if (!bad) {
-      double E0[16], S0[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
-      load4x4(a.in.extrinsics + r0 * 16, E0);
-      S0[10] = (double)(a.in.intrinsics[r0 * 9] / 200.0f);  // compute_singlev_xfs (model_utils.py:166-192)
-      if (nv == 2) {
-        double S0i[16];
-        mat4_inv(S0, S0i);
-        for (int v = 0; v < 2; ++v) {
-          double Ev[16], Evi[16], Sv[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1}, T[16];
-          load4x4(a.in.extrinsics + (r0 + v) * 16, Ev);
-          Sv[10] = (double)(a.in.intrinsics[(r0 + v) * 9] / 200.0f);
-          mat4_inv(Ev, Evi);
-          mat4_mul(Evi, Sv, T);  // xf_to_world = inv(E_v) @ S_v
-          mat4_mul(E0, T, T);    // xf_0 @ ...
-          mat4_mul(S0i, T, T);   // s_0 @ ...
-          for (int r = 0; r < 3; ++r) {
-            for (int q = 0; q < 3; ++q) X[v][r * 3 + q] = (float)T[r * 4 + q];
-            X[v][9 + r] = (float)T[r * 4 + 3];
-          }
-        }
-      } else {  // single view: FTL by S_v only (feature_extractor.py:89-94)
-        for (int r = 0; r < 3; ++r) {
-          for (int q = 0; q < 3; ++q) X[0][r * 3 + q] = (float)S0[r * 4 + q];
-          X[0][9 + r] = 0.f;
-        }
+  // The float64 set-up (three 4x4 inverses, six products) is three independent chains - the transform of view 0, of
+  // view 1 and of the memory features; lane 0 of warps 0, 1 and 2 take one each (one thread doing all three was most of
+  // this kernel's time).  Every chain keeps its operation order, so the matrices are bit-identical to the serial version.
+  const int64_t r0 = a.in.sample_range[2 * i], r1 = a.in.sample_range[2 * i + 1];
+  const int64_t m = a.in.memory_idx[i];
+  int nv = (int)(r1 - r0);
+  const bool bad = r0 < 0 || r1 > a.in.c || nv < 1 || nv > 2 || m < 0 || m >= a.st.capacity;
+  if (bad) nv = 0;
+  const int use_memory = bad ? 0 : (int)a.in.use_memory[i];
+  const int role = (threadIdx.x & 31) == 0 ? (int)(threadIdx.x >> 5) : -1;   // 0, 1: views; 2: memory
+  if (role == 0) {
+    if (bad) atomicOr(a.status, 1);  // AT_STATUS_BAD_SAMPLE_RANGE (the encoder ORs its own bit into the same word)
+    s_info[0] = (int)r0; s_info[1] = nv; s_info[2] = (int)m; s_info[3] = use_memory;
+  }
+  if (!bad && role >= 0 && role <= 2) {
+    double E0[16], S0[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+    load4x4(a.in.extrinsics + r0 * 16, E0);
+    S0[10] = (double)(a.in.intrinsics[r0 * 9] / 200.0f);  // compute_singlev_xfs (model_utils.py:166-192)
+    if (role < 2 && nv == 2) {
+      const int v = role;
+      double S0i[16];
+      mat4_inv(S0, S0i);
+      double Ev[16], Evi[16], Sv[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1}, T[16];
+      load4x4(a.in.extrinsics + (r0 + v) * 16, Ev);
+      Sv[10] = (double)(a.in.intrinsics[(r0 + v) * 9] / 200.0f);
+      mat4_inv(Ev, Evi);
+      mat4_mul(Evi, Sv, T);  // xf_to_world = inv(E_v) @ S_v
+      mat4_mul(E0, T, T);    // xf_0 @ ...
+      mat4_mul(S0i, T, T);   // s_0 @ ...
+      for (int r = 0; r < 3; ++r) {
+        for (int q = 0; q < 3; ++q) X[v][r * 3 + q] = (float)T[r * 4 + q];
+        X[v][9 + r] = (float)T[r * 4 + 3];
       }
-      if (s_info[3]) {  // prev_cam0 -> cur_cam0 (temporal.py:69-73)
+    } else if (role == 0) {  // single view: FTL by S_v only (feature_extractor.py:89-94)
+      for (int r = 0; r < 3; ++r) {
+        for (int q = 0; q < 3; ++q) X[0][r * 3 + q] = (float)S0[r * 4 + q];
+        X[0][9 + r] = 0.f;
+      }
+    }
+    if (role == 2) {
+      if (use_memory) {  // prev_cam0 -> cur_cam0 (temporal.py:69-73)
         double P[16], Pi[16], T[16];
         load4x4(a.st.prev_extrinsics + m * 16, P);
         mat4_inv(P, Pi);
@@ -235,7 +239,7 @@ __global__ void __launch_bounds__(128) tail_prepare_kernel(PrepArgs a) {
     }
   }
   __syncthreads();
-  const int r0 = s_info[0], nv = s_info[1], m = s_info[2], use_mem = s_info[3];
+  const int use_mem = s_info[3];
   if (nv == 0) return;
   // image features: 24 xyz triplets (channels k, k+24, k+48) per pixel per view
   for (int idx = threadIdx.x; idx < nv * kPix * 24; idx += blockDim.x) {
@@ -327,6 +331,8 @@ struct DecodeArgs {
 // AdaptiveAvgPool2d + decoders (regressor.py:76-121,163-186) + wrist->world (umetrack_model.py:77-90)
 __global__ void __launch_bounds__(64) decode_kernel(DecodeArgs a) {
   __shared__ float f[64];
+  __shared__ double s_E0i[16];   // inv(E_cam0): computed by warp 0 while warp 1 runs the Procrustes fit
+  __shared__ int s_have_E0;
   const int i = blockIdx.x;
   const int t = threadIdx.x;
   if (t < a.n_out) {
@@ -335,6 +341,15 @@ __global__ void __launch_bounds__(64) decode_kernel(DecodeArgs a) {
     f[t] = s / 36.0f;
   }
   __syncthreads();
+  if (t == 0) {
+    const int64_t r0 = a.sample_range[2 * i];
+    s_have_E0 = r0 >= 0 && r0 < a.c;
+    if (s_have_E0) {
+      double E0[16];
+      load4x4(a.extrinsics + r0 * 16, E0);
+      mat4_inv(E0, s_E0i);
+    }
+  }
   if (t < 22) a.out.joint_angles[i * 22 + t] = t < 20 ? f[t] : 0.0f;  // decode_joint_angles
   const int sig0 = 41 + (a.predict_scale ? 1 : 0);
   if (t < 21) {  // decode_landmark_unc_sigmas: clamp(softplus(x), 1e-5); softplus threshold 20
@@ -342,6 +357,7 @@ __global__ void __launch_bounds__(64) decode_kernel(DecodeArgs a) {
     const float sp = x > 20.0f ? x : log1pf(expf(x));
     a.out.sigmas[i * 21 + t] = fmaxf(sp, 1e-5f);
   }
+  double Wc[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 1};
   if (t == 32) {
     if (a.predict_scale && a.out.skel_scales) a.out.skel_scales[i] = expf(f[41]);  // decode_skel_scales
     // decode_wrist_xfs_svd: Procrustes from the fixed 7-point template (regressor.py:19-47)
@@ -365,18 +381,17 @@ __global__ void __launch_bounds__(64) decode_kernel(DecodeArgs a) {
         for (int cc = 0; cc < 3; ++cc) H[r * 3 + cc] += ((double)(float)A[k][r] - am[r]) * (B[k][cc] - bm[cc]);
     double R[9];
     kabsch_rotation(H, R);
-    double Wc[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 1};
     for (int r = 0; r < 3; ++r) {
       for (int cc = 0; cc < 3; ++cc) Wc[r * 4 + cc] = R[r * 3 + cc];
       Wc[r * 4 + 3] = bm[r] - (R[r * 3] * am[0] + R[r * 3 + 1] * am[1] + R[r * 3 + 2] * am[2]);
     }
+  }
+  __syncthreads();   // s_E0i
+  if (t == 32) {
     // wrist in world = inv(E_cam0) @ wrist_in_cam0; right hand: negate column 0
-    const int64_t r0 = a.sample_range[2 * i];
-    double E0[16], E0i[16], Ww[16];
-    if (r0 >= 0 && r0 < a.c) {
-      load4x4(a.extrinsics + r0 * 16, E0);
-      mat4_inv(E0, E0i);
-      mat4_mul(E0i, Wc, Ww);
+    double Ww[16];
+    if (s_have_E0) {
+      mat4_mul(s_E0i, Wc, Ww);
     } else {
       for (int k = 0; k < 16; ++k) Ww[k] = Wc[k];
     }

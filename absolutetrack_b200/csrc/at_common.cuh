@@ -5,6 +5,8 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
 
 #include "absolutetrack_b200.h"
 
@@ -57,6 +59,31 @@ inline uint64_t this_device_bit() {
       at_once_mask_.fetch_or(at_bit_, std::memory_order_release);  \
     }                                                              \
   } while (0)
+
+// Programmatic dependent launch for the chains of short kernels (the tail: 18 launches of 10-30 us): launched with the
+// stream-serialization attribute a kernel becomes resident while its predecessor drains and runs up to its
+// pdl_prologue() - which every such kernel calls before it touches global memory - so the launch latency and the
+// CTA ramp-up overlap the previous kernel's tail.  A predecessor without the trigger simply completes first; a kernel
+// launched without the attribute passes through pdl_prologue() at once.  AT_TAIL_PDL=0: plain launches (A/B).
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+  static const bool on = getenv("AT_TAIL_PDL") == nullptr || atoi(getenv("AT_TAIL_PDL")) != 0;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = on ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_prologue() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+#endif
 
 template <typename K>
 inline void prefer_max_smem_carveout(K kernel) {

@@ -424,6 +424,7 @@ struct ConvArgsH {
 
 template <int BN>
 __global__ void __launch_bounds__(kConvThreads) conv_nhwc_f16x3_kernel(ConvArgsH ah_) {
+  pdl_prologue();
   const ConvArgs& a = ah_.a;
   constexpr int BM = 128;
   constexpr int WN = BN / 2;   // warp tile 32 x WN
@@ -778,10 +779,10 @@ int conv_nhwc_f16x3(const ConvLayer& L, const float* blob, const void* wsplit, c
   a.M = (int)M;
   if (f16x3_bn(L) == 96) {
     dim3 grid((unsigned)((M + 127) / 128), (unsigned)(h.Np / 96));
-    conv_nhwc_f16x3_kernel<96><<<grid, kConvThreads, 0, stream>>>(h);
+    launch_pdl(conv_nhwc_f16x3_kernel<96>, dim3(grid), dim3(kConvThreads), 0, stream, h);
   } else {
     dim3 grid((unsigned)((M + 127) / 128), (unsigned)(h.Np / 64));
-    conv_nhwc_f16x3_kernel<64><<<grid, kConvThreads, 0, stream>>>(h);
+    launch_pdl(conv_nhwc_f16x3_kernel<64>, dim3(grid), dim3(kConvThreads), 0, stream, h);
   }
   return check_launch("conv_nhwc_f16x3_kernel");
 }

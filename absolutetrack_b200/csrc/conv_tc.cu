@@ -654,6 +654,7 @@ Level make_level(int H, int W, int C, long long n_img) {
 
 // zero the front guard, everything behind the last image, and (optionally) the pad cells
 __global__ void zero_halo_kernel(uint4* base, long long n_planes, Level L, int zero_pads) {
+  pdl_prologue();
   const uint4 z = make_uint4(0u, 0u, 0u, 0u);
   const long long tail = L.plane_px - L.guard - L.P;  // cells behind the images (incl. back guard)
   const long long pads_per_img = zero_pads ? (L.Hp + L.Wp - 1) : 0;
@@ -682,7 +683,7 @@ int zero_halo(uint4* base, long long n_planes, const Level& L, bool pads, cudaSt
   const long long per_plane = L.guard + (L.plane_px - L.guard - L.P) + (pads ? (L.Hp + L.Wp - 1) * L.n_img : 0);
   const long long total = per_plane * n_planes;
   const int blocks = (int)std::min<long long>((total + 255) / 256, 148 * 8);
-  zero_halo_kernel<<<blocks, 256, 0, s>>>(base, n_planes, L, pads ? 1 : 0);
+  launch_pdl(zero_halo_kernel, dim3(blocks), dim3(256), 0, s, base, n_planes, L, pads ? 1 : 0);
   return check_launch("zero_halo_kernel");
 }
 
@@ -1699,6 +1700,7 @@ __global__ void head_prepack_kernel(const float* __restrict__ w /*[9][cin][coutP
 // order; pad cells are written as zeros.
 __global__ void head_split_pack_kernel(const float* __restrict__ in, uint4* __restrict__ base /*plane0,px0*/, Level L,
                                        int hc) {
+  pdl_prologue();
   const long long total = L.P * (kHeadCp / 8);
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
@@ -1755,7 +1757,7 @@ int head_tc_forward(const ConvLayer* L4, const float* blob, const void* const* w
   if ((rc = zero_halo(A, 2 * HL.planes(), HL, false, s))) return rc;
   {
     const long long total = HL.P * (kHeadCp / 8);
-    head_split_pack_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(x, A + HL.guard, HL, hc);
+    launch_pdl(head_split_pack_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, s, x, A + HL.guard, HL, hc);
     if ((rc = check_launch("head_split_pack_kernel"))) return rc;
   }
   auto conv = [&](int i, const uint4* in, const float* res, float* out_f32, uint4* out_split) -> int {

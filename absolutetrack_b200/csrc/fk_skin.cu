@@ -284,6 +284,7 @@ __global__ void __launch_bounds__(kFast, kFastCtas) fk_skin_shared_kernel(const 
                                                                   const int64_t* __restrict__ hand_idx, AtHandModel m,
                                                                   int64_t n, float* __restrict__ landmarks, float tscale,
                                                                   float* __restrict__ wrist_out) {
+  abt::pdl_prologue();
   extern __shared__ __align__(16) float smem[];
   __shared__ FastTables tb;
   __shared__ int s_b[64];
@@ -483,6 +484,7 @@ constexpr int kEvalWarps = 8;
 __global__ void __launch_bounds__(kEvalWarps * 32)
 eval_accumulate_kernel(const float* __restrict__ lm, const float* __restrict__ gt, const float* __restrict__ ja,
                        const float* __restrict__ gja, const uint8_t* __restrict__ valid, int64_t n, double* __restrict__ sums) {
+  abt::pdl_prologue();
   __shared__ float s_part[kEvalWarps][3];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float e_sum = 0.f, a_sum = 0.f, cnt = 0.f;
@@ -630,7 +632,7 @@ extern "C" int at_eval_accumulate_f32(const float* landmarks, const float* gt_la
   AT_REQUIRE(landmarks && gt_landmarks && sums, "at_eval_accumulate_f32: NULL pointer");
   AT_REQUIRE((joint_angles == nullptr) == (gt_joint_angles == nullptr), "at_eval_accumulate_f32: give both joint-angle arrays or none");
   const int64_t blocks = std::min<int64_t>((n + kEvalWarps - 1) / kEvalWarps, 4 * abt::kNumSMs);
-  eval_accumulate_kernel<<<(unsigned)blocks, kEvalWarps * 32, 0, (cudaStream_t)stream>>>(landmarks, gt_landmarks, joint_angles,
+  abt::launch_pdl(eval_accumulate_kernel, dim3((unsigned)blocks), dim3(kEvalWarps * 32), 0, (cudaStream_t)stream, landmarks, gt_landmarks, joint_angles,
                                                                                         gt_joint_angles, valid, n, sums);
   return abt::check_launch("eval_accumulate_kernel");
 }
@@ -663,7 +665,7 @@ extern "C" int at_fk_skin_scaled_f32(const float* joint_angles, const float* wri
         cudaFuncSetAttribute(fk_skin_shared_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fast_smem);
         cudaFuncSetAttribute(fk_skin_shared_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     const int64_t fb = std::min<int64_t>((n + kFast - 1) / kFast, kFastCtas * abt::kNumSMs);  // persistent
-    fk_skin_shared_kernel<<<(unsigned)fb, kFast, fast_smem, (cudaStream_t)stream>>>(
+    abt::launch_pdl(fk_skin_shared_kernel, dim3((unsigned)fb), dim3(kFast), fast_smem, (cudaStream_t)stream, 
         joint_angles, wrist_xforms, hand_idx, *model, n, landmarks, translation_scale, wrist_out);
     return abt::check_launch("fk_skin_shared_kernel");
   }

@@ -153,6 +153,7 @@ __device__ __forceinline__ void load4x4(const float* p, double* o) {
 __global__ void skeleton_kernel(const float* __restrict__ axes, const float* __restrict__ rest,
                                 const float* __restrict__ w, const float* __restrict__ b,
                                 float* __restrict__ out /*[n_skel,144]*/) {
+  pdl_prologue();
   __shared__ float in[132];
   const int s = blockIdx.x;
   for (int k = threadIdx.x; k < 132; k += blockDim.x) {
@@ -181,6 +182,7 @@ struct PrepArgs {
 // input, single-view shortcut (feature_extractor.py:89-94), and the memory warp / reset of
 // temporal.py:51-91 written into channels [0,18) of the temporal input.
 __global__ void __launch_bounds__(128) tail_prepare_kernel(PrepArgs a) {
+  pdl_prologue();
   __shared__ float X[2][12];  // per view: 3x3 R (row-major) + t
   __shared__ float Xm[12];
   __shared__ int s_info[4];   // r0, nv, mem slot, use_memory
@@ -282,6 +284,7 @@ __global__ void __launch_bounds__(128) tail_prepare_kernel(PrepArgs a) {
 __global__ void post_fusion_kernel(const float* __restrict__ fused /*[n,36,72]*/, const float* __restrict__ intrinsics,
                                    const int64_t* __restrict__ sample_range, int n, int c,
                                    float* __restrict__ temp_in /*[n,36,90]*/) {
+  pdl_prologue();
   const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= (int64_t)n * kPix * kFeat) return;
   const int ch = (int)(gid % kFeat);
@@ -300,6 +303,7 @@ __global__ void split_kernel(const float* __restrict__ t_out /*[n,36,90]*/, cons
                              int64_t capacity, float* __restrict__ mem /*[cap,36,18]*/,
                              const float* __restrict__ skel /*[n_skel,144] or null*/, int n_skel, int n, int head_c,
                              float* __restrict__ head_in /*[n,36,head_c]*/) {
+  pdl_prologue();
   const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int per = 90 + (head_c - kFeat);
   if (gid >= (int64_t)n * kPix * per) return;
@@ -330,6 +334,7 @@ struct DecodeArgs {
 
 // AdaptiveAvgPool2d + decoders (regressor.py:76-121,163-186) + wrist->world (umetrack_model.py:77-90)
 __global__ void __launch_bounds__(64) decode_kernel(DecodeArgs a) {
+  pdl_prologue();
   __shared__ float f[64];
   __shared__ double s_E0i[16];   // inv(E_cam0): computed by warp 0 while warp 1 runs the Procrustes fit
   __shared__ int s_have_E0;
@@ -525,7 +530,7 @@ extern "C" int at_tail_forward_f16(const float* blob, const void* f16_blob, cons
 
   PrepArgs pa;
   pa.in = *in; pa.st = *state; pa.fuse_in = fuse_in; pa.temp_in = temp_in; pa.status = out->status;
-  tail_prepare_kernel<<<n, 128, 0, s>>>(pa);
+  launch_pdl(tail_prepare_kernel, dim3(n), dim3(128), 0, s, pa);
   int rc = check_launch("tail_prepare_kernel");
   if (rc) return rc;
   // 2-view fusion (model_utils.py:141-163).  Rows of single-view samples are computed on
@@ -535,7 +540,7 @@ extern "C" int at_tail_forward_f16(const float* blob, const void* f16_blob, cons
   if ((rc = conv(L_FUSION + 2, f2, 72, nullptr, 0, f3, 72, false))) return rc;
   {
     const int64_t tot = (int64_t)n * kPix * kFeat;
-    post_fusion_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(f3, in->intrinsics, in->sample_range, n, c, temp_in);
+    launch_pdl(post_fusion_kernel, dim3((unsigned)((tot + 255) / 256)), dim3(256), 0, s, f3, in->intrinsics, in->sample_range, n, c, temp_in);
     if ((rc = check_launch("post_fusion_kernel"))) return rc;
   }
   // SimpleConvRNN step (temporal.py:76-91): 3x conv1x1(90->90), ReLU after the first two
@@ -545,13 +550,13 @@ extern "C" int at_tail_forward_f16(const float* blob, const void* f16_blob, cons
   const int hc = known ? 76 : 72;
   if (known) {
     const ConvLayer& L = T[L_SKEL];
-    skeleton_kernel<<<in->n_skel, 160, 0, s>>>(in->skel_axes, in->skel_rest, blob + L.weight_offset,
+    launch_pdl(skeleton_kernel, dim3(in->n_skel), dim3(160), 0, s, in->skel_axes, in->skel_rest, blob + L.weight_offset,
                                                blob + L.bias_offset, skel);
     if ((rc = check_launch("skeleton_kernel"))) return rc;
   }
   {
     const int64_t tot = (int64_t)n * kPix * (90 + hc - kFeat);
-    split_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(t3, in->memory_idx, state->capacity, state->mem_features,
+    launch_pdl(split_kernel, dim3((unsigned)((tot + 255) / 256)), dim3(256), 0, s, t3, in->memory_idx, state->capacity, state->mem_features,
                                                                known ? skel : nullptr, in->n_skel, n, hc, head_in);
     if ((rc = check_launch("split_kernel"))) return rc;
   }
@@ -575,6 +580,6 @@ extern "C" int at_tail_forward_f16(const float* blob, const void* f16_blob, cons
   da.head_out = ho; da.ld = 64; da.n_out = known ? 62 : 63;
   da.extrinsics = in->extrinsics; da.sample_range = in->sample_range; da.hand_idx = in->hand_idx;
   da.n = n; da.c = c; da.predict_scale = known ? 0 : 1; da.out = *out;
-  decode_kernel<<<n, 64, 0, s>>>(da);
+  launch_pdl(decode_kernel, dim3(n), dim3(64), 0, s, da);
   return check_launch("decode_kernel");
 }

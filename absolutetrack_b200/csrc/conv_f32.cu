@@ -424,7 +424,9 @@ struct ConvArgsH {
 
 template <int BN>
 __global__ void __launch_bounds__(kConvThreads) conv_nhwc_f16x3_kernel(ConvArgsH ah_) {
-  pdl_prologue();
+  // programmatic dependent launch: the index set-up and the first weight tile (constants) run while the previous kernel
+  // of the stream drains; its output - this conv's input - is first read behind griddepcontrol.wait below
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const ConvArgs& a = ah_.a;
   constexpr int BM = 128;
   constexpr int WN = BN / 2;   // warp tile 32 x WN
@@ -461,7 +463,22 @@ __global__ void __launch_bounds__(kConvThreads) conv_nhwc_f16x3_kernel(ConvArgsH
 
   float4 ra[A_F4];
   uint4 rb[B_V];
-  auto load_step = [&](int step) {
+  auto load_b = [&](int step) {
+    const int tap = step / kchunks;
+    const int k0 = (step - tap * kchunks) * BK;
+#pragma unroll
+    for (int i = 0; i < B_V; ++i) {
+      const int l = tid + i * kConvThreads;
+      rb[i] = make_uint4(0u, 0u, 0u, 0u);
+      if (l < 2 * BN * 2) {
+        const int part = l / (BN * 2), rem = l - part * (BN * 2);
+        const int n = rem >> 1, h = rem & 1;
+        rb[i] = __ldg(reinterpret_cast<const uint4*>(
+            ah_.wsplit + (((int64_t)part * taps + tap) * ah_.Np + n0 + n) * ah_.Kp + k0 + h * 8));
+      }
+    }
+  };
+  auto load_a = [&](int step) {
     const int tap = step / kchunks;
     const int k0 = (step - tap * kchunks) * BK;
     const int r = tap / a.ksize, s = tap - r * a.ksize;
@@ -484,18 +501,8 @@ __global__ void __launch_bounds__(kConvThreads) conv_nhwc_f16x3_kernel(ConvArgsH
       }
       ra[i] = v;
     }
-#pragma unroll
-    for (int i = 0; i < B_V; ++i) {
-      const int l = tid + i * kConvThreads;
-      rb[i] = make_uint4(0u, 0u, 0u, 0u);
-      if (l < 2 * BN * 2) {
-        const int part = l / (BN * 2), rem = l - part * (BN * 2);
-        const int n = rem >> 1, h = rem & 1;
-        rb[i] = __ldg(reinterpret_cast<const uint4*>(
-            ah_.wsplit + (((int64_t)part * taps + tap) * ah_.Np + n0 + n) * ah_.Kp + k0 + h * 8));
-      }
-    }
   };
+  auto load_step = [&](int step) { load_a(step); load_b(step); };
   auto store_step = [&](int buf) {
 #pragma unroll
     for (int i = 0; i < A_F4; ++i) {
@@ -531,7 +538,9 @@ __global__ void __launch_bounds__(kConvThreads) conv_nhwc_f16x3_kernel(ConvArgsH
   const int a_lrow = (lane & 7) + ((lane >> 3) & 1) * 8, a_lk = (lane >> 4) * 8;
   const int b_lrow = (lane & 7) + (lane >> 4) * 8, b_lk = ((lane >> 3) & 1) * 8;
 
-  load_step(0);
+  load_b(0);
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  load_a(0);
   store_step(0);
   __syncthreads();
   for (int step = 0; step < steps; ++step) {

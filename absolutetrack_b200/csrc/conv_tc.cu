@@ -1539,8 +1539,8 @@ int encoder_forward_bf16(const float* blob, const void* tc_blob, const void* cro
 #define AT_STEM_LAUNCH(TIN, F)                                                                                        \
   do {                                                                                                              \
     AT_CARVEOUT_ONCE((stem_mma_kernel<TIN, F>));                                                                    \
-    stem_mma_kernel<TIN, F><<<grid, kStemThreads, 0, ss>>>((const TIN*)crops + (size_t)cg0 * 96 * 96, (int)n, wf, bias, \
-                                                          buf(0, 0), L0, g_status, s2d ? 1 : 0);                    \
+    launch_pdl(stem_mma_kernel<TIN, F>, dim3(grid), dim3(kStemThreads), 0, ss, (const TIN*)crops + (size_t)cg0 * 96 * 96, (int)n, \
+               wf, bias, buf(0, 0), L0, g_status, s2d ? 1 : 0);                                                      \
   } while (0)
       if (crop_dtype == AT_U8) { if (fmt) AT_STEM_LAUNCH(uint8_t, 1); else AT_STEM_LAUNCH(uint8_t, 0); }
       else { if (fmt) AT_STEM_LAUNCH(float, 1); else AT_STEM_LAUNCH(float, 0); }

@@ -555,6 +555,7 @@ crop_resample_lattice_kernel(const uint8_t* __restrict__ src, int64_t frame_stri
   __shared__ int s_box[6];
   __shared__ float2 s_lat[kLatMaxDim * kLatPitch];
   __shared__ unsigned short s_list[kLatMaxFlagged];
+  abt::pdl_prologue();   // (programmatic dependent launch: resident while the previous kernel of the stream drains)
   const int crop = blockIdx.x;
   const AtCropParams& g = params[crop];
   if (threadIdx.x < 9) { P.M[threadIdx.x] = (float)g.M[threadIdx.x]; PD.M[threadIdx.x] = g.M[threadIdx.x]; }
@@ -1111,8 +1112,8 @@ extern "C" int at_crop_resample_fisheye62_u8_ex(const uint8_t* src, int64_t fram
         cudaFuncSetAttribute(crop_resample_lattice_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kLatStageBytes);
         cudaFuncSetAttribute(crop_resample_lattice_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     static const int exact = getenv("AT_CROP_EXACT") == nullptr || atoi(getenv("AT_CROP_EXACT")) != 0;  // 0: A/B only
-    crop_resample_lattice_kernel<<<(unsigned)n_crops, kThreads, kLatStageBytes, (cudaStream_t)stream>>>(
-        src, frame_stride, view_stride, row_stride, params, dst_w, dst_h, out, out_dtype, staged_bytes, exact);
+    abt::launch_pdl(crop_resample_lattice_kernel, dim3((unsigned)n_crops), dim3(kThreads), kLatStageBytes, (cudaStream_t)stream,
+                    src, frame_stride, view_stride, row_stride, params, dst_w, dst_h, out, out_dtype, staged_bytes, exact);
   } else if (dst_w % kFastPx == 0 && (src_on_host || staged_bytes != nullptr || getenv("AT_CROP_STAGED") != nullptr)) {
     AT_ONCE_PER_DEVICE(
         cudaFuncSetAttribute(crop_resample_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStageBytes);

@@ -52,6 +52,7 @@ stem_mma_kernel(const TIn* __restrict__ crops, int n_crops, const uint2* __restr
   __shared__ uint16_t lut[256];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int r = lane >> 2, j = lane & 3;
+  ptx::pdl_launch_dependents();   // layer1.0.conv1 may set up while this grid drains (it waits before its first load)
   uint2 bf[16];
 #pragma unroll
   for (int b = 0; b < 16; ++b) bf[b] = __ldg(wfrag + b * 32 + lane);
@@ -63,6 +64,7 @@ stem_mma_kernel(const TIn* __restrict__ crops, int n_crops, const uint2* __restr
   for (int i = tid; i < 2 * kStemPW; i += kStemThreads) tile[i < kStemPW ? i : (kStemRows - 1) * kStemPW + (i - kStemPW)] = 0u;
   const int HWp = L.Hp * L.Wp;
   uint32_t ovf = 0u;
+  ptx::pdl_wait();   // the crops come from the previous kernel of the stream (weights, bias and the table above do not)
   for (int crop = blockIdx.x; crop < n_crops; crop += gridDim.x) {
     __syncthreads();  // the previous crop's fragments have been read (and the table / border rows are written)
     // ---- stage: thread (row y, half h) converts 48 pixels (+1) into words (col 2m-1, col 2m)

@@ -1701,18 +1701,19 @@ __global__ void head_prepack_kernel(const float* __restrict__ w /*[9][cin][coutP
 __global__ void head_split_pack_kernel(const float* __restrict__ in, uint4* __restrict__ base /*plane0,px0*/, Level L,
                                        int hc) {
   pdl_prologue();
-  const long long total = L.P * (kHeadCp / 8);
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  // 32-bit index arithmetic (the launcher checks the range): the 64-bit divisions were most of this kernel
+  const uint32_t total = (uint32_t)L.P * (kHeadCp / 8);
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
-  const int cg = (int)(i % (kHeadCp / 8));
-  const long long g = i / (kHeadCp / 8);
-  const int HWp = L.Hp * L.Wp;
-  const long long img = g / HWp;
+  const uint32_t g = i / (kHeadCp / 8);
+  const int cg = (int)(i - g * (kHeadCp / 8));
+  const uint32_t HWp = (uint32_t)(L.Hp * L.Wp);
+  const uint32_t img = g / HWp;
   const int rem = (int)(g - img * HWp);
   const int y = rem / L.Wp, x = rem - y * L.Wp;
   uint4 hi = make_uint4(0u, 0u, 0u, 0u), lo = hi;
   if (y < L.H && x < L.W) {
-    const float* ip = in + ((img * L.H + y) * L.W + x) * hc + cg * 8;
+    const float* ip = in + ((long long)(img * L.H + y) * L.W + x) * hc + cg * 8;
     float v[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) v[k] = cg * 8 + k < hc ? ip[k] : 0.f;
@@ -1757,6 +1758,7 @@ int head_tc_forward(const ConvLayer* L4, const float* blob, const void* const* w
   if ((rc = zero_halo(A, 2 * HL.planes(), HL, false, s))) return rc;
   {
     const long long total = HL.P * (kHeadCp / 8);
+    AT_REQUIRE(total < (1LL << 31), "head_tc_forward: too many samples for one call");
     launch_pdl(head_split_pack_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, s, x, A + HL.guard, HL, hc);
     if ((rc = check_launch("head_split_pack_kernel"))) return rc;
   }

@@ -285,16 +285,19 @@ __global__ void post_fusion_kernel(const float* __restrict__ fused /*[n,36,72]*/
                                    const int64_t* __restrict__ sample_range, int n, int c,
                                    float* __restrict__ temp_in /*[n,36,90]*/) {
   pdl_prologue();
-  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (gid >= (int64_t)n * kPix * kFeat) return;
-  const int ch = (int)(gid % kFeat);
-  const int64_t ip = gid / kFeat;  // sample*36 + pixel
-  const int i = (int)(ip / kPix);
+  // one CTA per sample (the per-element version spent its time in 64-bit index divisions: 18 us for 10 MB)
+  const int i = blockIdx.x;
+  if (i >= n) return;
   const int64_t r0 = sample_range[2 * i], r1 = sample_range[2 * i + 1];
   if (r1 - r0 != 2 || r0 < 0 || r1 > c) return;
   const float sz = intrinsics[r0 * 9] / 200.0f;
-  const float v = fused[gid];
-  temp_in[ip * 90 + kMem + ch] = ch >= 48 ? sz * v : v;
+  const float* src = fused + (int64_t)i * kPix * kFeat;
+  float* dst = temp_in + (int64_t)i * kPix * 90 + kMem;
+  for (int idx = threadIdx.x; idx < kPix * kFeat; idx += blockDim.x) {
+    const int p = idx / kFeat, ch = idx - p * kFeat;
+    const float v = src[idx];
+    dst[p * 90 + ch] = ch >= 48 ? sz * v : v;
+  }
 }
 
 // After the temporal convs (temporal.py:84-91,127-137): out[:, :18] -> memory[memory_idx],
@@ -304,21 +307,28 @@ __global__ void split_kernel(const float* __restrict__ t_out /*[n,36,90]*/, cons
                              const float* __restrict__ skel /*[n_skel,144] or null*/, int n_skel, int n, int head_c,
                              float* __restrict__ head_in /*[n,36,head_c]*/) {
   pdl_prologue();
-  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int per = 90 + (head_c - kFeat);
-  if (gid >= (int64_t)n * kPix * per) return;
-  const int ch = (int)(gid % per);
-  const int64_t ip = gid / per;
-  const int i = (int)(ip / kPix), p = (int)(ip % kPix);
-  if (ch < kMem) {
-    const int64_t m = memory_idx[i];
-    if (m >= 0 && m < capacity) mem[(m * kPix + p) * kMem + ch] = t_out[ip * 90 + ch];
-  } else if (ch < 90) {
-    head_in[ip * head_c + (ch - kMem)] = t_out[ip * 90 + ch];
-  } else {
-    const int sc = ch - 90;  // skeleton channel 0..3, feature index sc*36 + p (View((-1,4,6,6)))
-    const int s = n_skel == 1 ? 0 : i;
-    head_in[ip * head_c + kFeat + sc] = skel[s * 144 + sc * kPix + p];
+  // one CTA per sample, 32-bit index arithmetic (see post_fusion_kernel)
+  const int i = blockIdx.x;
+  if (i >= n) return;
+  const int64_t m = memory_idx[i];
+  const bool m_ok = m >= 0 && m < capacity;
+  const float* src = t_out + (int64_t)i * kPix * 90;
+  float* hin = head_in + (int64_t)i * kPix * head_c;
+  float* mrow = mem + (m_ok ? m : 0) * kPix * kMem;
+  for (int idx = threadIdx.x; idx < kPix * 90; idx += blockDim.x) {
+    const int p = idx / 90, ch = idx - p * 90;
+    const float v = src[idx];
+    if (ch < kMem) {
+      if (m_ok) mrow[p * kMem + ch] = v;
+    } else {
+      hin[p * head_c + (ch - kMem)] = v;
+    }
+  }
+  const int extra = head_c - kFeat;  // skeleton channels 0..3, feature index sc*36 + p (View((-1,4,6,6)))
+  const float* sk = skel != nullptr ? skel + (int64_t)(n_skel == 1 ? 0 : i) * 144 : nullptr;
+  for (int idx = threadIdx.x; idx < kPix * extra; idx += blockDim.x) {
+    const int p = idx / extra, sc = idx - p * extra;
+    hin[p * head_c + kFeat + sc] = sk[sc * kPix + p];
   }
 }
 
@@ -539,8 +549,7 @@ extern "C" int at_tail_forward_f16(const float* blob, const void* f16_blob, cons
   if ((rc = conv(L_FUSION + 1, f1, 108, nullptr, 0, f2, 72, true))) return rc;
   if ((rc = conv(L_FUSION + 2, f2, 72, nullptr, 0, f3, 72, false))) return rc;
   {
-    const int64_t tot = (int64_t)n * kPix * kFeat;
-    launch_pdl(post_fusion_kernel, dim3((unsigned)((tot + 255) / 256)), dim3(256), 0, s, f3, in->intrinsics, in->sample_range, n, c, temp_in);
+    launch_pdl(post_fusion_kernel, dim3((unsigned)n), dim3(256), 0, s, f3, in->intrinsics, in->sample_range, n, c, temp_in);
     if ((rc = check_launch("post_fusion_kernel"))) return rc;
   }
   // SimpleConvRNN step (temporal.py:76-91): 3x conv1x1(90->90), ReLU after the first two
@@ -555,8 +564,7 @@ extern "C" int at_tail_forward_f16(const float* blob, const void* f16_blob, cons
     if ((rc = check_launch("skeleton_kernel"))) return rc;
   }
   {
-    const int64_t tot = (int64_t)n * kPix * (90 + hc - kFeat);
-    launch_pdl(split_kernel, dim3((unsigned)((tot + 255) / 256)), dim3(256), 0, s, t3, in->memory_idx, state->capacity, state->mem_features,
+    launch_pdl(split_kernel, dim3((unsigned)n), dim3(256), 0, s, t3, in->memory_idx, state->capacity, state->mem_features,
                                                                known ? skel : nullptr, in->n_skel, n, hc, head_in);
     if ((rc = check_launch("split_kernel"))) return rc;
   }

@@ -181,7 +181,7 @@ struct PrepArgs {
 // per-view features into the canonical space (feature_extractor.py:123-128) laid out as the fusion
 // input, single-view shortcut (feature_extractor.py:89-94), and the memory warp / reset of
 // temporal.py:51-91 written into channels [0,18) of the temporal input.
-__global__ void __launch_bounds__(128) tail_prepare_kernel(PrepArgs a) {
+__global__ void __launch_bounds__(128, 7) tail_prepare_kernel(PrepArgs a) {   // 1,024 CTAs (one per sample) fit ONE wave of 148 x 7
   pdl_prologue();
   __shared__ float X[2][12];  // per view: 3x3 R (row-major) + t
   __shared__ float Xm[12];

@@ -546,3 +546,35 @@ def test_ctypes_structs_match_the_c_header(tmp_path):
     out = dict(line.split() for line in subprocess.check_output([str(exe)], text=True).splitlines())
     for n in names:
         assert int(out[n]) == ctypes.sizeof(getattr(_cabi, n)), n
+
+
+def test_layer1_space_to_depth_weight_mapping_is_the_same_convolution():
+    """The encoder runs layer 1 (3x3, 32 -> 32, 48 x 48) as a 3x3 conv with 64 -> 64 channels over the x-space-to-depth
+    view (rows of 24 pixel pairs, channels [even column | odd column]); csrc/conv_tc.cu::prepack_s2d_kernel builds the
+    weights as W'[dy][di][(pi, ci)][(po, co)] = W[dy][dx = 2 di + pi - po][ci][co] for |dx| <= 1, else 0.  Restated in
+    torch on the CPU: both forms are the same convolution, the side taps (di = +-1) only connect one input parity to
+    one output parity (the K steps / column halves the kernel does not issue), and the bias wraps modulo 32."""
+    import torch
+    import torch.nn.functional as F
+
+    g = torch.Generator().manual_seed(3)
+    w = torch.randn(32, 32, 3, 3, generator=g, dtype=torch.float64)   # [co, ci, ky, kx]
+    b = torch.randn(32, generator=g, dtype=torch.float64)
+    x = torch.randn(2, 32, 48, 48, generator=g, dtype=torch.float64)
+    ref = F.conv2d(x, w, b, padding=1)
+
+    w2 = torch.zeros(64, 64, 3, 3, dtype=torch.float64)               # [(po, co), (pi, ci), ky, kdi]
+    for di in (-1, 0, 1):
+        for pi in (0, 1):
+            for po in (0, 1):
+                dx = 2 * di + pi - po
+                if -1 <= dx <= 1:
+                    w2[po * 32:(po + 1) * 32, pi * 32:(pi + 1) * 32, :, di + 1] = w[:, :, :, dx + 1]
+    # structural zeros the kernel skips: di = -1 uses only odd inputs -> even outputs, di = +1 even inputs -> odd outputs
+    assert not w2[:, :32, :, 0].any() and not w2[32:, :, :, 0].any()
+    assert not w2[:, 32:, :, 2].any() and not w2[:32, :, :, 2].any()
+    xs = torch.cat([x[:, :, :, 0::2], x[:, :, :, 1::2]], dim=1)        # [n, 64, 48, 24]
+    ys = F.conv2d(xs, w2, b.repeat(2), padding=1)
+    out = torch.empty_like(ref)
+    out[:, :, :, 0::2], out[:, :, :, 1::2] = ys[:, :32], ys[:, 32:]
+    assert torch.allclose(out, ref, rtol=0, atol=1e-12)

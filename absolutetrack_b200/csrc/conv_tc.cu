@@ -1389,7 +1389,13 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
     }
   }
   {
-    static const bool use_pdl = getenv("AT_TC_PDL") == nullptr || atoi(getenv("AT_TC_PDL")) != 0;
+    // Programmatic dependent launch.  Backbone layers: off by default since round 2 - with one 220 KB CTA per SM the next
+    // layer's CTAs cannot become resident before their predecessors exit anyway, and their resident-weight loads then
+    // compete with the stragglers: 2.36 -> 2.33 ms per 2048 crops without it (ABAB on two boxes, AT_TC_PDL=1 for A/B).
+    // The pose-head convs (out_mode 3) sit in the tail's chain of short kernels and follow AT_TAIL_PDL (default on).
+    static const bool pdl_backbone = getenv("AT_TC_PDL") != nullptr && atoi(getenv("AT_TC_PDL")) != 0;
+    static const bool pdl_tail = getenv("AT_TAIL_PDL") == nullptr || atoi(getenv("AT_TAIL_PDL")) != 0;
+    const bool use_pdl = io.out_mode == 3 ? pdl_tail : pdl_backbone;
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
     cfg.gridDim = dim3((unsigned)grid);

@@ -1288,7 +1288,8 @@ int launch_conv_tc(int layer_id, const float* blob, const void* tc_blob, const L
     p.w_block_bytes = io.s2d ? (uint32_t)kS2dUnitBytes : (uint32_t)(p.kc * p.n * 2);
     p.sc_a_bytes = (uint32_t)p.sc_planes * p.a_plane_bytes;
     p.w_resident = (int64_t)nblocks * p.w_block_bytes <= 100 * 1024;
-    p.ws = p.w_resident ? nblocks : 4;
+    static const int ws_stream = getenv("AT_TC_WS") != nullptr ? std::max(2, atoi(getenv("AT_TC_WS"))) : 4;   // A/B knob: weight ring depth
+    p.ws = p.w_resident ? nblocks : ws_stream;
     while (!p.w_resident && p.ws > 2 && (int64_t)p.ws * p.w_block_bytes > 128 * 1024) --p.ws;
     w_bytes = (int64_t)p.ws * p.w_block_bytes;
     ra = (kSmemBudget - w_bytes - misc) / p.a_slot_bytes;
